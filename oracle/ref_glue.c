@@ -1,0 +1,292 @@
+/* TEST INFRASTRUCTURE -- not part of the product.
+ *
+ * Glue that exposes the UNMODIFIED reference (KyleSiefring/daala, compiled from
+ * the sources where they lie under /root/reference by oracle/Makefile) to the
+ * tests through a flat C interface.  Nothing here re-implements arithmetic:
+ * every sample goes through the reference's own functions.
+ *
+ * This translation unit #includes the reference's src/encode.c (the idiom the
+ * reference itself uses in src/tests/test_coef_coder.c:25-34) so that the
+ * `static` driver od_compute_dcts (src/encode.c:1286-1343) is reachable.
+ * The inverse walk below mirrors the transform slices of od_decode_recursive
+ * (src/decode.c:842-866) and od_block_decode (src/decode.c:632-638), which are
+ * interleaved with entropy decoding in the reference and so cannot be called
+ * as they are.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load the library built from this file.
+ */
+#include <stdlib.h>
+#include <string.h>
+#include "encode.c"
+#include "tf.h"
+
+typedef struct ref_ctx {
+  daala_enc_ctx *enc;
+  int pic_width;
+  int pic_height;
+} ref_ctx;
+
+/* impl: 0 = generic C tables (OD_FDCT_2D_C), 1 = whatever the reference's
+   runtime CPU dispatch installs (src/x86/x86state.c:39-97). */
+static void ref_pick_vtbl(ref_ctx *r, int impl) {
+  int i;
+  if (impl == 0) {
+    for (i = 0; i <= OD_NBSIZES; i++) {
+      r->enc->state.opt_vtbl.fdct_2d[i] = OD_FDCT_2D_C[i];
+      r->enc->state.opt_vtbl.idct_2d[i] = OD_IDCT_2D_C[i];
+    }
+  }
+  else {
+#if defined(OD_X86ASM)
+    od_state_opt_vtbl_init_x86(&r->enc->state);
+#endif
+  }
+}
+
+void *ref_ctx_create(int pic_width, int pic_height) {
+  daala_info info;
+  ref_ctx *r;
+  daala_info_init(&info);
+  info.pic_width = pic_width;
+  info.pic_height = pic_height;
+  info.nplanes = 3;
+  info.plane_info[0].xdec = info.plane_info[0].ydec = 0;
+  info.plane_info[1].xdec = info.plane_info[1].ydec = 1;
+  info.plane_info[2].xdec = info.plane_info[2].ydec = 1;
+  info.timebase_numerator = 30;
+  info.timebase_denominator = 1;
+  info.frame_duration = 1;
+  info.pixel_aspect_numerator = 1;
+  info.pixel_aspect_denominator = 1;
+  info.keyframe_rate = 1;
+  r = (ref_ctx *)calloc(1, sizeof(*r));
+  if (!r) return NULL;
+  r->enc = daala_encode_create(&info);
+  if (!r->enc) {
+    free(r);
+    return NULL;
+  }
+  r->pic_width = pic_width;
+  r->pic_height = pic_height;
+  return r;
+}
+
+void ref_ctx_free(void *h) {
+  ref_ctx *r = (ref_ctx *)h;
+  if (!r) return;
+  daala_encode_free(r->enc);
+  free(r);
+}
+
+int ref_ctx_frame_width(void *h) { return ((ref_ctx *)h)->enc->state.frame_width; }
+int ref_ctx_frame_height(void *h) { return ((ref_ctx *)h)->enc->state.frame_height; }
+int ref_ctx_nhsb(void *h) { return ((ref_ctx *)h)->enc->state.nhsb; }
+int ref_ctx_nvsb(void *h) { return ((ref_ctx *)h)->enc->state.nvsb; }
+
+/* Copies a caller map (one byte per 8x8 luma block, nhsb*4 x nvsb*4 entries,
+   row stride `stride`) into the state's padded map. */
+static void ref_load_bsize(ref_ctx *r, const unsigned char *bsize, int stride) {
+  od_state *s = &r->enc->state;
+  int i;
+  int j;
+  for (i = 0; i < s->nvsb*OD_BSIZE_GRID; i++) {
+    for (j = 0; j < s->nhsb*OD_BSIZE_GRID; j++) {
+      s->bsize[i*s->bstride + j] = bsize[i*stride + j];
+    }
+  }
+}
+
+/* Forward stage of one plane, exactly as od_encode_coefficients runs it
+   (src/encode.c:2425-2429, 2492): SB-edge prefilter over the plane, then
+   od_compute_dcts on every superblock.  c is lapped in place, d receives the
+   coefficients.  Both are (frame_width>>dec) x (frame_height>>dec). */
+void ref_tdlt_fwd_plane(void *h, od_coeff *d, od_coeff *c, int dec,
+ const unsigned char *bsize, int bsize_stride, int is_keyframe, int use_haar,
+ int impl) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *s = &r->enc->state;
+  od_mb_enc_ctx ctx;
+  od_coeff *dplanes[OD_NPLANES_MAX];
+  int sbx;
+  int sby;
+  ref_pick_vtbl(r, impl);
+  ref_load_bsize(r, bsize, bsize_stride);
+  memset(&ctx, 0, sizeof(ctx));
+  memset(dplanes, 0, sizeof(dplanes));
+  dplanes[0] = d;
+  ctx.d = dplanes;
+  ctx.c = c;
+  ctx.is_keyframe = is_keyframe;
+  ctx.use_haar_wavelet = use_haar;
+  if (!use_haar) {
+    od_apply_prefilter_frame_sbs(c, s->frame_width >> dec, s->nhsb, s->nvsb,
+     dec, dec);
+  }
+  for (sby = 0; sby < s->nvsb; sby++) {
+    for (sbx = 0; sbx < s->nhsb; sbx++) {
+      od_compute_dcts(r->enc, &ctx, 0, sbx, sby, OD_NBSIZES - 1, dec, dec,
+       use_haar);
+    }
+  }
+}
+
+static void ref_inv_recursive(ref_ctx *r, od_coeff *c, od_coeff *d, int bx,
+ int by, int bsi, int dec, int dc_split, int use_haar) {
+  od_state *s = &r->enc->state;
+  int obs;
+  int bs;
+  int w;
+  int bo;
+  w = s->frame_width >> dec;
+  obs = OD_BLOCK_SIZE4x4(s->bsize, s->bstride, bx << bsi, by << bsi);
+  bs = OD_MAXI(obs, dec);
+  if (bs == bsi) {
+    bs -= dec;
+    bo = (by << (OD_LOG_BSIZE0 + bs))*w + (bx << (OD_LOG_BSIZE0 + bs));
+    if (use_haar) od_haar_inv(c + bo, w, d + bo, w, bs + 2);
+    else (*s->opt_vtbl.idct_2d[bs])(c + bo, w, d + bo, w);
+  }
+  else {
+    int f;
+    int hfilter;
+    int vfilter;
+    bs = bsi - dec;
+    f = OD_FILT_SIZE(bs - 1, dec);
+    bo = (by << (OD_LOG_BSIZE0 + bs))*w + (bx << (OD_LOG_BSIZE0 + bs));
+    hfilter = (bx + 1) << (OD_LOG_BSIZE0 + bs) <= s->info.pic_width;
+    vfilter = (by + 1) << (OD_LOG_BSIZE0 + bs) <= s->info.pic_height;
+    if (dc_split) {
+      /* The decoder's top-down DC reconstruction, src/decode.c:722-738, with
+         no quantisation or gradient prediction in between. */
+      od_coeff x[4];
+      int ln;
+      int cx;
+      int cy;
+      ln = bsi - 1 - dec + 2;
+      cx = 2*bx;
+      cy = 2*by;
+      x[0] = d[(cy << ln)*w + (cx << ln)];
+      x[1] = d[(cy << ln)*w + ((cx + 1) << ln)];
+      x[2] = d[((cy + 1) << ln)*w + (cx << ln)];
+      x[3] = d[((cy + 1) << ln)*w + ((cx + 1) << ln)];
+      OD_HAAR_KERNEL(x[0], x[1], x[2], x[3]);
+      d[(cy << ln)*w + (cx << ln)] = x[0];
+      d[(cy << ln)*w + ((cx + 1) << ln)] = x[1];
+      d[((cy + 1) << ln)*w + (cx << ln)] = x[2];
+      d[((cy + 1) << ln)*w + ((cx + 1) << ln)] = x[3];
+    }
+    ref_inv_recursive(r, c, d, 2*bx + 0, 2*by + 0, bsi - 1, dec, dc_split,
+     use_haar);
+    ref_inv_recursive(r, c, d, 2*bx + 1, 2*by + 0, bsi - 1, dec, dc_split,
+     use_haar);
+    ref_inv_recursive(r, c, d, 2*bx + 0, 2*by + 1, bsi - 1, dec, dc_split,
+     use_haar);
+    ref_inv_recursive(r, c, d, 2*bx + 1, 2*by + 1, bsi - 1, dec, dc_split,
+     use_haar);
+    od_postfilter_split(c + bo, w, bs, f, 0, NULL, 0, hfilter, vfilter);
+  }
+}
+
+/* Inverse stage of one plane: per superblock the decoder's recursion (DC
+   split, leaf inverse transforms, split postfilters), then the SB-edge
+   postfilter over the plane (src/decode.c:1010-1041).  d is modified when
+   dc_split is set, as it is in the decoder. */
+void ref_tdlt_inv_plane(void *h, od_coeff *c, od_coeff *d, int dec,
+ const unsigned char *bsize, int bsize_stride, int dc_split, int use_haar,
+ int impl) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *s = &r->enc->state;
+  int sbx;
+  int sby;
+  ref_pick_vtbl(r, impl);
+  ref_load_bsize(r, bsize, bsize_stride);
+  for (sby = 0; sby < s->nvsb; sby++) {
+    for (sbx = 0; sbx < s->nhsb; sbx++) {
+      ref_inv_recursive(r, c, d, sbx, sby, OD_NBSIZES - 1, dec, dc_split,
+       use_haar);
+    }
+  }
+  if (!use_haar) {
+    od_apply_postfilter_frame_sbs(c, s->frame_width >> dec, s->nhsb, s->nvsb,
+     dec, dec, 0, NULL, 0);
+  }
+}
+
+/* Pixel <-> coefficient conversion (src/state.c:1209-1315) on raw buffers.
+   xstride is 1 (8-bit references) or 2 (16-bit references). */
+void ref_buf_to_coeff(int bitdepth_mode, od_coeff *dst, int dst_ystride,
+ int lossless_p, unsigned char *src, int src_xstride, int src_ystride, int w,
+ int h) {
+  od_state *s = (od_state *)calloc(1, sizeof(*s));
+  s->info.bitdepth_mode = bitdepth_mode;
+  od_ref_buf_to_coeff(s, dst, dst_ystride, lossless_p, src, src_xstride,
+   src_ystride, w, h);
+  free(s);
+}
+
+void ref_coeff_to_buf(int bitdepth_mode, unsigned char *dst, int dst_xstride,
+ int dst_ystride, od_coeff *src, int src_ystride, int lossless_p, int w,
+ int h) {
+  od_state *s = (od_state *)calloc(1, sizeof(*s));
+  s->info.bitdepth_mode = bitdepth_mode;
+  od_coeff_to_ref_buf(s, dst, dst_xstride, dst_ystride, src, src_ystride,
+   lossless_p, w, h);
+  free(s);
+}
+
+/* 1-D transforms through the reference's tables (src/dct.c:58-72). */
+void ref_fdct1d(int bs, od_coeff *y, const od_coeff *x, int xstride) {
+  (*OD_FDCT_1D[bs])(y, x, xstride);
+}
+
+void ref_idct1d(int bs, od_coeff *x, int xstride, const od_coeff *y) {
+  (*OD_IDCT_1D[bs])(x, xstride, y);
+}
+
+/* Runs the real encoder on one 4:2:0 8-bit frame (y, u, v are pic-sized /
+   half-sized planes) as a keyframe, and returns the block-size map its RDO
+   chose (nhsb*4 x nvsb*4 bytes, tightly packed) -- used to obtain realistic
+   maps for BASELINE config 1/3.  Returns 0 on success. */
+int ref_encode_keyframe_bsize(void *h, const unsigned char *y,
+ const unsigned char *u, const unsigned char *v, int quality, int complexity,
+ unsigned char *bsize_out) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *s = &r->enc->state;
+  od_img img;
+  daala_packet pkt;
+  int i;
+  int j;
+  int ret;
+  int left;
+  int bframes;
+  memset(&img, 0, sizeof(img));
+  img.nplanes = 3;
+  img.width = r->pic_width;
+  img.height = r->pic_height;
+  img.planes[0].data = (unsigned char *)y;
+  img.planes[0].xstride = 1;
+  img.planes[0].ystride = r->pic_width;
+  img.planes[1].data = (unsigned char *)u;
+  img.planes[1].xdec = img.planes[1].ydec = 1;
+  img.planes[1].xstride = 1;
+  img.planes[1].ystride = (r->pic_width + 1) >> 1;
+  img.planes[2].data = (unsigned char *)v;
+  img.planes[2].xdec = img.planes[2].ydec = 1;
+  img.planes[2].xstride = 1;
+  img.planes[2].ystride = (r->pic_width + 1) >> 1;
+  daala_encode_ctl(r->enc, OD_SET_QUANT, &quality, sizeof(quality));
+  daala_encode_ctl(r->enc, OD_SET_COMPLEXITY, &complexity, sizeof(complexity));
+  bframes = 0;
+  daala_encode_ctl(r->enc, OD_SET_B_FRAMES, &bframes, sizeof(bframes));
+  left = 0;
+  ret = daala_encode_img_in(r->enc, &img, 0, 0, &left);
+  if (ret < 0) return ret;
+  while (daala_encode_packet_out(r->enc, 0, &pkt) > 0);
+  for (i = 0; i < s->nvsb*OD_BSIZE_GRID; i++) {
+    for (j = 0; j < s->nhsb*OD_BSIZE_GRID; j++) {
+      bsize_out[i*s->nhsb*OD_BSIZE_GRID + j] = s->bsize[i*s->bstride + j];
+    }
+  }
+  return 0;
+}

@@ -1,0 +1,197 @@
+"""ctypes bindings for the two CHECKERS (test infrastructure only):
+
+* ``port``  -- oracle/libtdlt_oracle.so, the plain-C restatement.
+* ``ref``   -- oracle/_ref/libdaala_ref.so, the unmodified reference compiled
+               from /root/reference by oracle/Makefile (present wherever
+               ``__graft_entry__.build()`` ran with the reference mounted; it
+               travels to the GPU box as a prebuilt file).
+
+Nothing under daala_b200/ imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+PORT_SO = os.path.join(ORACLE_DIR, "libtdlt_oracle.so")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libdaala_ref.so")
+
+I32P = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+U8P = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+def _ensure_port():
+    if not os.path.exists(PORT_SO) or (
+            os.path.getmtime(PORT_SO) < os.path.getmtime(os.path.join(ORACLE_DIR, "tdlt_oracle.c"))):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "port"], stdout=subprocess.DEVNULL)
+
+
+_port = None
+_ref = None
+
+
+def port():
+    """The C restatement (always buildable: needs only gcc)."""
+    global _port
+    if _port is None:
+        _ensure_port()
+        _port = C.CDLL(PORT_SO)
+    return _port
+
+
+def have_ref():
+    if os.path.exists(REF_SO):
+        return True
+    if os.path.isdir("/root/reference/src"):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "ref", "-j8"], stdout=subprocess.DEVNULL)
+        return os.path.exists(REF_SO)
+    return False
+
+
+def ref():
+    """The compiled reference (None-safe: call have_ref() first)."""
+    global _ref
+    if _ref is None:
+        assert have_ref(), "oracle/_ref/libdaala_ref.so is not built"
+        _ref = C.CDLL(REF_SO)
+        _ref.ref_ctx_create.restype = C.c_void_p
+        _ref.ref_ctx_create.argtypes = [C.c_int, C.c_int]
+        _ref.ref_ctx_free.argtypes = [C.c_void_p]
+        for f in ("ref_ctx_frame_width", "ref_ctx_frame_height", "ref_ctx_nhsb", "ref_ctx_nvsb"):
+            getattr(_ref, f).argtypes = [C.c_void_p]
+    return _ref
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def padded_dims(pic_w, pic_h):
+    """Frame dimensions: picture padded to a multiple of 64 (reference
+    src/state.c:372-375)."""
+    return (pic_w + 63) & ~63, (pic_h + 63) & ~63
+
+
+# ---------------------------------------------------------------- port API --
+def port_fwd_plane(c, bsize, dec, pic_w, pic_h, keyframe, use_haar=0):
+    """c: (H, W) int32 spatial plane.  Returns (d, lapped c)."""
+    lib = port()
+    c = np.ascontiguousarray(c, dtype=np.int32).copy()
+    d = np.zeros_like(c)
+    H, W = c.shape
+    nhsb, nvsb = (W << dec) // 32, (H << dec) // 32
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    lib.oc_tdlt_fwd_plane(ptr(d), ptr(c), nhsb, nvsb, dec, ptr(bsize), bsize.shape[1],
+                          pic_w, pic_h, int(keyframe), int(use_haar))
+    return d, c
+
+
+def port_inv_plane(d, bsize, dec, pic_w, pic_h, dc_split, use_haar=0):
+    lib = port()
+    d = np.ascontiguousarray(d, dtype=np.int32).copy()
+    c = np.zeros_like(d)
+    H, W = d.shape
+    nhsb, nvsb = (W << dec) // 32, (H << dec) // 32
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    lib.oc_tdlt_inv_plane(ptr(c), ptr(d), nhsb, nvsb, dec, ptr(bsize), bsize.shape[1],
+                          pic_w, pic_h, int(dc_split), int(use_haar))
+    return c
+
+
+# ----------------------------------------------------------------- ref API --
+class RefCtx:
+    """An instance of the reference encoder state for one picture size."""
+
+    def __init__(self, pic_w, pic_h):
+        self.lib = ref()
+        self.h = self.lib.ref_ctx_create(pic_w, pic_h)
+        assert self.h, "daala_encode_create failed"
+        self.pic_w, self.pic_h = pic_w, pic_h
+        self.fw = self.lib.ref_ctx_frame_width(self.h)
+        self.fh = self.lib.ref_ctx_frame_height(self.h)
+        self.nhsb = self.lib.ref_ctx_nhsb(self.h)
+        self.nvsb = self.lib.ref_ctx_nvsb(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.ref_ctx_free(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def fwd_plane(self, c, bsize, dec, keyframe, use_haar=0, impl=0):
+        c = np.ascontiguousarray(c, dtype=np.int32).copy()
+        assert c.shape == (self.fh >> dec, self.fw >> dec)
+        d = np.zeros_like(c)
+        bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+        self.lib.ref_tdlt_fwd_plane(C.c_void_p(self.h), ptr(d), ptr(c), dec, ptr(bsize),
+                                    bsize.shape[1], int(keyframe), int(use_haar), impl)
+        return d, c
+
+    def inv_plane(self, d, bsize, dec, dc_split, use_haar=0, impl=0):
+        d = np.ascontiguousarray(d, dtype=np.int32).copy()
+        c = np.zeros_like(d)
+        bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+        self.lib.ref_tdlt_inv_plane(C.c_void_p(self.h), ptr(c), ptr(d), dec, ptr(bsize),
+                                    bsize.shape[1], int(dc_split), int(use_haar), impl)
+        return c
+
+    def encode_keyframe_bsize(self, y, u, v, quality=20, complexity=7):
+        out = np.zeros((self.nvsb * 4, self.nhsb * 4), dtype=np.uint8)
+        y, u, v = (np.ascontiguousarray(p, dtype=np.uint8) for p in (y, u, v))
+        rc = self.lib.ref_encode_keyframe_bsize(C.c_void_p(self.h), ptr(y), ptr(u), ptr(v),
+                                                quality, complexity, ptr(out))
+        assert rc == 0, rc
+        return out
+
+
+# ------------------------------------------------------------- generators --
+def lcg_stream(seed, n):
+    """The IEEE-1180 style LCG the reference's self-test seeds its vectors with
+    (x = x*1103515245 + 12345, reference src/dct.c:2385)."""
+    out = np.empty(n, dtype=np.int64)
+    x = seed
+    for i in range(n):
+        x = (x * 1103515245 + 12345) & 0xFFFFFFFF
+        out[i] = x
+    return out
+
+
+def random_quadtree_bsize(nhsb, nvsb, rng, p32=0.8, p16=0.6, p8=0.5):
+    """Random block-size map: one byte per 8x8 luma block."""
+    b = np.full((nvsb * 4, nhsb * 4), 3, dtype=np.uint8)
+    for sy in range(nvsb):
+        for sx in range(nhsb):
+            if rng.random() >= p32:
+                continue
+            for qy in range(2):
+                for qx in range(2):
+                    y0, x0 = sy * 4 + qy * 2, sx * 4 + qx * 2
+                    if rng.random() >= p16:
+                        b[y0:y0 + 2, x0:x0 + 2] = 2
+                        continue
+                    for ry in range(2):
+                        for rx in range(2):
+                            b[y0 + ry, x0 + rx] = 0 if rng.random() < p8 else 1
+    return b
+
+
+def ar1_plane(h, w, rng, rho=0.95, sigma=40.0, mean=0.0, scale=16, lo=-2048, hi=2047):
+    """Separable AR(1) field (the reference's own image model, src/dct.c:2209-2222),
+    returned as int32 coefficients-domain samples."""
+    e = rng.standard_normal((h, w)) * sigma * (1 - rho * rho)
+    a = np.empty_like(e)
+    a[0] = e[0]
+    for i in range(1, h):
+        a[i] = rho * a[i - 1] + e[i]
+    for j in range(1, w):
+        a[:, j] = rho * a[:, j - 1] + a[:, j]
+    v = np.clip(np.rint(a + mean) * scale, lo, hi)
+    return v.astype(np.int32)

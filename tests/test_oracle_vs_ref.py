@@ -1,0 +1,259 @@
+"""Pins the C restatement (oracle/tdlt_oracle.c) against the UNMODIFIED reference
+compiled into oracle/_ref/libdaala_ref.so -- element by element, on the kind of
+vectors the reference's own self-test uses (src/dct.c:3322-3391, 3439-3469:
+uniform ranges +-256/255, +-5, +-300 scaled by OD_COEFF_SCALE; impulses and
+extremes :3759-3830; all sign patterns of +-676 for the filters,
+src/filter.c:2041-2116).  CPU only.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_libs as ol
+from oracle_libs import ptr
+
+SIZES = [0, 1, 2, 3]
+
+
+def _vectors(n, rng, count=400):
+    """Rows of length n: self-test style ranges, impulses, extremes."""
+    rows = []
+    for lo, hi in ((-256, 255), (-5, 5), (-300, 300)):
+        rows.append(rng.integers(lo, hi + 1, size=(count, n)) * 16)
+    rows.append(rng.integers(-(1 << 15), 1 << 15, size=(count, n)))
+    imp = np.zeros((2 * n, n), dtype=np.int64)
+    for i in range(n):
+        imp[2 * i, i] = 255 * 16
+        imp[2 * i + 1, i] = -256 * 16
+    rows.append(imp)
+    ext = np.where(rng.integers(0, 2, size=(count, n)) > 0, 255 * 16, -256 * 16)
+    rows.append(ext)
+    return np.ascontiguousarray(np.concatenate(rows, 0), dtype=np.int32)
+
+
+@pytest.mark.parametrize("bs", SIZES)
+def test_dct_1d_matches_reference(reflib, bs):
+    n = 4 << bs
+    rng = np.random.default_rng(100 + bs)
+    X = _vectors(n, rng)
+    port = ol.port()
+    for x in X:
+        y_p = np.zeros(n, np.int32)
+        y_r = np.zeros(n, np.int32)
+        port.oc_fdct1d(bs, ptr(y_p), ptr(x), 1)
+        reflib.ref_fdct1d(bs, ptr(y_r), ptr(x), 1)
+        assert np.array_equal(y_p, y_r)
+        # inverse on RAW vectors as coefficients (not only on fdct outputs)
+        x_p = np.zeros(n, np.int32)
+        x_r = np.zeros(n, np.int32)
+        port.oc_idct1d(bs, ptr(x_p), 1, ptr(x))
+        reflib.ref_idct1d(bs, ptr(x_r), 1, ptr(x))
+        assert np.array_equal(x_p, x_r)
+        # perfect reconstruction
+        port.oc_idct1d(bs, ptr(x_p), 1, ptr(y_p))
+        assert np.array_equal(x_p, x)
+
+
+def _ref_2d(reflib, name):
+    f = getattr(reflib, name)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    return f
+
+
+@pytest.mark.parametrize("bs", SIZES)
+def test_dct_2d_matches_reference_c_and_simd(reflib, bs):
+    n = 4 << bs
+    rng = np.random.default_rng(200 + bs)
+    port = ol.port()
+    nm = "%dx%d" % (n, n)
+    fwd = [_ref_2d(reflib, "od_bin_fdct" + nm)]
+    inv = [_ref_2d(reflib, "od_bin_idct" + nm)]
+    if bs == 0:
+        fwd += [_ref_2d(reflib, "od_bin_fdct4x4_sse2"), _ref_2d(reflib, "od_bin_fdct4x4_sse41")]
+        inv += [_ref_2d(reflib, "od_bin_idct4x4_sse2"), _ref_2d(reflib, "od_bin_idct4x4_sse41")]
+    if bs == 1:
+        fwd += [_ref_2d(reflib, "od_bin_fdct8x8_" + s) for s in ("sse2", "sse41", "avx2")]
+        inv += [_ref_2d(reflib, "od_bin_idct8x8_" + s) for s in ("sse2", "sse41", "avx2")]
+    blocks = _vectors(n * n, rng, count=60 if bs < 3 else 20).reshape(-1, n, n)
+    for x in blocks:
+        x = np.ascontiguousarray(x)
+        y_p = np.zeros((n, n), np.int32)
+        port.oc_fdct2d(bs, ptr(y_p), n, ptr(x), n)
+        for f in fwd:
+            y_r = np.zeros((n, n), np.int32)
+            f(ptr(y_r), n, ptr(x), n)
+            assert np.array_equal(y_p, y_r)
+        x_p = np.zeros((n, n), np.int32)
+        port.oc_idct2d(bs, ptr(x_p), n, ptr(x), n)
+        for f in inv:
+            x_r = np.zeros((n, n), np.int32)
+            f(ptr(x_r), n, ptr(x), n)
+            assert np.array_equal(x_p, x_r)
+        port.oc_idct2d(bs, ptr(x_p), n, ptr(y_p), n)
+        assert np.array_equal(x_p, x)
+
+
+@pytest.mark.parametrize("f", SIZES)
+def test_lapping_filters_match_reference(reflib, f):
+    n = 4 << f
+    rng = np.random.default_rng(300 + f)
+    port = ol.port()
+    pre = getattr(reflib, "od_pre_filter%d" % n)
+    post = getattr(reflib, "od_post_filter%d" % n)
+    X = [_vectors(n, rng)]
+    if n <= 8:
+        # every sign pattern of +-676 (reference src/filter.c:2041-2116)
+        pats = np.array([[676 if (m >> k) & 1 else -676 for k in range(n)] for m in range(1 << n)])
+        X.append(pats.astype(np.int32))
+    else:
+        X.append(np.where(rng.integers(0, 2, size=(4096, n)) > 0, 676, -676).astype(np.int32))
+    for x in np.concatenate(X, 0):
+        x = np.ascontiguousarray(x)
+        a = np.zeros(n, np.int32)
+        b = np.zeros(n, np.int32)
+        port.oc_pre_filter(f, ptr(a), ptr(x))
+        pre(ptr(b), ptr(x))
+        assert np.array_equal(a, b)
+        port.oc_post_filter(f, ptr(a), ptr(x))
+        post(ptr(b), ptr(x))
+        assert np.array_equal(a, b)
+        port.oc_pre_filter(f, ptr(a), ptr(x))
+        port.oc_post_filter(f, ptr(b), ptr(a))
+        assert np.array_equal(b, x)
+
+
+@pytest.mark.parametrize("ln", [2, 3, 4, 5])
+def test_haar_matches_reference(reflib, ln):
+    n = 1 << ln
+    rng = np.random.default_rng(400 + ln)
+    port = ol.port()
+    for _ in range(20):
+        x = rng.integers(-4096, 4096, size=(n, n)).astype(np.int32)
+        a = np.zeros((n, n), np.int32)
+        b = np.zeros((n, n), np.int32)
+        port.oc_haar(ptr(a), n, ptr(x), n, ln)
+        reflib.od_haar(ptr(b), n, ptr(x), n, ln)
+        assert np.array_equal(a, b)
+        xa = np.zeros((n, n), np.int32)
+        xb = np.zeros((n, n), np.int32)
+        port.oc_haar_inv(ptr(xa), n, ptr(x), n, ln)
+        reflib.od_haar_inv(ptr(xb), n, ptr(x), n, ln)
+        assert np.array_equal(xa, xb)
+        port.oc_haar_inv(ptr(xa), n, ptr(a), n, ln)
+        assert np.array_equal(xa, x)
+
+
+@pytest.mark.parametrize("n", [4, 8, 16])
+def test_tf_matches_reference(reflib, n):
+    rng = np.random.default_rng(500 + n)
+    port = ol.port()
+    m = 2 * n
+    for _ in range(10):
+        src = rng.integers(-30000, 30000, size=(m, m)).astype(np.int32)
+        for name, args in (("tf_up_hv", (n,)), ("tf_down_hv", (m,)),
+                           ("tf_up_hv_lp", (n, n, m)), ("tf_up_h_lp", (n, m)),
+                           ("tf_up_v_lp", (n, m)), ("tf_filter_2d", (m,)),
+                           ("tf_filter_inv_2d", (m,))):
+            a = np.zeros((m, m), np.int32)
+            b = np.zeros((m, m), np.int32)
+            getattr(port, "oc_" + name)(ptr(a), m, ptr(src), m, *args)
+            getattr(reflib, "od_" + name)(ptr(b), m, ptr(src), m, *args)
+            assert np.array_equal(a, b), name
+        # up then down is the identity
+        a = np.zeros((m, m), np.int32)
+        b = np.zeros((m, m), np.int32)
+        port.oc_tf_up_hv(ptr(a), m, ptr(src), m, n)
+        port.oc_tf_down_hv(ptr(b), m, ptr(a), m, m)
+        assert np.array_equal(b, src)
+
+
+@pytest.mark.parametrize("curr,dest,filt", [(1, 0, 0), (2, 0, 1), (3, 1, 0), (3, 0, 1), (2, 2, 0)])
+def test_convert_block_down_matches_reference(reflib, curr, dest, filt):
+    rng = np.random.default_rng(600 + curr * 10 + dest)
+    port = ol.port()
+    n = 4 << curr
+    src = rng.integers(-30000, 30000, size=(n, n)).astype(np.int32)
+    a = np.zeros((n, n), np.int32)
+    b = np.zeros((n, n), np.int32)
+    port.oc_convert_block_down(ptr(a), n, ptr(src), n, curr, dest, filt)
+    reflib.od_convert_block_down(ptr(b), n, ptr(src), n, curr, dest, filt)
+    assert np.array_equal(a, b)
+
+
+PLANE_CASES = [
+    # pic_w, pic_h, dec, keyframe
+    (352, 288, 0, 1), (352, 288, 1, 1), (352, 288, 0, 0), (352, 288, 1, 0),
+    (200, 136, 0, 1), (200, 136, 1, 1), (64, 64, 0, 1), (64, 64, 1, 0),
+]
+
+
+@pytest.mark.parametrize("pic_w,pic_h,dec,key", PLANE_CASES)
+def test_plane_stages_match_reference(reflib, pic_w, pic_h, dec, key):
+    rng = np.random.default_rng(700 + pic_w + dec * 7 + key)
+    with ol.RefCtx(pic_w, pic_h) as rc:
+        H, W = rc.fh >> dec, rc.fw >> dec
+        for trial in range(3):
+            if trial == 0:
+                bsize = ol.random_quadtree_bsize(rc.nhsb, rc.nvsb, rng)
+            elif trial == 1:
+                bsize = np.full((rc.nvsb * 4, rc.nhsb * 4), rng.integers(0, 4), np.uint8)
+            else:
+                bsize = ol.random_quadtree_bsize(rc.nhsb, rc.nvsb, rng, 1.0, 1.0, 0.5)
+            c = rng.integers(-2048, 2048, size=(H, W)).astype(np.int32)
+            d_r, lap_r = rc.fwd_plane(c, bsize, dec, key, impl=0)
+            d_s, _ = rc.fwd_plane(c, bsize, dec, key, impl=1)
+            d_p, lap_p = ol.port_fwd_plane(c, bsize, dec, pic_w, pic_h, key)
+            assert np.array_equal(lap_p, lap_r)
+            assert np.array_equal(d_p, d_r)
+            assert np.array_equal(d_s, d_r)  # C == SIMD dispatch
+            # inverse on the forward output (round trip) and on raw coefficients
+            for dd in (d_r, rng.integers(-30000, 30000, size=(H, W)).astype(np.int32)):
+                c_r = rc.inv_plane(dd, bsize, dec, key, impl=0)
+                c_s = rc.inv_plane(dd, bsize, dec, key, impl=1)
+                c_p = ol.port_inv_plane(dd, bsize, dec, pic_w, pic_h, key)
+                assert np.array_equal(c_p, c_r)
+                assert np.array_equal(c_s, c_r)
+            assert np.array_equal(rc.inv_plane(d_r, bsize, dec, key), c)
+
+
+@pytest.mark.parametrize("dec", [0, 1])
+def test_haar_plane_matches_reference(reflib, dec):
+    rng = np.random.default_rng(800 + dec)
+    pic_w, pic_h = 176, 144
+    with ol.RefCtx(pic_w, pic_h) as rc:
+        H, W = rc.fh >> dec, rc.fw >> dec
+        bsize = np.full((rc.nvsb * 4, rc.nhsb * 4), 3, np.uint8)
+        c = rng.integers(-128, 128, size=(H, W)).astype(np.int32)
+        d_r, _ = rc.fwd_plane(c, bsize, dec, 1, use_haar=1)
+        d_p, _ = ol.port_fwd_plane(c, bsize, dec, pic_w, pic_h, 1, use_haar=1)
+        assert np.array_equal(d_p, d_r)
+        c_r = rc.inv_plane(d_r, bsize, dec, 0, use_haar=1)
+        c_p = ol.port_inv_plane(d_r, bsize, dec, pic_w, pic_h, 0, use_haar=1)
+        assert np.array_equal(c_p, c_r)
+        assert np.array_equal(c_r, c)
+
+
+@pytest.mark.parametrize("mode,lossless,xstride", [
+    (1, 0, 1), (1, 1, 1), (2, 1, 1), (3, 1, 1), (1, 0, 2), (2, 1, 2), (3, 1, 2), (2, 0, 2)])
+def test_pixel_conversion_matches_reference(reflib, mode, lossless, xstride):
+    rng = np.random.default_rng(900 + mode * 10 + lossless + xstride)
+    port = ol.port()
+    w, h = 48, 20
+    ystride = (w + 16) * xstride
+    if xstride == 1:
+        src = rng.integers(0, 256, size=(h, ystride)).astype(np.uint8)
+    else:
+        src = rng.integers(0, 4096, size=(h, ystride // 2)).astype(np.int16).view(np.uint8).reshape(h, ystride)
+    src = np.ascontiguousarray(src)
+    a = np.zeros((h, w), np.int32)
+    b = np.zeros((h, w), np.int32)
+    port.oc_buf_to_coeff(mode, ptr(a), w, lossless, ptr(src), xstride, ystride, w, h)
+    reflib.ref_buf_to_coeff(mode, ptr(b), w, lossless, ptr(src), xstride, ystride, w, h)
+    assert np.array_equal(a, b)
+    co = rng.integers(-5000, 5000, size=(h, w)).astype(np.int32)
+    pa = np.zeros((h, ystride), np.uint8)
+    pb = np.zeros((h, ystride), np.uint8)
+    port.oc_coeff_to_buf(mode, ptr(pa), xstride, ystride, ptr(co), w, lossless, w, h)
+    reflib.ref_coeff_to_buf(mode, ptr(pb), xstride, ystride, ptr(co), w, lossless, w, h)
+    assert np.array_equal(pa, pb)
