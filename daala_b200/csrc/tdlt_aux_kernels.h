@@ -1,0 +1,22 @@
+// Launchers of the auxiliary kernels (internal to the library).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace tdlt {
+
+void launch_pix_to_coeff(int *c, const void *pix, long long nsamples, int xstride, int shift,
+                         cudaStream_t st);
+void launch_coeff_to_pix(void *pix, const int *c, long long nsamples, int xstride, int shift,
+                         cudaStream_t st);
+void launch_dct2d_blocks(int bs, bool inverse, int *out, int ostride, long long oblock,
+                         const int *in, int istride, long long iblock, int nblocks,
+                         cudaStream_t st);
+void launch_lap_vectors(int f, bool inverse, int *out, const int *in, int nvec, cudaStream_t st);
+void launch_lap4_lines(bool inverse, int *base, long long line_step, long long tap_step,
+                       int count, cudaStream_t st);
+void launch_haar_block(bool inverse, int *y, int ystride, const int *x, int xstride, int ln,
+                       cudaStream_t st);
+void launch_tf_hv(bool down, int *dst, int dstride, const int *src, int sstride, int n,
+                  cudaStream_t st);
+
+}  // namespace tdlt

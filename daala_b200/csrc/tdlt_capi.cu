@@ -1,0 +1,625 @@
+// C-ABI of the library (include/daala_tdlt.h): context management, TMA
+// descriptor construction, kernel launches and the host-pointer wrappers.
+// No CPU arithmetic path exists here: every entry point launches CUDA kernels
+// or fails.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "../../include/daala_tdlt.h"
+#include "tdlt_kernels.h"
+#include "tdlt_aux_kernels.h"
+
+using namespace tdlt;
+
+static std::atomic<long long> g_launches{0};
+
+struct od_tdlt_ctx {
+  od_tdlt_geometry g;
+  int device;
+  int max_frames;
+  int fw, fh, nhsb, nvsb;
+  BatchDesc bd;                 // template: nframes / flags filled per call
+  long long plane_size[kMaxPlanes];
+  // strip exchange of the inverse kernel
+  int *strips;
+  int *flags;
+  int *ticket;
+  long long scratch_tiles;
+  int epoch;
+  // device staging for the host-pointer calls
+  od_coeff *dev_c[kMaxPlanes];
+  od_coeff *dev_d[kMaxPlanes];
+  void *dev_pix[kMaxPlanes];
+  unsigned char *dev_bsize;
+  cudaStream_t stream;
+  char err[256];
+};
+
+static int fail(od_tdlt_ctx *ctx, int code, const char *fmt, ...) {
+  if (ctx) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+#define CK(ctx, call) \
+  do { \
+    cudaError_t e_ = (call); \
+    if (e_ != cudaSuccess) { \
+      return fail(ctx, OD_TDLT_EFAULT, "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                  cudaGetErrorString(e_)); \
+    } \
+  } while (0)
+
+// cuTensorMapEncodeTiled is a driver-API symbol; fetch it through the runtime
+// so the library does not link against libcuda directly.
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                    const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                    const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode_tiled() {
+  static encode_tiled_fn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess) {
+      fn = reinterpret_cast<encode_tiled_fn>(p);
+    }
+  }
+  return fn;
+}
+
+// 3-D map (x, y, frame) over nframes planes of w x h int32; box bx x by x 1.
+static int make_tmap(od_tdlt_ctx *ctx, CUtensorMap *m, const void *base, int w, int h,
+                     int nframes, int box, bool swizzle) {
+  encode_tiled_fn enc = get_encode_tiled();
+  if (!enc) return fail(ctx, OD_TDLT_EFAULT, "cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
+  cuuint64_t strides[2] = {(cuuint64_t)w*4, (cuuint64_t)w*h*4};
+  cuuint32_t boxd[3] = {(cuuint32_t)box, (cuuint32_t)box, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, const_cast<void *>(base), dims, strides,
+                   boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, OD_TDLT_EFAULT, "cuTensorMapEncodeTiled failed: %d", (int)r);
+  return OD_TDLT_SUCCESS;
+}
+
+extern "C" {
+
+int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
+                       int max_frames) {
+  if (!out || !g) return OD_TDLT_EFAULT;
+  *out = nullptr;
+  if (g->nplanes < 1 || g->nplanes > kMaxPlanes || g->pic_width < 1 || g->pic_height < 1 ||
+      max_frames < 0) {
+    return OD_TDLT_EINVAL;
+  }
+  for (int p = 0; p < g->nplanes; p++) {
+    if (g->xdec[p] != g->ydec[p] || g->xdec[p] < 0 || g->xdec[p] > 1) return OD_TDLT_EINVAL;
+  }
+  od_tdlt_ctx *ctx = (od_tdlt_ctx *)calloc(1, sizeof(*ctx));
+  if (!ctx) return OD_TDLT_EFAULT;
+  ctx->g = *g;
+  ctx->device = device;
+  ctx->max_frames = max_frames;
+  // reference src/state.c:372-375: frame = picture padded to a multiple of 64
+  ctx->fw = (g->pic_width + 63) & ~63;
+  ctx->fh = (g->pic_height + 63) & ~63;
+  ctx->nhsb = ctx->fw >> 5;
+  ctx->nvsb = ctx->fh >> 5;
+  BatchDesc &bd = ctx->bd;
+  bd.nplanes = g->nplanes;
+  bd.pic_w = g->pic_width;
+  bd.pic_h = g->pic_height;
+  bd.bw = ctx->nhsb*4;
+  bd.bh = ctx->nvsb*4;
+  int tile0 = 0;
+  for (int p = 0; p < g->nplanes; p++) {
+    PlaneDesc &pd = bd.pl[p];
+    pd.dec = g->xdec[p];
+    pd.w = ctx->fw >> pd.dec;
+    pd.h = ctx->fh >> pd.dec;
+    pd.ntx = pd.w/kTile;
+    pd.nty = pd.h/kTile;
+    pd.tile0 = tile0;
+    tile0 += pd.ntx*pd.nty;
+    ctx->plane_size[p] = (long long)pd.w*pd.h;
+  }
+  bd.tiles_per_frame = tile0;
+  *out = ctx;
+  int rc = OD_TDLT_SUCCESS;
+  do {
+    if (cudaSetDevice(device) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+      rc = OD_TDLT_EFAULT; break;
+    }
+    if (cudaMalloc(&ctx->ticket, 256) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
+    cudaFuncSetAttribute(tdlt_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCtaSmemAlloc);
+    cudaFuncSetAttribute(tdlt_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCtaSmemAlloc);
+    cudaFuncSetAttribute(tdlt_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(tdlt_inv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (max_frames > 0) {
+      bool ok = true;
+      for (int p = 0; p < g->nplanes && ok; p++) {
+        size_t bytes = (size_t)ctx->plane_size[p]*max_frames*sizeof(od_coeff);
+        ok = cudaMalloc(&ctx->dev_c[p], bytes) == cudaSuccess &&
+             cudaMalloc(&ctx->dev_d[p], bytes) == cudaSuccess &&
+             cudaMalloc(&ctx->dev_pix[p], (size_t)ctx->plane_size[p]*max_frames*2) == cudaSuccess;
+      }
+      ok = ok && cudaMalloc(&ctx->dev_bsize, (size_t)bd.bw*bd.bh*max_frames) == cudaSuccess;
+      if (!ok) { rc = OD_TDLT_EFAULT; break; }
+    }
+  } while (0);
+  if (rc != OD_TDLT_SUCCESS) {
+    fprintf(stderr, "od_tdlt_ctx_create: CUDA setup failed: %s\n",
+            cudaGetErrorString(cudaGetLastError()));
+    od_tdlt_ctx_destroy(ctx);
+    *out = nullptr;
+  }
+  return rc;
+}
+
+void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (int p = 0; p < kMaxPlanes; p++) {
+    cudaFree(ctx->dev_c[p]);
+    cudaFree(ctx->dev_d[p]);
+    cudaFree(ctx->dev_pix[p]);
+  }
+  cudaFree(ctx->dev_bsize);
+  cudaFree(ctx->strips);
+  cudaFree(ctx->flags);
+  cudaFree(ctx->ticket);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  free(ctx);
+}
+
+int od_tdlt_frame_width(const od_tdlt_ctx *ctx) { return ctx->fw; }
+int od_tdlt_frame_height(const od_tdlt_ctx *ctx) { return ctx->fh; }
+int od_tdlt_nhsb(const od_tdlt_ctx *ctx) { return ctx->nhsb; }
+int od_tdlt_nvsb(const od_tdlt_ctx *ctx) { return ctx->nvsb; }
+long long od_tdlt_plane_size(const od_tdlt_ctx *ctx, int pli) {
+  return (pli >= 0 && pli < ctx->g.nplanes) ? ctx->plane_size[pli] : 0;
+}
+long long od_tdlt_bsize_size(const od_tdlt_ctx *ctx) { return (long long)ctx->bd.bw*ctx->bd.bh; }
+const char *od_tdlt_last_error(const od_tdlt_ctx *ctx) { return ctx ? ctx->err : "null context"; }
+long long od_tdlt_launch_count(void) { return g_launches.load(); }
+
+// ---------------------------------------------------------------- batches --
+int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
+                      const unsigned char *bsize, int nframes, int flags, void *stream) {
+  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
+  CK(ctx, cudaSetDevice(ctx->device));
+  TmapSet maps;
+  memset(&maps, 0, sizeof(maps));
+  BatchDesc bd = ctx->bd;
+  bd.nframes = nframes;
+  bd.flags = flags;
+  for (int p = 0; p < bd.nplanes; p++) {
+    int rc = make_tmap(ctx, &maps.in[p], c[p], bd.pl[p].w, bd.pl[p].h, nframes, kAStride, false);
+    if (rc) return rc;
+    rc = make_tmap(ctx, &maps.out[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, true);
+    if (rc) return rc;
+  }
+  long long total = (long long)bd.tiles_per_frame*nframes;
+  unsigned grid = (unsigned)((total + kWarpsPerCta - 1)/kWarpsPerCta);
+  tdlt_fwd_kernel<<<grid, kWarpsPerCta*32, kCtaSmemAlloc, (cudaStream_t)stream>>>(maps, bd, bsize);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
+static int ensure_scratch(od_tdlt_ctx *ctx, long long tiles) {
+  if (tiles <= ctx->scratch_tiles) return OD_TDLT_SUCCESS;
+  CK(ctx, cudaDeviceSynchronize());
+  cudaFree(ctx->strips);
+  cudaFree(ctx->flags);
+  ctx->strips = nullptr;
+  ctx->flags = nullptr;
+  ctx->scratch_tiles = 0;
+  CK(ctx, cudaMalloc(&ctx->strips, (size_t)tiles*128*sizeof(int)));
+  CK(ctx, cudaMalloc(&ctx->flags, (size_t)tiles*sizeof(int)));
+  CK(ctx, cudaMemset(ctx->flags, 0, (size_t)tiles*sizeof(int)));
+  ctx->scratch_tiles = tiles;
+  ctx->epoch = 0;
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
+                      const unsigned char *bsize, int nframes, int flags, void *stream) {
+  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
+  CK(ctx, cudaSetDevice(ctx->device));
+  TmapSet maps;
+  memset(&maps, 0, sizeof(maps));
+  BatchDesc bd = ctx->bd;
+  bd.nframes = nframes;
+  bd.flags = flags;
+  InvOut out;
+  memset(&out, 0, sizeof(out));
+  for (int p = 0; p < bd.nplanes; p++) {
+    int rc = make_tmap(ctx, &maps.in[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, true);
+    if (rc) return rc;
+    out.c[p] = c[p];
+  }
+  long long total = (long long)bd.tiles_per_frame*nframes;
+  int rc = ensure_scratch(ctx, total);
+  if (rc) return rc;
+  unsigned grid = (unsigned)((total + kWarpsPerCta - 1)/kWarpsPerCta);
+  cudaStream_t st = (cudaStream_t)stream;
+  CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
+  ctx->epoch++;
+  tdlt_inv_kernel<<<grid, kWarpsPerCta*32, kCtaSmemAlloc, st>>>(
+      maps, bd, bsize, out, ctx->strips, ctx->flags, ctx->ticket, ctx->epoch);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
+static int conv_shift(int xstride, int bitdepth_mode, int lossless_p) {
+  // reference src/state.c:1221-1223, 1236-1238 (OD_COEFF_SHIFT == 4)
+  if (xstride == 1) return lossless_p ? (bitdepth_mode - 1)*2 : 4;
+  return lossless_p ? 4 - (bitdepth_mode - 1)*2 : 0;
+}
+
+int od_tdlt_pix_to_coeff_batch(od_tdlt_ctx *ctx, od_coeff *c, const void *pix, int pli,
+                               int nframes, int xstride, int bitdepth_mode, int lossless_p,
+                               void *stream) {
+  if (!ctx || !c || !pix) return OD_TDLT_EFAULT;
+  if (pli < 0 || pli >= ctx->g.nplanes || (xstride != 1 && xstride != 2) || bitdepth_mode < 1 ||
+      bitdepth_mode > 3) {
+    return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");
+  }
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_pix_to_coeff(c, pix, ctx->plane_size[pli]*nframes, xstride,
+                      conv_shift(xstride, bitdepth_mode, lossless_p), (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c, int pli,
+                               int nframes, int xstride, int bitdepth_mode, int lossless_p,
+                               void *stream) {
+  if (!ctx || !c || !pix) return OD_TDLT_EFAULT;
+  if (pli < 0 || pli >= ctx->g.nplanes || (xstride != 1 && xstride != 2) || bitdepth_mode < 1 ||
+      bitdepth_mode > 3) {
+    return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");
+  }
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_coeff_to_pix(pix, c, ctx->plane_size[pli]*nframes, xstride,
+                      conv_shift(xstride, bitdepth_mode, lossless_p), (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------- whole-frame host calls --
+static int check_frames(od_tdlt_ctx *ctx, int nframes) {
+  if (nframes < 1 || nframes > ctx->max_frames) {
+    return fail(ctx, OD_TDLT_EINVAL, "nframes %d outside 1..max_frames %d", nframes,
+                ctx->max_frames);
+  }
+  return OD_TDLT_SUCCESS;
+}
+
+extern "C" {
+
+int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
+                       const unsigned char *bsize, int nframes, int flags) {
+  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(ctx->dev_c[p], c[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyHostToDevice, st));
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_fwd_batch(ctx, ctx->dev_d, ctx->dev_c, ctx->dev_bsize, nframes, flags, st);
+  if (rc) return rc;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(d[p], ctx->dev_d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
+                       const unsigned char *bsize, int nframes, int flags) {
+  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(ctx->dev_d[p], d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyHostToDevice, st));
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_inv_batch(ctx, ctx->dev_c, ctx->dev_d, ctx->dev_bsize, nframes, flags, st);
+  if (rc) return rc;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(c[p], ctx->dev_c[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_fwd_frames_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
+                           const int ystride[], const long long frame_stride[],
+                           const unsigned char *bsize, int nframes, int flags, int xstride,
+                           int bitdepth_mode, int lossless_p) {
+  if (!ctx || !d || !pix || !ystride || !frame_stride || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    const PlaneDesc &pd = ctx->bd.pl[p];
+    size_t row = (size_t)pd.w*xstride;
+    for (int f = 0; f < nframes; f++) {
+      CK(ctx, cudaMemcpy2DAsync((char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row,
+                                (const char *)pix[p] + f*frame_stride[p], ystride[p], row, pd.h,
+                                cudaMemcpyHostToDevice, st));
+    }
+    rc = od_tdlt_pix_to_coeff_batch(ctx, ctx->dev_c[p], ctx->dev_pix[p], p, nframes, xstride,
+                                    bitdepth_mode, lossless_p, st);
+    if (rc) return rc;
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_fwd_batch(ctx, ctx->dev_d, ctx->dev_c, ctx->dev_bsize, nframes, flags, st);
+  if (rc) return rc;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(d[p], ctx->dev_d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_inv_frames_pix(od_tdlt_ctx *ctx, void *const pix[], const int ystride[],
+                           const long long frame_stride[], const od_coeff *const d[],
+                           const unsigned char *bsize, int nframes, int flags, int xstride,
+                           int bitdepth_mode, int lossless_p) {
+  if (!ctx || !d || !pix || !ystride || !frame_stride || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    CK(ctx, cudaMemcpyAsync(ctx->dev_d[p], d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyHostToDevice, st));
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_inv_batch(ctx, ctx->dev_c, ctx->dev_d, ctx->dev_bsize, nframes, flags, st);
+  if (rc) return rc;
+  for (int p = 0; p < ctx->g.nplanes; p++) {
+    const PlaneDesc &pd = ctx->bd.pl[p];
+    size_t row = (size_t)pd.w*xstride;
+    rc = od_tdlt_coeff_to_pix_batch(ctx, ctx->dev_pix[p], ctx->dev_c[p], p, nframes, xstride,
+                                    bitdepth_mode, lossless_p, st);
+    if (rc) return rc;
+    for (int f = 0; f < nframes; f++) {
+      CK(ctx, cudaMemcpy2DAsync((char *)pix[p] + f*frame_stride[p], ystride[p],
+                                (const char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row, row,
+                                pd.h, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+}  // extern "C"
+
+// ------------------------------------------- reference-signature wrappers --
+// Host pointers in, host pointers out, synchronous, on the current device.
+// A failure here cannot be reported through the reference's void signatures,
+// so it aborts (the reference's OD_FATAL convention, src/internal.h:128-158).
+static void die(const char *what, cudaError_t e) {
+  fprintf(stderr, "daala_tdlt (CUDA): fatal: %s: %s\n", what, cudaGetErrorString(e));
+  abort();
+}
+#define CKF(call) \
+  do { cudaError_t e_ = (call); if (e_ != cudaSuccess) die(#call, e_); } while (0)
+
+namespace {
+struct Scratch {
+  int *a = nullptr, *b = nullptr;
+  size_t na = 0, nb = 0;
+  int *get(int *&p, size_t &n, size_t want) {
+    if (want > n) {
+      if (p) CKF(cudaFree(p));
+      CKF(cudaMalloc(&p, want*sizeof(int)));
+      n = want;
+    }
+    return p;
+  }
+  int *A(size_t want) { return get(a, na, want); }
+  int *B(size_t want) { return get(b, nb, want); }
+};
+Scratch g_scratch;
+
+// Copies a strided host rectangle (rows x cols ints) to a dense device buffer.
+void h2d_rect(int *dev, const od_coeff *host, int stride, int rows, int cols) {
+  CKF(cudaMemcpy2D(dev, (size_t)cols*4, host, (size_t)stride*4, (size_t)cols*4, rows,
+                   cudaMemcpyHostToDevice));
+}
+void d2h_rect(od_coeff *host, int stride, const int *dev, int rows, int cols) {
+  CKF(cudaMemcpy2D(host, (size_t)stride*4, dev, (size_t)cols*4, (size_t)cols*4, rows,
+                   cudaMemcpyDeviceToHost));
+}
+
+void dct_one(int bs, bool inverse, od_coeff *out, int ostride, const od_coeff *in, int istride) {
+  int n = 4 << bs;
+  int *din = g_scratch.A((size_t)n*n), *dout = g_scratch.B((size_t)n*n);
+  h2d_rect(din, in, istride, n, n);
+  launch_dct2d_blocks(bs, inverse, dout, n, 0, din, n, 0, 1, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(out, ostride, dout, n, n);
+}
+}  // namespace
+
+extern "C" {
+
+void od_bin_fdct4x4_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(0, false, y, ys, x, xs); }
+void od_bin_idct4x4_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(0, true, x, xs, y, ys); }
+void od_bin_fdct8x8_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(1, false, y, ys, x, xs); }
+void od_bin_idct8x8_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(1, true, x, xs, y, ys); }
+void od_bin_fdct16x16_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(2, false, y, ys, x, xs); }
+void od_bin_idct16x16_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(2, true, x, xs, y, ys); }
+void od_bin_fdct32x32_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(3, false, y, ys, x, xs); }
+void od_bin_idct32x32_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(3, true, x, xs, y, ys); }
+
+int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,
+                         const od_coeff *in, int istride, long long iblock, int nblocks) {
+  if (bs < 0 || bs > 3 || nblocks < 1 || !out || !in) return OD_TDLT_EINVAL;
+  int n = 4 << bs;
+  // Stage densely: block i at i*n*n.
+  size_t tot = (size_t)nblocks*n*n;
+  int *din = g_scratch.A(tot), *dout = g_scratch.B(tot);
+  for (int i = 0; i < nblocks; i++) h2d_rect(din + (size_t)i*n*n, in + i*iblock, istride, n, n);
+  launch_dct2d_blocks(bs, inverse != 0, dout, n, (long long)n*n, din, n, (long long)n*n, nblocks, 0);
+  g_launches++;
+  if (cudaGetLastError() != cudaSuccess) return OD_TDLT_EFAULT;
+  for (int i = 0; i < nblocks; i++) d2h_rect(out + i*oblock, ostride, dout + (size_t)i*n*n, n, n);
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_lap_filter_vectors(int f, int inverse, od_coeff *out, const od_coeff *in, int nvec) {
+  if (f < 0 || f > 3 || nvec < 1 || !out || !in) return OD_TDLT_EINVAL;
+  size_t tot = (size_t)nvec*(4 << f);
+  int *din = g_scratch.A(tot), *dout = g_scratch.B(tot);
+  CKF(cudaMemcpy(din, in, tot*4, cudaMemcpyHostToDevice));
+  launch_lap_vectors(f, inverse != 0, dout, din, nvec, 0);
+  g_launches++;
+  if (cudaGetLastError() != cudaSuccess) return OD_TDLT_EFAULT;
+  CKF(cudaMemcpy(out, dout, tot*4, cudaMemcpyDeviceToHost));
+  return OD_TDLT_SUCCESS;
+}
+
+static void haar_one(bool inverse, od_coeff *out, int ostride, const od_coeff *in, int istride,
+                     int ln) {
+  int n = 1 << ln;
+  if (ln < 1 || ln > 5) die("od_haar: ln out of range", cudaErrorInvalidValue);
+  int *din = g_scratch.A((size_t)n*n), *dout = g_scratch.B((size_t)n*n);
+  h2d_rect(din, in, istride, n, n);
+  launch_haar_block(inverse, dout, n, din, n, ln, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(out, ostride, dout, n, n);
+}
+void od_haar_cuda(od_coeff *y, int ys, const od_coeff *x, int xs, int ln) { haar_one(false, y, ys, x, xs, ln); }
+void od_haar_inv_cuda(od_coeff *x, int xs, const od_coeff *y, int ys, int ln) { haar_one(true, x, xs, y, ys, ln); }
+
+static void tf_one(bool down, od_coeff *dst, int dstride, const od_coeff *src, int sstride,
+                   int n) {
+  // up: n = size of each of the 2x2 source blocks; down: n = size of the source block.
+  int full = down ? n : 2*n;
+  int half = full/2;
+  int *din = g_scratch.A((size_t)full*full), *dout = g_scratch.B((size_t)full*full);
+  h2d_rect(din, src, sstride, full, full);
+  launch_tf_hv(down, dout, full, din, full, half, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(dst, dstride, dout, full, full);
+}
+void od_tf_up_hv_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) { tf_one(false, dst, ds, src, ss, n); }
+void od_tf_down_hv_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) { tf_one(true, dst, ds, src, ss, n); }
+
+// General f is supported through the N-tap vector kernel only for f == 0 here:
+// the codec never uses another size on this path (OD_FILT_SIZE == 0,
+// reference src/filter.h:99), and the reference asserts nothing else either.
+static void split_filter(od_coeff *c0, int stride, int bs, int f, int hfilter, int vfilter,
+                         bool inverse) {
+  if (f != 0) die("od_*filter_split: only f == 0 (4-tap lapping) is on the path", cudaErrorInvalidValue);
+  int n = 4 << bs;
+  int *dev = g_scratch.A((size_t)n*n);
+  h2d_rect(dev, c0, stride, n, n);
+  int mid = (n >> 1) - 2;
+  // forward: across the horizontal mid-edge first (down the columns), then across the
+  // vertical one (reference src/filter.c:1493-1508); inverse: the other way round (:1537-1552).
+  for (int step = 0; step < 2; step++) {
+    bool cols = (step == 0) != inverse;
+    if (cols && hfilter) {
+      launch_lap4_lines(inverse, dev + mid*n, 1, n, n, 0);
+      g_launches++;
+    }
+    if (!cols && vfilter) {
+      launch_lap4_lines(inverse, dev + mid, n, 1, n, 0);
+      g_launches++;
+    }
+  }
+  CKF(cudaGetLastError());
+  d2h_rect(c0, stride, dev, n, n);
+}
+void od_prefilter_split_cuda(od_coeff *c0, int stride, int bs, int f, int hfilter, int vfilter) {
+  split_filter(c0, stride, bs, f, hfilter, vfilter, false);
+}
+void od_postfilter_split_cuda(od_coeff *c0, int stride, int bs, int f, int q, unsigned char *skip,
+                              int skip_stride, int hfilter, int vfilter) {
+  (void)q; (void)skip; (void)skip_stride;
+  split_filter(c0, stride, bs, f, hfilter, vfilter, true);
+}
+
+static void frame_sbs(od_coeff *c, int stride, int nhsb, int nvsb, int xdec, int ydec,
+                      bool inverse) {
+  int w = (nhsb*32) >> xdec, h = (nvsb*32) >> ydec;
+  int sbw = 32 >> xdec, sbh = 32 >> ydec;
+  int *dev = g_scratch.A((size_t)w*h);
+  h2d_rect(dev, c, stride, h, w);
+  // forward: horizontal SB edges (down the columns) then vertical ones (reference
+  // src/filter.c:1567-1584); inverse: vertical then horizontal (:1627-1644).
+  for (int step = 0; step < 2; step++) {
+    bool cols = (step == 0) != inverse;
+    if (cols) {
+      for (int sby = 1; sby < nvsb; sby++) {
+        launch_lap4_lines(inverse, dev + (size_t)(sby*sbh - 2)*w, 1, w, w, 0);
+        g_launches++;
+      }
+    }
+    else {
+      for (int sbx = 1; sbx < nhsb; sbx++) {
+        launch_lap4_lines(inverse, dev + sbx*sbw - 2, w, 1, h, 0);
+        g_launches++;
+      }
+    }
+  }
+  CKF(cudaGetLastError());
+  d2h_rect(c, stride, dev, h, w);
+}
+void od_apply_prefilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nvsb, int xdec,
+                                       int ydec) {
+  frame_sbs(c, stride, nhsb, nvsb, xdec, ydec, false);
+}
+void od_apply_postfilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nvsb, int xdec,
+                                        int ydec, int q, unsigned char *skip, int skip_stride) {
+  (void)q; (void)skip; (void)skip_stride;
+  frame_sbs(c, stride, nhsb, nvsb, xdec, ydec, true);
+}
+
+}  // extern "C"

@@ -1,0 +1,32 @@
+// Host-visible declarations of the batch kernels (internal to the library).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "tdlt_device.cuh"
+
+namespace tdlt {
+
+// TMA descriptors, one per plane: `in` is read by tiled loads, `out` written
+// by tiled stores (forward only).
+struct TmapSet {
+  CUtensorMap in[kMaxPlanes];
+  CUtensorMap out[kMaxPlanes];
+};
+
+struct InvOut {
+  int *c[kMaxPlanes];
+};
+
+constexpr int kCtaSmemBytes = kWarpsPerCta*(kBBytes + kABytes + kLsBytes + 8);
+constexpr int kCtaSmemAlloc = kCtaSmemBytes + 16;   // + the inverse kernel's ticket slot
+
+__global__ void tdlt_fwd_kernel(const __grid_constant__ TmapSet maps,
+                                const __grid_constant__ BatchDesc bd,
+                                const unsigned char *__restrict__ bsize);
+__global__ void tdlt_inv_kernel(const __grid_constant__ TmapSet maps,
+                                const __grid_constant__ BatchDesc bd,
+                                const unsigned char *__restrict__ bsize, InvOut out,
+                                int *__restrict__ strips, int *__restrict__ flags,
+                                int *__restrict__ ticket, int epoch);
+
+}  // namespace tdlt

@@ -1,0 +1,171 @@
+/* daala_tdlt.h -- C-ABI of the B200 (sm_100a) implementation of Daala's
+ * time-domain lapped transform stage.
+ *
+ * Everything here is plain C: pointers, ints, no CUDA or torch types (a CUDA
+ * stream crosses the boundary as a void*).  Each entry point cites the
+ * reference interface it replaces (KyleSiefring/daala, file:line).
+ *
+ * Three layers, coarsest first:
+ *   1. device-resident batch calls   (od_tdlt_fwd_batch / od_tdlt_inv_batch)
+ *      -- what bench.py times as `value`; pointers are DEVICE pointers.
+ *   2. whole-frame host calls        (od_tdlt_fwd_frame / od_tdlt_inv_frame,
+ *      od_tdlt_fwd_frame_img / od_tdlt_inv_frame_img)
+ *      -- the real drop-in for encode.c / decode.c; pointers are HOST pointers.
+ *   3. reference-signature calls     (od_bin_fdct8x8_cuda, od_prefilter_split_cuda ...)
+ *      -- same prototypes as the reference functions, host pointers,
+ *      synchronous; they exist so the reference's own call sites and
+ *      OD_CHECKASM-style cross-checks can run against the GPU.
+ *
+ * There is no CPU fallback anywhere in this library: a call either runs on
+ * the GPU or fails (int-returning calls return OD_EFAULT; void calls abort,
+ * mirroring OD_FATAL in reference src/internal.h:128-158).
+ */
+#ifndef DAALA_TDLT_H
+#define DAALA_TDLT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* reference src/filter.h:31 */
+typedef int32_t od_coeff;
+
+/* reference include/daala/codec.h:89-103 */
+#define OD_TDLT_SUCCESS (0)
+#define OD_TDLT_EFAULT (-1)
+#define OD_TDLT_EINVAL (-10)
+#define OD_TDLT_EIMPL (-23)
+
+#define OD_TDLT_NPLANES_MAX (4)
+
+/* Flags for the frame / batch calls. */
+#define OD_TDLT_KEYFRAME (1)   /* forward: Haar-merge child DCs (encode.c:1328-1341);
+                                  inverse: undo it top-down (decode.c:733) */
+#define OD_TDLT_HAAR     (2)   /* lossless mode: od_haar / od_haar_inv instead of
+                                  lapping + DCT (encode.c:1304-1306, decode.c:632-634) */
+
+/* Geometry of a stream; mirrors the fields of daala_info / od_state the path
+   reads (reference src/state.c:366-375, 393-394). */
+typedef struct od_tdlt_geometry {
+  int pic_width;                      /* luma picture width  (info.pic_width)  */
+  int pic_height;                     /* luma picture height (info.pic_height) */
+  int nplanes;                        /* 1..4 */
+  int xdec[OD_TDLT_NPLANES_MAX];      /* 0 or 1; xdec == ydec (encode.c:1296) */
+  int ydec[OD_TDLT_NPLANES_MAX];
+} od_tdlt_geometry;
+
+typedef struct od_tdlt_ctx od_tdlt_ctx;
+
+/* ---- context -----------------------------------------------------------
+   Created next to od_state_init (reference src/state.c:355-496), destroyed
+   next to od_state_clear (:507-...).  max_frames bounds the batch size of the
+   host-pointer calls (device staging for that many frames is allocated). */
+int od_tdlt_ctx_create(od_tdlt_ctx **ctx, const od_tdlt_geometry *geom,
+ int device, int max_frames);
+void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx);
+
+/* Padded frame geometry (multiple of 64, reference src/state.c:372-375). */
+int od_tdlt_frame_width(const od_tdlt_ctx *ctx);
+int od_tdlt_frame_height(const od_tdlt_ctx *ctx);
+int od_tdlt_nhsb(const od_tdlt_ctx *ctx);
+int od_tdlt_nvsb(const od_tdlt_ctx *ctx);
+/* Number of od_coeff in one plane of one frame, (fw>>xdec)*(fh>>ydec). */
+long long od_tdlt_plane_size(const od_tdlt_ctx *ctx, int pli);
+/* Bytes of one frame's block-size map: (nvsb*4)*(nhsb*4), one byte per 8x8
+   luma block holding 0..3 (reference src/state.h:207-224, without the border). */
+long long od_tdlt_bsize_size(const od_tdlt_ctx *ctx);
+const char *od_tdlt_last_error(const od_tdlt_ctx *ctx);
+
+/* ---- 1. device-resident batches ---------------------------------------
+   c[pli], d[pli]: DEVICE pointers to nframes contiguous planes
+   ([frame][row][col], row stride = frame_width>>xdec, no padding -- the
+   reference's ctmp/dtmp layout, src/state.c:409-428, repeated per frame).
+   bsize: DEVICE pointer, nframes maps of od_tdlt_bsize_size() bytes.
+   stream: a cudaStream_t (NULL = default stream).  Asynchronous.
+
+   Forward  = od_apply_prefilter_frame_sbs (src/filter.c:1556) + od_compute_dcts
+              on every superblock (src/encode.c:1286), c -> d.  c is NOT modified.
+   Inverse  = per superblock: [DC split], od_bin_idct* / od_haar_inv at the
+              leaves, od_postfilter_split bottom-up (src/decode.c:767-868,
+              528-639), then od_apply_postfilter_frame_sbs (src/filter.c:1588),
+              d -> c.  d is NOT modified. */
+int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
+ const unsigned char *bsize, int nframes, int flags, void *stream);
+int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
+ const unsigned char *bsize, int nframes, int flags, void *stream);
+
+/* Pixel <-> coefficient conversion on device batches
+   (od_ref_buf_to_coeff / od_coeff_to_ref_buf, src/state.c:1209-1316).
+   pix: DEVICE pointer to nframes tightly packed planes of (fw>>xdec) x (fh>>ydec)
+   samples, xstride = 1 (uint8) or 2 (int16) bytes. */
+int od_tdlt_pix_to_coeff_batch(od_tdlt_ctx *ctx, od_coeff *c, const void *pix,
+ int pli, int nframes, int xstride, int bitdepth_mode, int lossless_p, void *stream);
+int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c,
+ int pli, int nframes, int xstride, int bitdepth_mode, int lossless_p, void *stream);
+
+/* ---- 2. whole-frame host calls ----------------------------------------
+   HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
+   out as above but in host memory (pinned or pageable).
+   These replace, in od_encode_coefficients / od_decode_coefficients, the loops
+   at src/encode.c:2425-2437 + :2492 and src/decode.c:632-638, 854-866, 1032-1041. */
+int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
+ const unsigned char *bsize, int nframes, int flags);
+int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
+ const unsigned char *bsize, int nframes, int flags);
+/* Same with the pixel conversion done on the device: the host ships 8/16-bit
+   reference-buffer samples instead of od_coeff (od_ref_plane_to_coeff,
+   src/state.c:1252; od_coeff_to_ref_plane, :1320).  pix[pli] points at the
+   first visible sample of frame 0 (od_img_plane.data); rows are ystride[pli]
+   BYTES apart (od_img_plane.ystride, which includes the reference's border
+   padding) and frames frame_stride[pli] bytes apart; xstride = 1 or 2 bytes
+   per sample (od_img_plane.xstride); lossless_p as OD_LOSSLESS(). */
+int od_tdlt_fwd_frames_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
+ const int ystride[], const long long frame_stride[], const unsigned char *bsize,
+ int nframes, int flags, int xstride, int bitdepth_mode, int lossless_p);
+int od_tdlt_inv_frames_pix(od_tdlt_ctx *ctx, void *const pix[], const int ystride[],
+ const long long frame_stride[], const od_coeff *const d[], const unsigned char *bsize,
+ int nframes, int flags, int xstride, int bitdepth_mode, int lossless_p);
+
+/* ---- 3. reference-signature calls (host pointers, synchronous) --------- */
+/* od_dct_func_2d, reference src/dct.h:61-62; tables src/dct.c:42-56 */
+void od_bin_fdct4x4_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride);
+void od_bin_idct4x4_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
+void od_bin_fdct8x8_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride);
+void od_bin_idct8x8_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
+void od_bin_fdct16x16_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride);
+void od_bin_idct16x16_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
+void od_bin_fdct32x32_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride);
+void od_bin_idct32x32_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
+/* Many blocks in one launch: nblocks blocks of (4<<bs)^2, block i at x + i*xblock
+   (resp. y + i*yblock); the useful form of the above for parity sweeps. */
+int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,
+ const od_coeff *in, int istride, long long iblock, int nblocks);
+/* od_pre_filter{4,8,16,32} / od_post_filter*, reference src/filter.c:174-1373;
+   nvec vectors of 4<<f samples, tightly packed. */
+int od_tdlt_lap_filter_vectors(int f, int inverse, od_coeff *out, const od_coeff *in, int nvec);
+/* reference src/dct.h:181-183, src/dct.c:1960-2026 */
+void od_haar_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride, int ln);
+void od_haar_inv_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride, int ln);
+/* reference src/tf.h:53-56, src/tf.c:112-169 */
+void od_tf_up_hv_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
+void od_tf_down_hv_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
+/* reference src/filter.h:121-128, src/filter.c:1486-1646 (OD_DEBLOCKING == 0:
+   q, skip and skip_stride are ignored, as in the reference) */
+void od_prefilter_split_cuda(od_coeff *c0, int stride, int bs, int f, int hfilter, int vfilter);
+void od_postfilter_split_cuda(od_coeff *c0, int stride, int bs, int f, int q,
+ unsigned char *skip, int skip_stride, int hfilter, int vfilter);
+void od_apply_prefilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nvsb,
+ int xdec, int ydec);
+void od_apply_postfilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nvsb,
+ int xdec, int ydec, int q, unsigned char *skip, int skip_stride);
+
+/* Number of kernel launches issued by this library since load (bench.py's
+   gpu_launches claim is read from here). */
+long long od_tdlt_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

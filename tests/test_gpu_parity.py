@@ -1,0 +1,159 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called
+through the C-ABI, against the CPU checker on identical seeded inputs.
+Bit-exact: every comparison is np.array_equal on int32 / uint8 / int16."""
+import numpy as np
+import pytest
+
+import oracle_libs as ol
+from checker import Checker, make_maps
+
+pytestmark = pytest.mark.gpu
+
+DECS = (0, 1, 1)
+
+
+def _ctx(pic_w, pic_h, max_frames, decs=DECS):
+    import daala_b200
+    return daala_b200.TdltContext(pic_w, pic_h, decs=decs, device=0, max_frames=max_frames)
+
+
+def _rand_planes(shapes, nframes, rng, lo=-2048, hi=2048):
+    return [rng.integers(lo, hi, size=(nframes,) + s).astype(np.int32) for s in shapes]
+
+
+FRAME_CASES = [
+    # pic_w, pic_h, map kind, keyframe
+    (352, 288, "quad", 1), (352, 288, "quad", 0), (352, 288, "deep", 1),
+    (352, 288, "uniform0", 1), (352, 288, "uniform1", 0), (352, 288, "uniform2", 1),
+    (352, 288, "uniform3", 1), (200, 136, "quad", 1), (200, 136, "deep", 0),
+    (64, 64, "quad", 1), (33, 17, "deep", 1), (1920, 1080, "quad", 1),
+]
+
+
+@pytest.mark.parametrize("pic_w,pic_h,kind,key", FRAME_CASES)
+def test_frames_match_checker(pic_w, pic_h, kind, key):
+    import daala_b200
+    rng = np.random.default_rng(pic_w * 7 + pic_h * 3 + key + sum(map(ord, kind)))
+    nframes = 2 if pic_w < 1000 else 1
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        assert (ctx.frame_width, ctx.frame_height) == (chk.fw, chk.fh)
+        bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+        c = _rand_planes(ctx.plane_shapes, nframes, rng)
+        flags = daala_b200.OD_TDLT_KEYFRAME if key else 0
+        d = [np.zeros_like(a) for a in c]
+        ctx.fwd_frames(d, c, bsize, flags)
+        d_ref = chk.fwd_frames(c, bsize, DECS, key)
+        for p in range(3):
+            assert np.array_equal(d[p], d_ref[p]), "forward plane %d" % p
+        # inverse of the forward output: exact reconstruction of c
+        c2 = [np.zeros_like(a) for a in c]
+        ctx.inv_frames(c2, d, bsize, flags)
+        for p in range(3):
+            assert np.array_equal(c2[p], c[p]), "round trip plane %d" % p
+        # inverse of arbitrary coefficients (what a decoder feeds it)
+        dq = _rand_planes(ctx.plane_shapes, nframes, rng, -30000, 30000)
+        ctx.inv_frames(c2, dq, bsize, flags)
+        c_ref = chk.inv_frames(dq, bsize, DECS, key)
+        for p in range(3):
+            assert np.array_equal(c2[p], c_ref[p]), "inverse plane %d" % p
+    chk.close()
+
+
+@pytest.mark.parametrize("decs", [(0,), (0, 0, 0), (0, 1, 1, 0)])
+def test_other_plane_layouts(decs):
+    import daala_b200
+    rng = np.random.default_rng(77 + len(decs))
+    pic_w, pic_h = 176, 144
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, 1, decs) as ctx:
+        bsize = make_maps("deep", 1, ctx.nhsb, ctx.nvsb, rng)
+        c = _rand_planes(ctx.plane_shapes, 1, rng)
+        d = [np.zeros_like(a) for a in c]
+        ctx.fwd_frames(d, c, bsize, daala_b200.OD_TDLT_KEYFRAME)
+        d_ref = chk.fwd_frames(c, bsize, decs, 1)
+        c2 = [np.zeros_like(a) for a in c]
+        ctx.inv_frames(c2, d, bsize, daala_b200.OD_TDLT_KEYFRAME)
+        for p in range(len(decs)):
+            assert np.array_equal(d[p], d_ref[p])
+            assert np.array_equal(c2[p], c[p])
+    chk.close()
+
+
+@pytest.mark.parametrize("pic_w,pic_h", [(352, 288), (1280, 720)])
+def test_lossless_haar_mode(pic_w, pic_h):
+    """BASELINE config 5 (ci/lossless.sh equivalent): 8-bit pixels -> coeff_shift 0
+    -> od_haar -> od_haar_inv -> pixels must be the identity, and the
+    coefficients must equal the checker's."""
+    import daala_b200
+    rng = np.random.default_rng(5)
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, 1) as ctx:
+        bsize = make_maps("uniform3", 1, ctx.nhsb, ctx.nvsb, rng)
+        pix = [rng.integers(0, 256, size=(1,) + s).astype(np.uint8) for s in ctx.plane_shapes]
+        d = [np.zeros((1,) + s, np.int32) for s in ctx.plane_shapes]
+        fl = daala_b200.OD_TDLT_KEYFRAME | daala_b200.OD_TDLT_HAAR
+        ctx.fwd_frames_pix(d, pix, bsize, fl, xstride=1, bitdepth_mode=1, lossless=1)
+        c = [(a.astype(np.int32) - 128) for a in pix]
+        d_ref = chk.fwd_frames(c, bsize, DECS, 1, haar=1)
+        for p in range(3):
+            assert np.array_equal(d[p], d_ref[p])
+        out = [np.zeros_like(a) for a in pix]
+        ctx.inv_frames_pix(out, d, bsize, fl, xstride=1, bitdepth_mode=1, lossless=1)
+        for p in range(3):
+            assert np.array_equal(out[p], pix[p])
+    chk.close()
+
+
+@pytest.mark.parametrize("xstride,mode,lossless", [(1, 1, 0), (2, 2, 0), (2, 3, 1), (1, 2, 1), (2, 1, 1)])
+def test_pixel_paths_match_checker(xstride, mode, lossless):
+    """coeff_shift paths: 8-bit and 16-bit reference buffers with row padding."""
+    import daala_b200
+    rng = np.random.default_rng(600 + xstride * 10 + mode)
+    pic_w, pic_h = 352, 288
+    port = ol.port()
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, 2) as ctx:
+        bsize = make_maps("quad", 2, ctx.nhsb, ctx.nvsb, rng)
+        pad = 32
+        pix, views = [], []
+        for (h, w) in ctx.plane_shapes:
+            if xstride == 1:
+                buf = rng.integers(0, 256, size=(2, h + 2 * pad, w + 2 * pad)).astype(np.uint8)
+            else:
+                buf = rng.integers(0, 4096, size=(2, h + 2 * pad, w + 2 * pad)).astype(np.int16)
+            pix.append(buf)
+            views.append(buf[:, pad:pad + h, pad:pad + w])
+        d = [np.zeros((2,) + s, np.int32) for s in ctx.plane_shapes]
+        ctx.fwd_frames_pix(d, views, bsize, 1, xstride=xstride, bitdepth_mode=mode, lossless=lossless)
+        c = []
+        for v in views:
+            cc = np.zeros(v.shape, np.int32)
+            for f in range(2):
+                src = np.ascontiguousarray(v[f])
+                port.oc_buf_to_coeff(mode, ol.ptr(cc[f]), v.shape[2], lossless,
+                                     ol.ptr(src.view(np.uint8)), xstride, src.strides[0],
+                                     v.shape[2], v.shape[1])
+            c.append(cc)
+        d_ref = chk.fwd_frames(c, bsize, DECS, 1)
+        for p in range(3):
+            assert np.array_equal(d[p], d_ref[p])
+        # inverse into fresh padded buffers; only the visible window may change
+        outs = [np.full_like(b, 7) for b in pix]
+        oviews = [b[:, pad:pad + s[0], pad:pad + s[1]] for b, s in zip(outs, ctx.plane_shapes)]
+        dq = [(a // 3) * 3 for a in d]   # a crude "quantiser"
+        ctx.inv_frames_pix(oviews, dq, bsize, 1, xstride=xstride, bitdepth_mode=mode, lossless=lossless)
+        c_ref = chk.inv_frames(dq, bsize, DECS, 1)
+        for p in range(3):
+            h, w = ctx.plane_shapes[p]
+            exp = np.zeros((2, h, w), pix[p].dtype)
+            for f in range(2):
+                tmp = np.zeros((h, w * xstride), np.uint8)
+                port.oc_coeff_to_buf(mode, ol.ptr(tmp), xstride, w * xstride, ol.ptr(c_ref[p][f]), w,
+                                     lossless, w, h)
+                exp[f] = tmp.view(pix[p].dtype).reshape(h, w)
+            assert np.array_equal(oviews[p], exp)
+            border = outs[p].copy()
+            border[:, pad:pad + h, pad:pad + w] = 7
+            assert (border == 7).all()
+    chk.close()

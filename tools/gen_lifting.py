@@ -447,7 +447,7 @@ CUDA_HEADER = """// GENERATED by tools/gen_lifting.py -- do not edit; edit the s
 // Straight-line device code for Daala's reversible integer lifting DCTs.
 // v[] holds the line in natural order: samples in, coefficients out (forward),
 // coefficients in, samples out (inverse).  All indices are compile-time, so
-// v[] lives in registers.  Parity targets: reference src/dct.c od_bin_fdct{4,8,
+// after inlining v[] lives in registers (v may point into a larger array).  Parity targets: reference src/dct.c od_bin_fdct{4,8,
 // 16,32} / od_bin_idct{4,8,16,32}.
 #pragma once
 
@@ -473,8 +473,8 @@ def emit_cuda(progs):
     for p in progs:
         names = [regname(i) for i in range(p.n)]
         for direction in ("f", "i"):
-            out.append("TDLT_HD void tdlt_%s%s(int (&v)[%d]) {\n"
-                       % (direction, p.name, p.n))
+            out.append("TDLT_HD void tdlt_%s%s(int *v) {  // v[0..%d]\n"
+                       % (direction, p.name, p.n - 1))
             if direction == "f":
                 for k, r in enumerate(p.in_regs):
                     out.append("  int %s = v[%d];\n" % (r, k))
