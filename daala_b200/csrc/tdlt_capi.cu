@@ -80,12 +80,12 @@ static encode_tiled_fn get_encode_tiled() {
 
 // 3-D map (x, y, frame) over nframes planes of w x h int32; box bx x by x 1.
 static int make_tmap(od_tdlt_ctx *ctx, CUtensorMap *m, const void *base, int w, int h,
-                     int nframes, int box, bool swizzle) {
+                     int nframes, int boxw, int boxh, bool swizzle) {
   encode_tiled_fn enc = get_encode_tiled();
   if (!enc) return fail(ctx, OD_TDLT_EFAULT, "cuTensorMapEncodeTiled unavailable");
   cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
   cuuint64_t strides[2] = {(cuuint64_t)w*4, (cuuint64_t)w*h*4};
-  cuuint32_t boxd[3] = {(cuuint32_t)box, (cuuint32_t)box, 1};
+  cuuint32_t boxd[3] = {(cuuint32_t)boxw, (cuuint32_t)boxh, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, const_cast<void *>(base), dims, strides,
                    boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -210,9 +210,9 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   bd.nframes = nframes;
   bd.flags = flags;
   for (int p = 0; p < bd.nplanes; p++) {
-    int rc = make_tmap(ctx, &maps.in[p], c[p], bd.pl[p].w, bd.pl[p].h, nframes, kAStride, false);
+    int rc = make_tmap(ctx, &maps.in[p], c[p], bd.pl[p].w, bd.pl[p].h, nframes, kAStride, kARows, false);
     if (rc) return rc;
-    rc = make_tmap(ctx, &maps.out[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, true);
+    rc = make_tmap(ctx, &maps.out[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, kTile, true);
     if (rc) return rc;
   }
   long long total = (long long)bd.tiles_per_frame*nframes;
@@ -252,7 +252,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   InvOut out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < bd.nplanes; p++) {
-    int rc = make_tmap(ctx, &maps.in[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, true);
+    int rc = make_tmap(ctx, &maps.in[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, kTile, true);
     if (rc) return rc;
     out.c[p] = c[p];
   }

@@ -12,9 +12,12 @@ namespace tdlt {
 // Geometry shared by host and device
 // ---------------------------------------------------------------------------
 constexpr int kTile = 32;          // a work tile is 32x32 samples of one plane
-constexpr int kAStride = 36;       // words per row of the lapping buffer
+constexpr int kAStride = 40;       // words per row of the lapping buffer
 constexpr int kARows = 36;
-constexpr int kABytes = kAStride*kARows*4;   // 5184
+constexpr int kAColOff = 4;        // tile column 0 sits at buffer column 4 ...
+constexpr int kARowOff = 2;        // ... and tile row 0 at buffer row 2
+constexpr int kABytes = kAStride*kARows*4;   // 5760, what the TMA load delivers (45 x 128)
+constexpr int kAAlloc = kABytes;
 constexpr int kBBytes = kTile*kTile*4;       // 4096, TMA SWIZZLE_128B layout
 constexpr int kLsStride = 8;       // leaf-size ring: 6x6 units, row stride 8
 constexpr int kLsBytes = 64;
@@ -91,17 +94,21 @@ __device__ __forceinline__ void haar2x2(int &ll, int &lh, int &hl, int &hh) {
 
 // ---------------------------------------------------------------------------
 // Shared-memory layouts
-//  A: 36x36 words, row stride 36.  Holds plane rows Y0-2..Y0+33, columns
-//     X0-2..X0+33 of a tile whose origin is (X0, Y0): "cell aligned" -- every
-//     4x4 lapping cell (centred on a multiple of 4) starts on a 16-byte
-//     boundary, and stride 36 makes both row-wise 128-bit and column-wise
-//     32-bit warp accesses bank-conflict free.
+//  A: 36 rows x 40 words.  Holds plane rows Y0-2..Y0+33, columns X0-4..X0+35
+//     of a tile whose origin is (X0, Y0).  The innermost TMA coordinate must be
+//     16-byte aligned (measured on B200: a tiled load at x = 30 raises "illegal
+//     instruction", x = 28 or 32 is fine), hence the 4-column halo although the
+//     lapping only needs 2.  Block aligned: 16-byte chunks start on multiples
+//     of 4 columns; the 4x4 lapping cells (centred on multiples of 4) straddle
+//     two chunks and are accessed as 8-byte halves.
 //  B: 32x32 words in the TMA SWIZZLE_128B pattern (16-byte chunk index XOR
 //     row&7; the buffer is 1024-byte aligned): "block aligned" -- conflict
 //     free for 128-bit row accesses by 8 consecutive rows AND for column-wise
 //     accesses, and it is exactly what a TMA tile load/store produces/consumes.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ int a_off(int r, int c) { return r*kAStride + c; }
+// tile sample (r, c), r and c in [-2, 34)
+__device__ __forceinline__ int a_at(int r, int c) { return (r + kARowOff)*kAStride + c + kAColOff; }
 __device__ __forceinline__ int b_off(int r, int c) {
   return r*32 + ((((c >> 2) ^ (r & 7)) << 2) | (c & 3));
 }

@@ -28,10 +28,10 @@ struct WarpSmem {
 __device__ __forceinline__ WarpSmem carve(unsigned char *base, int warp) {
   WarpSmem s;
   s.B = reinterpret_cast<int *>(base + warp*kBBytes);
-  s.A = reinterpret_cast<int *>(base + kWarpsPerCta*kBBytes + warp*kABytes);
-  s.ls = base + kWarpsPerCta*(kBBytes + kABytes) + warp*kLsBytes;
+  s.A = reinterpret_cast<int *>(base + kWarpsPerCta*kBBytes + warp*kAAlloc);
+  s.ls = base + kWarpsPerCta*(kBBytes + kAAlloc) + warp*kLsBytes;
   s.bar = reinterpret_cast<unsigned long long *>(
-      base + kWarpsPerCta*(kBBytes + kABytes + kLsBytes) + warp*8);
+      base + kWarpsPerCta*(kBBytes + kAAlloc + kLsBytes) + warp*8);
   return s;
 }
 
@@ -71,10 +71,10 @@ __device__ __forceinline__ void haar_fwd_tile(int *A, int *B, int lane, int sb) 
         int blk = it/(np*np), e = it - blk*np*np;
         int i = e/np, j = e - i*np;
         int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        a[k] = A[a_off(2 + r0 + 2*i, 2 + c0 + 2*j)];
-        b[k] = A[a_off(2 + r0 + 2*i + 1, 2 + c0 + 2*j)];
-        c[k] = A[a_off(2 + r0 + 2*i, 2 + c0 + 2*j + 1)];
-        d[k] = A[a_off(2 + r0 + 2*i + 1, 2 + c0 + 2*j + 1)];
+        a[k] = A[a_at(r0 + 2*i, c0 + 2*j)];
+        b[k] = A[a_at(r0 + 2*i + 1, c0 + 2*j)];
+        c[k] = A[a_at(r0 + 2*i, c0 + 2*j + 1)];
+        d[k] = A[a_at(r0 + 2*i + 1, c0 + 2*j + 1)];
       }
     }
     __syncwarp();
@@ -86,7 +86,7 @@ __device__ __forceinline__ void haar_fwd_tile(int *A, int *B, int lane, int sb) 
         int i = e/np, j = e - i*np;
         int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
         haar2x2(a[k], b[k], c[k], d[k]);
-        A[a_off(2 + r0 + i, 2 + c0 + j)] = a[k];
+        A[a_at(r0 + i, c0 + j)] = a[k];
         B[b_off(r0 + i, c0 + j + np)] = b[k];
         B[b_off(r0 + i + np, c0 + j)] = c[k];
         B[b_off(r0 + i + np, c0 + j + np)] = d[k];
@@ -111,7 +111,7 @@ __device__ __forceinline__ void haar_inv_tile(int *A, int *B, int lane, int sb) 
         int blk = it/(np*np), e = it - blk*np*np;
         int i = e/np, j = e - i*np;
         int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        a[k] = (np == 1) ? B[b_off(r0, c0)] : A[a_off(2 + r0 + i, 2 + c0 + j)];
+        a[k] = (np == 1) ? B[b_off(r0, c0)] : A[a_at(r0 + i, c0 + j)];
         b[k] = B[b_off(r0 + i, c0 + j + np)];
         c[k] = B[b_off(r0 + i + np, c0 + j)];
         d[k] = B[b_off(r0 + i + np, c0 + j + np)];
@@ -126,10 +126,10 @@ __device__ __forceinline__ void haar_inv_tile(int *A, int *B, int lane, int sb) 
         int i = e/np, j = e - i*np;
         int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
         haar2x2(a[k], b[k], c[k], d[k]);
-        A[a_off(2 + r0 + 2*i, 2 + c0 + 2*j)] = a[k];
-        A[a_off(2 + r0 + 2*i + 1, 2 + c0 + 2*j)] = b[k];
-        A[a_off(2 + r0 + 2*i, 2 + c0 + 2*j + 1)] = c[k];
-        A[a_off(2 + r0 + 2*i + 1, 2 + c0 + 2*j + 1)] = d[k];
+        A[a_at(r0 + 2*i, c0 + 2*j)] = a[k];
+        A[a_at(r0 + 2*i + 1, c0 + 2*j)] = b[k];
+        A[a_at(r0 + 2*i, c0 + 2*j + 1)] = c[k];
+        A[a_at(r0 + 2*i + 1, c0 + 2*j + 1)] = d[k];
       }
     }
     __syncwarp();
@@ -156,7 +156,7 @@ tdlt_fwd_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
     mbar_init(s.bar, 1);
     fence_mbar_init();
     mbar_expect_tx(s.bar, kABytes);
-    tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 2, Y0 - 2, id.frame);
+    tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - kAColOff, Y0 - kARowOff, id.frame);
   }
   load_leaf_sizes(s.ls, bsize, bd, pd, id, lane);
   __syncwarp();
@@ -285,7 +285,7 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
 #pragma unroll 1
     for (int it = 0; it < 16; it++) {
       int r = 2*it + (lane >> 4), c = 2*(lane & 15);
-      int2 val = *reinterpret_cast<int2 *>(s.A + a_off(2 + r, 2 + c));
+      int2 val = *reinterpret_cast<int2 *>(s.A + a_at(r, c));
       *reinterpret_cast<int2 *>(gout + (size_t)(Y0 + r)*pd.w + X0 + c) = val;
     }
     return;
@@ -343,9 +343,9 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
     int e = 2*lane;                       // bottom rows 30, 31: 64 words
     int a = e >> 5, c = e & 31;
     *reinterpret_cast<int2 *>(mine + e) =
-        *reinterpret_cast<int2 *>(s.A + a_off(32 + a, 2 + c));
+        *reinterpret_cast<int2 *>(s.A + a_at(30 + a, c));
     *reinterpret_cast<int2 *>(mine + 64 + 2*lane) =   // right columns 30, 31
-        *reinterpret_cast<int2 *>(s.A + a_off(2 + lane, 32));
+        *reinterpret_cast<int2 *>(s.A + a_at(lane, 30));
     __syncwarp();
     if (lane == 0) {
       __threadfence();
@@ -368,17 +368,17 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
       const int *up = strips + (size_t)(t - pd.ntx)*128;
       int e = 2*lane, a = e >> 5, c = e & 31;
       int2 val = __ldcg(reinterpret_cast<const int2 *>(up + e));
-      *reinterpret_cast<int2 *>(s.A + a_off(a, 2 + c)) = val;
+      *reinterpret_cast<int2 *>(s.A + a_at(a - 2, c)) = val;
     }
     if (has_l) {
       const int *left = strips + (size_t)(t - 1)*128;
       int2 val = __ldcg(reinterpret_cast<const int2 *>(left + 64 + 2*lane));
-      *reinterpret_cast<int2 *>(s.A + a_off(2 + lane, 0)) = val;
+      *reinterpret_cast<int2 *>(s.A + a_at(lane, -2)) = val;
     }
     if (has_u && has_l && lane < 2) {
       const int *ul = strips + (size_t)(t - pd.ntx - 1)*128;
       int2 val = __ldcg(reinterpret_cast<const int2 *>(ul + lane*32 + 30));
-      *reinterpret_cast<int2 *>(s.A + a_off(lane, 0)) = val;
+      *reinterpret_cast<int2 *>(s.A + a_at(lane - 2, -2)) = val;
     }
     __syncwarp();
   }
@@ -396,7 +396,7 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
     __syncwarp();
   }
 
-  // ---- store: A row a <-> plane row Y0-2+a, A column b <-> X0-2+b ----------
+  // ---- store: region row a <-> plane row Y0-2+a, region column b <-> X0-2+b -
   {
     const int a0 = (id.ty == 0) ? 2 : 0, a1 = last_r ? 34 : 32;
     const int b0 = (id.tx == 0) ? 2 : 0;
@@ -406,7 +406,7 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
       int a = 2*it + (lane >> 4), b = 2*(lane & 15);
       if (a >= a0 && a < a1 && b >= b0) {
         *reinterpret_cast<int2 *>(g + (ptrdiff_t)a*pd.w + b) =
-            *reinterpret_cast<int2 *>(s.A + a_off(a, b));
+            *reinterpret_cast<int2 *>(s.A + a_at(a - 2, b - 2));
       }
     }
     if (last_c) {
@@ -414,7 +414,7 @@ tdlt_inv_kernel(const __grid_constant__ TmapSet maps, const __grid_constant__ Ba
       for (int a = lane; a < 34; a += 32) {
         if (a >= a0 && a < a1) {
           *reinterpret_cast<int2 *>(g + (ptrdiff_t)a*pd.w + 32) =
-              *reinterpret_cast<int2 *>(s.A + a_off(a, 32));
+              *reinterpret_cast<int2 *>(s.A + a_at(a - 2, 30));
         }
       }
     }

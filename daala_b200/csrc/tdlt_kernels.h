@@ -17,7 +17,7 @@ struct InvOut {
   int *c[kMaxPlanes];
 };
 
-constexpr int kCtaSmemBytes = kWarpsPerCta*(kBBytes + kABytes + kLsBytes + 8);
+constexpr int kCtaSmemBytes = kWarpsPerCta*(kBBytes + kAAlloc + kLsBytes + 8);
 constexpr int kCtaSmemAlloc = kCtaSmemBytes + 16;   // + the inverse kernel's ticket slot
 
 __global__ void tdlt_fwd_kernel(const __grid_constant__ TmapSet maps,

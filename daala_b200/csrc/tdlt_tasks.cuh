@@ -13,7 +13,7 @@
 //
 // (k = lane's index 0..7 among the 8 lanes of a 16x16 leaf.)  The assignments
 // were chosen so that every shared-memory access below is bank-conflict free
-// on buffer B and at worst 2-way conflicted on buffer A.
+// for the transforms; the lapping cells on buffer A see at most 2-way conflicts.
 #pragma once
 #include "tdlt_device.cuh"
 
@@ -37,10 +37,10 @@ __device__ __forceinline__ Lane make_lane(int lane) {
 }
 
 // ------------------------------------------------------------------ buffer A
-// Column tasks on A (tile sample (r, c) lives at A[(r+2)*36 + c+2]).
+// Column tasks on A (tile sample (r, c) lives at A[a_at(r, c)]).
 template <bool kStore>
 __device__ __forceinline__ void colA_32(int *A, int lane, int *v) {
-  int *p = A + a_off(2, 2 + lane);
+  int *p = A + a_at(0, lane);
 #pragma unroll
   for (int r = 0; r < 32; r++) {
     if (kStore) p[r*kAStride] = v[r]; else v[r] = p[r*kAStride];
@@ -48,7 +48,7 @@ __device__ __forceinline__ void colA_32(int *A, int lane, int *v) {
 }
 template <bool kStore>
 __device__ __forceinline__ void colA_16(int *A, const Lane &L, int *v) {
-  int2 *p = reinterpret_cast<int2 *>(A + a_off(2 + L.r16, 2 + L.c16 + 2*L.k16));
+  int2 *p = reinterpret_cast<int2 *>(A + a_at(L.r16, L.c16 + 2*L.k16));
 #pragma unroll
   for (int r = 0; r < 16; r++) {
     if (kStore) p[r*(kAStride/2)] = make_int2(v[r], v[16 + r]);
@@ -58,17 +58,11 @@ __device__ __forceinline__ void colA_16(int *A, const Lane &L, int *v) {
 // 8 rows x 4 columns, element (r, q) <-> v[8*q + r]  (q-th column contiguous)
 template <bool kStore>
 __device__ __forceinline__ void colA_8(int *A, const Lane &L, int *v) {
-  int2 *p = reinterpret_cast<int2 *>(A + a_off(2 + L.ur*8, 2 + L.uc*8 + 4*L.h));
+  int4 *p = reinterpret_cast<int4 *>(A + a_at(L.ur*8, L.uc*8 + 4*L.h));
 #pragma unroll
   for (int r = 0; r < 8; r++) {
-    if (kStore) {
-      p[r*(kAStride/2)] = make_int2(v[r], v[8 + r]);
-      p[r*(kAStride/2) + 1] = make_int2(v[16 + r], v[24 + r]);
-    }
-    else {
-      int2 t0 = p[r*(kAStride/2)], t1 = p[r*(kAStride/2) + 1];
-      v[r] = t0.x; v[8 + r] = t0.y; v[16 + r] = t1.x; v[24 + r] = t1.y;
-    }
+    if (kStore) p[r*(kAStride/4)] = make_int4(v[r], v[8 + r], v[16 + r], v[24 + r]);
+    else { int4 t = p[r*(kAStride/4)]; v[r] = t.x; v[8 + r] = t.y; v[16 + r] = t.z; v[24 + r] = t.w; }
   }
 }
 
@@ -208,19 +202,28 @@ __device__ __forceinline__ void cell_horz(int4 &r0, int4 &r1, int4 &r2, int4 &r3
   }
 }
 
-// Processes the cell whose top-left corner is A[(4i)*36 + 4j] in place.
-// Forward order: coarser edge first, vertical-direction first on ties; the
-// inverse undoes that back to front.
+// Processes cell (i, j) in place: rows 4i..4i+3, columns 4j+2..4j+5 of A, i.e.
+// the cell centred on tile-local (4i, 4j).  Forward order: coarser edge first,
+// vertical-direction first on ties; the inverse undoes that back to front.
 template <bool kInverse>
 __device__ __forceinline__ void lap_cell(int *A, int i, int j, int fl) {
   if ((fl & 15) == 0) return;
-  int4 *p = reinterpret_cast<int4 *>(A + a_off(4*i, 4*j));
-  int4 r0 = p[0], r1 = p[kAStride/4], r2 = p[2*(kAStride/4)], r3 = p[3*(kAStride/4)];
+  int2 *p = reinterpret_cast<int2 *>(A + a_off(4*i, 4*j + 2));
+  constexpr int S = kAStride/2;
+  int2 lo, hi;
+  int4 r0, r1, r2, r3;
+  lo = p[0]; hi = p[1]; r0 = make_int4(lo.x, lo.y, hi.x, hi.y);
+  lo = p[S]; hi = p[S + 1]; r1 = make_int4(lo.x, lo.y, hi.x, hi.y);
+  lo = p[2*S]; hi = p[2*S + 1]; r2 = make_int4(lo.x, lo.y, hi.x, hi.y);
+  lo = p[3*S]; hi = p[3*S + 1]; r3 = make_int4(lo.x, lo.y, hi.x, hi.y);
   bool vfirst = ((fl & 16) != 0) != kInverse;
   if (!vfirst) cell_horz<kInverse>(r0, r1, r2, r3, fl);
   cell_vert<kInverse>(r0, r1, r2, r3, fl);
   if (vfirst) cell_horz<kInverse>(r0, r1, r2, r3, fl);
-  p[0] = r0; p[kAStride/4] = r1; p[2*(kAStride/4)] = r2; p[3*(kAStride/4)] = r3;
+  p[0] = make_int2(r0.x, r0.y); p[1] = make_int2(r0.z, r0.w);
+  p[S] = make_int2(r1.x, r1.y); p[S + 1] = make_int2(r1.z, r1.w);
+  p[2*S] = make_int2(r2.x, r2.y); p[2*S + 1] = make_int2(r2.z, r2.w);
+  p[3*S] = make_int2(r3.x, r3.y); p[3*S + 1] = make_int2(r3.z, r3.w);
 }
 
 }  // namespace tdlt
