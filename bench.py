@@ -1,0 +1,384 @@
+#!/usr/bin/env python3
+"""bench.py -- forward+inverse TDLT throughput (Mpixel/s) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload 4k|1080p|1080p8x8|720p]
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      (the reference's CPU path, host cores)
+
+One "step" = forward stage then inverse stage over a batch of synthetic 4:2:0
+frames that is already resident in HBM.  Default workload = the one BASELINE.json's
+metric and target are quoted on: 3840x2160 4:2:0, variable block sizes (random
+quadtree maps), 64 frames per GPU, keyframe mode.  Frames are
+independent, so N GPUs each take their own batch (weak scaling, no collective on
+the data path; torch.distributed is used only for the timing barrier / max).
+
+"pixel" = one luma picture pixel (pic_width*pic_height*frames); its luma sample
+and 0.5 chroma samples go through both stages.  Algorithmic bytes: 8 per padded
+plane sample per direction (read int32, write int32), SURVEY 8d.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (pic_w, pic_h, frames per GPU, map kind)
+    "4k": (3840, 2160, 64, "quad"),
+    "1080p": (1920, 1080, 64, "quad"),
+    "1080p8x8": (1920, 1080, 64, "uniform1"),
+    "720p": (1280, 720, 64, "quad"),
+    "cif": (352, 288, 10, "quad"),
+}
+DECS = (0, 1, 1)
+
+
+def make_maps_np(kind, nframes, nhsb, nvsb, seed):
+    """Vectorised random quadtree (split 32 w.p. .8, 16 w.p. .6, 8 w.p. .5)."""
+    rng = np.random.default_rng(seed)
+    if kind.startswith("uniform"):
+        return np.full((nframes, nvsb * 4, nhsb * 4), int(kind[-1]), np.uint8)
+    s32 = rng.random((nframes, nvsb, nhsb)) < 0.8
+    s16 = rng.random((nframes, nvsb * 2, nhsb * 2)) < 0.6
+    s8 = rng.random((nframes, nvsb * 4, nhsb * 4)) < 0.5
+    up = lambda a, k: np.repeat(np.repeat(a, k, axis=1), k, axis=2)
+    m = np.where(s8, 0, 1)
+    m = np.where(up(s16, 2), m, 2)
+    m = np.where(up(s32, 4), m, 3)
+    return m.astype(np.uint8)
+
+
+def frame_dims(pic_w, pic_h):
+    return (pic_w + 63) & ~63, (pic_h + 63) & ~63
+
+
+# ----------------------------------------------------------------- clocks ----
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------- reference (CPU) ----
+def cpu_reference_run(pic_w, pic_h, kind, steps, warmup, budget_s=20.0):
+    """Times the reference's own CPU implementation of the path (oracle/_ref when it
+    is built, else the C restatement) on the host cores: frames spread over threads
+    (the functions are re-entrant; ctypes releases the GIL).  Returns a dict."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_libs as ol
+    use_ref = ol.have_ref()
+    fw, fh = frame_dims(pic_w, pic_h)
+    nhsb, nvsb = fw // 32, fh // 32
+    cores = os.cpu_count() or 1
+    nthreads = max(1, min(cores, 32))
+    rng = np.random.default_rng(11)
+    maps = make_maps_np(kind, 1, nhsb, nvsb, 7)[0]
+    planes = [rng.integers(-2048, 2048, size=(fh >> d, fw >> d)).astype(np.int32) for d in DECS]
+
+    def make_worker():
+        ctx = ol.RefCtx(pic_w, pic_h) if use_ref else None
+
+        def one_frame():
+            for p, dec in enumerate(DECS):
+                if ctx:
+                    d, _ = ctx.fwd_plane(planes[p], maps, dec, 1, impl=1)
+                    ctx.inv_plane(d, maps, dec, 1, impl=1)
+                else:
+                    d, _ = ol.port_fwd_plane(planes[p], maps, dec, pic_w, pic_h, 1)
+                    ol.port_inv_plane(d, maps, dec, pic_w, pic_h, 1)
+        return one_frame
+
+    workers = [make_worker() for _ in range(nthreads)]
+    # size the per-step sample from one single-thread frame
+    t0 = time.perf_counter()
+    workers[0]()
+    t_frame = time.perf_counter() - t0
+    total_steps = steps + warmup
+    per_thread = max(1, int(budget_s / max(t_frame, 1e-6) / max(total_steps, 1)))
+    per_thread = min(per_thread, 64)
+
+    def run_step():
+        ths = [threading.Thread(target=lambda w=w: [w() for _ in range(per_thread)]) for w in workers]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        return time.perf_counter() - t0
+
+    for _ in range(warmup):
+        run_step()
+    times = [run_step() for _ in range(steps)]
+    frames = nthreads * per_thread
+    el = float(np.mean(times))
+    mpix = pic_w * pic_h * frames / el / 1e6
+    return {"value": mpix, "unit": "Mpixel/s", "cores": nthreads,
+            "kind": "reference" if use_ref else "port",
+            "sample": "%d frames of %dx%d per step (%d threads x %d), fwd+inv, gcc -O2, "
+                      "x86 SIMD dispatch for 4x4/8x8" % (frames, pic_w, pic_h, nthreads, per_thread),
+            "ms_per_step": el * 1e3, "host_cores": cores}
+
+
+# ------------------------------------------------------------------- main ----
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="4k", choices=sorted(WORKLOADS))
+    ap.add_argument("--frames", type=int, default=0, help="frames per GPU (0 = workload default)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    pic_w, pic_h, nframes, kind = WORKLOADS[args.workload]
+    if args.frames:
+        nframes = args.frames
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    config = {"workload": "%dx%d 4:2:0, %s block-size maps, %d frames per GPU, keyframe DC pyramid, "
+                          "od_coeff int32 planes" % (pic_w, pic_h,
+                                                     "random-quadtree 4x4..32x32" if kind == "quad" else kind,
+                                                     nframes),
+              "frames_per_gpu": nframes, "l2": "inputs larger than L2 (no flush needed)",
+              "parallelism": "frames sharded over %d GPU(s), no collective" % world}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = cpu_reference_run(pic_w, pic_h, kind, args.steps, args.warmup)
+        line = {"impl": "reference", "metric": "Mpixel/s fwd+inv TDLT (4:2:0, var bsize)",
+                "value": r["value"], "unit": "Mpixel/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+                "config": config,
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": r["value"], "unit": "Mpixel/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import daala_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for the product path)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    ctx = daala_b200.TdltContext(pic_w, pic_h, decs=DECS, device=local_rank,
+                                 max_frames=0 if args.no_e2e else nframes)
+    fw, fh = ctx.frame_width, ctx.frame_height
+    shapes = ctx.plane_shapes
+    samples_per_frame = sum(h * w for h, w in shapes)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+
+    def synth(h, w):
+        # smooth field + texture, 12-bit coefficient scale (8-bit << 4), on the GPU
+        low = torch.randn((nframes, 1, h // 8 + 1, w // 8 + 1), device=dev, generator=g)
+        img = torch.nn.functional.interpolate(low, size=(h, w), mode="bilinear", align_corners=False)
+        img = img.squeeze(1) * 600.0 + torch.randn((nframes, h, w), device=dev, generator=g) * 60.0
+        return img.round().clamp_(-2048, 2047).to(torch.int32).contiguous()
+
+    c = [synth(h, w) for h, w in shapes]
+    d = [torch.empty_like(t) for t in c]
+    c2 = [torch.empty_like(t) for t in c]
+    maps_np = make_maps_np(kind, nframes, ctx.nhsb, ctx.nvsb, 99 + rank)
+    maps = torch.from_numpy(maps_np).to(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    cp = [t.data_ptr() for t in c]
+    dp = [t.data_ptr() for t in d]
+    c2p = [t.data_ptr() for t in c2]
+    FL = daala_b200.OD_TDLT_KEYFRAME
+
+    def fwd():
+        ctx.fwd_batch(dp, cp, maps.data_ptr(), nframes, FL, stream)
+
+    def inv():
+        ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, FL, stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        fwd()
+        inv()
+    torch.cuda.synchronize()
+    ok = all(torch.equal(a, b) for a, b in zip(c, c2))   # lossless round trip at full size
+    if not ok:
+        raise SystemExit("bench.py: round trip is not the identity -- refusing to report a number")
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    l0 = daala_b200.launch_count()
+    ev[0].record()
+    for k in range(args.steps):
+        fwd()
+        ev[2 * k + 1].record()
+        inv()
+        ev[2 * k + 2].record()
+    torch.cuda.synchronize()
+    launches = daala_b200.launch_count() - l0
+    clocks = sampler.stop()
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    fwd_ms = float(np.mean([ev[2 * k].elapsed_time(ev[2 * k + 1]) for k in range(args.steps)]))
+    inv_ms = float(np.mean([ev[2 * k + 1].elapsed_time(ev[2 * k + 2]) for k in range(args.steps)]))
+    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    pixels_per_step = pic_w * pic_h * nframes * world
+    value = pixels_per_step / (ms_per_step * 1e-3) / 1e6
+
+    # roofline of the dominant kernel (8 algorithmic bytes per padded plane sample per launch)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    alg_bytes = 8.0 * samples_per_frame * nframes
+    dom, dom_ms = ("tdlt_inv_kernel", inv_ms) if inv_ms >= fwd_ms else ("tdlt_fwd_kernel", fwd_ms)
+    ach = alg_bytes / (dom_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+            "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg_bytes,
+            "fwd_ms": fwd_ms, "inv_ms": inv_ms,
+            "fwd_GBps": alg_bytes / (fwd_ms * 1e-3) / 1e9, "inv_GBps": alg_bytes / (inv_ms * 1e-3) / 1e9,
+            "step_frac_of_peak": 2 * alg_bytes / (ms_per_step * 1e-3) / 1e9 / peak}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roof["traffic"] = json.load(open(prof)).get(dom)
+        except Exception:
+            pass
+
+    # end to end: host (pinned) buffers through the frame-level C-ABI calls
+    e2e = None
+    if not args.no_e2e:
+        hc = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
+        hd = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
+        hc2 = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
+        for a, b in zip(hc, c):
+            a.copy_(b)
+        hmaps = torch.from_numpy(maps_np).pin_memory()
+        L = ctx.L
+        arr = daala_b200._ptr_array
+
+        def e2e_step():
+            rc = L.od_tdlt_fwd_frames(ctx._h, arr([x.data_ptr() for x in hd]), arr([x.data_ptr() for x in hc]),
+                                      hmaps.data_ptr(), nframes, FL)
+            rc |= L.od_tdlt_inv_frames(ctx._h, arr([x.data_ptr() for x in hc2]), arr([x.data_ptr() for x in hd]),
+                                       hmaps.data_ptr(), nframes, FL)
+            if rc:
+                raise SystemExit("e2e call failed: %s" % L.od_tdlt_last_error(ctx._h).decode())
+
+        e2e_steps = max(2, min(args.steps, 3))
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        el = time.perf_counter() - t0
+        tt = torch.tensor([el], device=dev, dtype=torch.float64)
+        if dist:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        el = float(tt.item())
+        if not all(torch.equal(a, b) for a, b in zip(hc, hc2)):
+            raise SystemExit("bench.py: e2e round trip mismatch")
+        plane_bytes = 4 * samples_per_frame * nframes
+        e2e = {"value": pic_w * pic_h * nframes * world * e2e_steps / el / 1e6, "unit": "Mpixel/s",
+               "h2d_bytes_per_step": 2 * plane_bytes + 2 * maps_np.nbytes,
+               "d2h_bytes_per_step": 2 * plane_bytes, "steps": e2e_steps,
+               "api": "od_tdlt_fwd_frames + od_tdlt_inv_frames (pinned host od_coeff planes)"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        r = cpu_reference_run(pic_w, pic_h, kind, 2, 1, budget_s=15.0)
+        cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {"metric": "Mpixel/s fwd+inv TDLT (4:2:0, var bsize)", "value": value, "unit": "Mpixel/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+                "data": "synthetic", "config": config, "clocks": clocks, "roofline": roof,
+                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "round_trip_exact": True}
+        print(json.dumps(line))
+    ctx.close()
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
