@@ -23,6 +23,7 @@ struct od_tdlt_ctx {
   int max_frames;
   int fw, fh, nhsb, nvsb;
   BatchDesc bd;                 // template: nframes / flags filled per call
+  RegionBatch rb;               // the same for the region kernels
   long long plane_size[kMaxPlanes];
   // strip exchange of the inverse kernel
   int *strips;
@@ -137,6 +138,25 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     ctx->plane_size[p] = (long long)pd.w*pd.h;
   }
   bd.tiles_per_frame = tile0;
+  RegionBatch &rb = ctx->rb;
+  rb.nplanes = g->nplanes;
+  rb.pic_w = g->pic_width;
+  rb.pic_h = g->pic_height;
+  rb.bw = bd.bw;
+  rb.bh = bd.bh;
+  int reg0 = 0;
+  for (int p = 0; p < g->nplanes; p++) {
+    RegionPlane &rp = rb.pl[p];
+    rp.dec = g->xdec[p];
+    rp.w = ctx->fw >> rp.dec;
+    rp.h = ctx->fh >> rp.dec;
+    rp.nrx = (rp.w + kRegW - 1)/kRegW;
+    rp.nry = (rp.h + kRegH - 1)/kRegH;
+    rp.reg0 = reg0;
+    rp.inv_nrx = 1.0f/(float)rp.nrx;
+    reg0 += rp.nrx*rp.nry;
+  }
+  rb.regs_per_frame = reg0;
   *out = ctx;
   int rc = OD_TDLT_SUCCESS;
   do {
@@ -145,10 +165,10 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
       rc = OD_TDLT_EFAULT; break;
     }
     if (cudaMalloc(&ctx->ticket, 256) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
-    cudaFuncSetAttribute(tdlt_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCtaSmemAlloc);
-    cudaFuncSetAttribute(tdlt_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCtaSmemAlloc);
-    cudaFuncSetAttribute(tdlt_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-    cudaFuncSetAttribute(tdlt_inv_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+    cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+    cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (max_frames > 0) {
       bool ok = true;
       for (int p = 0; p < g->nplanes && ok; p++) {
@@ -206,18 +226,18 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   CK(ctx, cudaSetDevice(ctx->device));
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
-  BatchDesc bd = ctx->bd;
-  bd.nframes = nframes;
-  bd.flags = flags;
-  for (int p = 0; p < bd.nplanes; p++) {
-    int rc = make_tmap(ctx, &maps.in[p], c[p], bd.pl[p].w, bd.pl[p].h, nframes, kAStride, kARows, false);
+  RegionBatch rb = ctx->rb;
+  rb.nframes = nframes;
+  rb.flags = flags;
+  for (int p = 0; p < rb.nplanes; p++) {
+    int rc = make_tmap(ctx, &maps.in[p], c[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
     if (rc) return rc;
-    rc = make_tmap(ctx, &maps.out[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, kTile, true);
+    rc = make_tmap(ctx, &maps.out[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kTile, kTile, true);
     if (rc) return rc;
   }
-  long long total = (long long)bd.tiles_per_frame*nframes;
-  unsigned grid = (unsigned)((total + kWarpsPerCta - 1)/kWarpsPerCta);
-  tdlt_fwd_kernel<<<grid, kWarpsPerCta*32, kCtaSmemAlloc, (cudaStream_t)stream>>>(maps, bd, bsize);
+  if (nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes > 65535");
+  dim3 grid((unsigned)rb.regs_per_frame, (unsigned)nframes);
+  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(maps, rb, bsize);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
@@ -231,7 +251,7 @@ static int ensure_scratch(od_tdlt_ctx *ctx, long long tiles) {
   ctx->strips = nullptr;
   ctx->flags = nullptr;
   ctx->scratch_tiles = 0;
-  CK(ctx, cudaMalloc(&ctx->strips, (size_t)tiles*128*sizeof(int)));
+  CK(ctx, cudaMalloc(&ctx->strips, (size_t)tiles*kRegionStripInts*sizeof(int)));
   CK(ctx, cudaMalloc(&ctx->flags, (size_t)tiles*sizeof(int)));
   CK(ctx, cudaMemset(ctx->flags, 0, (size_t)tiles*sizeof(int)));
   ctx->scratch_tiles = tiles;
@@ -246,25 +266,24 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaSetDevice(ctx->device));
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
-  BatchDesc bd = ctx->bd;
-  bd.nframes = nframes;
-  bd.flags = flags;
+  RegionBatch rb = ctx->rb;
+  rb.nframes = nframes;
+  rb.flags = flags;
   InvOut out;
   memset(&out, 0, sizeof(out));
-  for (int p = 0; p < bd.nplanes; p++) {
-    int rc = make_tmap(ctx, &maps.in[p], d[p], bd.pl[p].w, bd.pl[p].h, nframes, kTile, kTile, true);
+  for (int p = 0; p < rb.nplanes; p++) {
+    int rc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kTile, kTile, true);
     if (rc) return rc;
     out.c[p] = c[p];
   }
-  long long total = (long long)bd.tiles_per_frame*nframes;
+  long long total = (long long)rb.regs_per_frame*nframes;
   int rc = ensure_scratch(ctx, total);
   if (rc) return rc;
-  unsigned grid = (unsigned)((total + kWarpsPerCta - 1)/kWarpsPerCta);
   cudaStream_t st = (cudaStream_t)stream;
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
-  tdlt_inv_kernel<<<grid, kWarpsPerCta*32, kCtaSmemAlloc, st>>>(
-      maps, bd, bsize, out, ctx->strips, ctx->flags, ctx->ticket, ctx->epoch);
+  tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
+      maps, rb, bsize, out, ctx->strips, ctx->flags, ctx->ticket, ctx->epoch);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

@@ -1,0 +1,309 @@
+// Inverse TDLT over a batch of frames: d -> c.
+//   keyframe Haar-DC split (reference src/decode.c:697-738), leaf iDCTs
+//   (src/dct.c), split postfilters bottom-up (src/filter.c:1512-1554) and the
+//   SB-edge postfilter (:1588-1646); lossless mode: od_haar_inv (src/dct.c:1999).
+// One CTA per 128x64 region of one plane (tdlt_region.cuh).
+//
+// The post-filter of a block edge needs reconstructed samples from both sides
+// of it, so a region cannot finish alone: region (rx, ry) owns the OUTPUT
+// rectangle shifted by (-2, -2) -- plane rows Y0-2..Y0+61, columns
+// X0-2..X0+125, a whole number of lapping cells -- and needs the two bottom
+// rows / right columns of raw iDCT output of its upper / left / upper-left
+// neighbours.  Every region publishes those strips (1.5 KB) to global memory
+// and raises a flag; consumers wait on the flags of regions that precede them
+// in a TICKET order (CTAs draw tickets in the order they start running, so a
+// region only ever waits on work that is already resident: no deadlock, and on
+// average the producer is ahead because it started first).
+#include <cuda.h>
+#include "tdlt_tasks.cuh"
+#include "tdlt_region.cuh"
+#include "tdlt_kernels.h"
+
+namespace tdlt {
+
+constexpr int kStripInts = 2*kRegW + 2*kRegH;   // bottom rows 62, 63; right columns 126, 127
+
+__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int *p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
+// ---- lossless mode: inverse multi-level Haar wavelet of each superblock of a
+// tile (reference src/dct.c:1999-2026).  Y = the B tile, output in the tile's
+// part of A.
+__device__ __forceinline__ void region_haar_inv_tile(int *At, int *Bt, int lane, int sb) {
+  int ln = (sb == 32) ? 5 : 4;
+  int nb = 32/sb;
+#pragma unroll 1
+  for (int level = ln - 1; level >= 0; level--) {
+    int np = 1 << (ln - 1 - level);
+    int items = nb*nb*np*np;
+    int a[8], b[8], c[8], d[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int it = lane + 32*k;
+      if (it < items) {
+        int blk = it/(np*np), e = it - blk*np*np;
+        int i = e/np, j = e - i*np;
+        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
+        a[k] = (np == 1) ? Bt[b_off(r0, c0)] : At[(r0 + i)*kAP + c0 + j];
+        b[k] = Bt[b_off(r0 + i, c0 + j + np)];
+        c[k] = Bt[b_off(r0 + i + np, c0 + j)];
+        d[k] = Bt[b_off(r0 + i + np, c0 + j + np)];
+      }
+    }
+    __syncwarp();     // every read of the level precedes every write
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int it = lane + 32*k;
+      if (it < items) {
+        int blk = it/(np*np), e = it - blk*np*np;
+        int i = e/np, j = e - i*np;
+        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
+        haar2x2(a[k], b[k], c[k], d[k]);
+        At[(r0 + 2*i)*kAP + c0 + 2*j] = a[k];
+        At[(r0 + 2*i + 1)*kAP + c0 + 2*j] = b[k];
+        At[(r0 + 2*i)*kAP + c0 + 2*j + 1] = c[k];
+        At[(r0 + 2*i + 1)*kAP + c0 + 2*j + 1] = d[k];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(kRegThreads, 3)
+tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ bsize, InvOut out,
+                       int *__restrict__ strips, int *__restrict__ flags,
+                       int *__restrict__ ticket, int epoch) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const RegionSmem s = carve_region(smem);
+  if (tid == 0) s.cnt[0] = atomicAdd(ticket, 1);
+  if (tid >= 252) s.cnt[tid - 248] = 0;
+  __syncthreads();
+  const int t = s.cnt[0];
+  const int frame = t / bd.regs_per_frame;
+  const RegionId id = decode_region(bd, frame, t - frame*bd.regs_per_frame);
+  const RegionPlane &pd = bd.pl[id.pli];
+  const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
+  const bool haar = (bd.flags & 2) != 0;
+  const int sb = 32 >> pd.dec;
+
+  if (tid == 0) {
+    mbar_init(s.bar, 1);
+    fence_mbar_init();
+    int ntiles = 0;
+    for (int k = 0; k < kRegTiles; k++) {
+      ntiles += (X0 + 32*(k & 3) < pd.w && Y0 + 32*(k >> 2) < pd.h) ? 1 : 0;
+    }
+    mbar_expect_tx(s.bar, ntiles*kBBytes);
+    for (int k = 0; k < kRegTiles; k++) {
+      int TX = X0 + 32*(k & 3), TY = Y0 + 32*(k >> 2);
+      if (TX < pd.w && TY < pd.h) {
+        tma_load_3d(s.B + k*(kBBytes/4), &maps.in[id.pli], s.bar, TX, TY, id.frame);
+      }
+    }
+  }
+  region_setup_units(s, bsize, bd, pd, id, tid, lane);
+  __syncthreads();
+  mbar_wait(s.bar, 0);
+
+  int *gout = out.c[id.pli] + (size_t)id.frame*pd.w*pd.h;
+  const int tx = warp & 3, ty = warp >> 2;
+  const bool tile_on = X0 + 32*tx < pd.w && Y0 + 32*ty < pd.h;
+
+  if (haar) {
+    // No lapping in lossless mode: every tile is stored where it lies.
+    if (tile_on) {
+      int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;
+      region_haar_inv_tile(At, s.B + warp*(kBBytes/4), lane, sb);
+      int *g = gout + (size_t)(Y0 + 32*ty)*pd.w + X0 + 32*tx;
+#pragma unroll 1
+      for (int r = 0; r < 32; r++) g[(size_t)r*pd.w + lane] = At[r*kAP + lane];
+    }
+    return;
+  }
+
+  // ---- keyframe: undo the DC pyramid, top-down --------------------------------
+  if ((bd.flags & 1) && tile_on) {
+    int *Bt = s.B + warp*(kBBytes/4);
+    const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
+    if (pd.dec == 0) region_dc_level<true>(Bt, ls0, lane, 32);
+    region_dc_level<true>(Bt, ls0, lane, 16);
+    region_dc_level<true>(Bt, ls0, lane, 8);
+  }
+  __syncthreads();
+
+  // ---- inverse transforms: rows first, then columns (src/dct.c:144-149) --------
+  {
+    const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
+    const int q0 = (n0 + 15) >> 4, q1 = (n1 + 15) >> 4, q2 = (n2 + 3) >> 2;
+    const int ntask = q0 + q1 + q2 + n3;
+    unsigned char *Bb = reinterpret_cast<unsigned char *>(s.B);
+    int v[32];
+#pragma unroll 1
+    for (int g = warp; g < ntask; g += kRegWarps) {
+      if (g < n3) {
+        int e = s.tasks[3*kTaskListStride + g];
+        int UR = e >> 4, UC = e & 15;
+        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; pass++) {
+          if (pass == 0) b_row32<false>(tile, lane, v);
+          else b_col32<false>(tile, lane, v);
+          tdlt_idct32(v);
+          if (pass == 0) b_row32<true>(tile, lane, v);
+          else a_col32<true>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + lane, v);
+          __syncwarp();
+        }
+      }
+      else if (g < n3 + q2) {
+        int idx = (g - n3)*4 + (lane >> 3), k = lane & 7;
+        bool on = idx < n2;
+        int e = s.tasks[2*kTaskListStride + (on ? idx : 0)];
+        int UR = e >> 4, UC = e & 15;
+        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        int r16 = (UR & 2)*8, c16 = (UC & 2)*8;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; pass++) {
+          if (on) {
+            if (pass == 0) b_rows16<false>(tile, r16, c16, k, v);
+            else b_cols16<false>(tile, r16, c16, k, v);
+            tdlt_idct16(v);
+            tdlt_idct16(v + 16);
+            if (pass == 0) b_rows16<true>(tile, r16, c16, k, v);
+            else a_cols16<true>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 2*k, v);
+          }
+          __syncwarp();
+        }
+      }
+      else if (g < n3 + q2 + q1) {
+        int idx = (g - n3 - q2)*16 + (lane >> 1), h = lane & 1;
+        bool on = idx < n1;
+        int e = s.tasks[1*kTaskListStride + (on ? idx : 0)];
+        int UR = e >> 4, UC = e & 15;
+        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        int ur = UR & 3, uc = UC & 3;
+        int mu = (uc ^ (lane >> 1)) & 3;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; pass++) {
+          if (on) {
+            if (pass == 0) b_rows8<false>(tile, ur, uc, h, mu, v);
+            else b_8x4<false>(tile, ur, uc, h, v);
+#pragma unroll
+            for (int q = 0; q < 4; q++) tdlt_idct8(v + 8*q);
+            if (pass == 0) b_rows8<true>(tile, ur, uc, h, mu, v);
+            else st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+          }
+          __syncwarp();
+        }
+      }
+      else {
+        int idx = (g - n3 - q2 - q1)*16 + (lane >> 1), h = lane & 1;
+        if (idx < n0) {
+          int e = s.tasks[idx];
+          int UR = e >> 4, UC = e & 15;
+          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+          b_8x4<false>(tile, UR & 3, UC & 3, h, v);
+          idct4x4_pair(v);
+          st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- publish my bottom rows / right columns (raw iDCT output) ---------------
+  {
+    int *mine = strips + (size_t)t*kStripInts;
+    if (tid < 128) {          // rows 62, 63: 2 x 128 words as 128 int2
+      int a = tid >> 6, c = 2*(tid & 63);
+      *reinterpret_cast<int2 *>(mine + a*kRegW + c) =
+          *reinterpret_cast<int2 *>(s.A + (62 + a + 2)*kAP + c + 4);
+    }
+    else if (tid < 192) {     // columns 126, 127 of rows 0..63
+      int r = tid - 128;
+      *reinterpret_cast<int2 *>(mine + 2*kRegW + 2*r) =
+          *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 126 + 4);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) st_release_gpu(flags + t, epoch);
+  }
+
+  // ---- fetch the ring from the regions above / left / above-left ---------------
+  {
+    const bool has_l = id.rx > 0, has_u = id.ry > 0;
+    if (tid < 3) {
+      int nb = (tid == 0) ? t - 1 : (tid == 1) ? t - pd.nrx : t - pd.nrx - 1;
+      bool need = (tid == 0) ? has_l : (tid == 1) ? has_u : (has_l && has_u);
+      if (need) {
+        while (ld_acquire_gpu(flags + nb) != epoch) __nanosleep(64);
+      }
+    }
+    __syncthreads();
+    if (tid < 128) {
+      if (has_u) {
+        const int *up = strips + (size_t)(t - pd.nrx)*kStripInts;
+        int a = tid >> 6, c = 2*(tid & 63);
+        int2 val = __ldcg(reinterpret_cast<const int2 *>(up + a*kRegW + c));
+        *reinterpret_cast<int2 *>(s.A + a*kAP + c + 4) = val;
+      }
+    }
+    else if (tid < 192) {
+      if (has_l) {
+        const int *left = strips + (size_t)(t - 1)*kStripInts;
+        int r = tid - 128;
+        int2 val = __ldcg(reinterpret_cast<const int2 *>(left + 2*kRegW + 2*r));
+        *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 2) = val;
+      }
+    }
+    else if (tid < 194) {
+      if (has_u && has_l) {
+        const int *ul = strips + (size_t)(t - pd.nrx - 1)*kStripInts;
+        int a = tid - 192;
+        int2 val = __ldcg(reinterpret_cast<const int2 *>(ul + a*kRegW + 126));
+        *reinterpret_cast<int2 *>(s.A + a*kAP + 2) = val;
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
+  const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
+#pragma unroll 1
+  for (int lv = 4; lv <= sb; lv <<= 1) {
+    region_lap_rows<true>(s.A, s.ub, lv, sb, warp, lane, last_r);
+    __syncthreads();
+    region_lap_cols<true>(s.A, s.ub, lv, sb, tid);
+    __syncthreads();
+  }
+
+  // ---- store the owned rectangle: buffer row b <-> plane row Y0 - 2 + b ---------
+  {
+    const int b0 = (id.ry == 0) ? 2 : 0;
+    const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
+    const int c0 = (id.rx == 0) ? 2 : 0;                                  // in int2 units of
+    const int c1 = last_c ? min(kRegW, pd.w - X0) + 2 : kRegW;            // buffer column - 2
+    int *g = gout + (ptrdiff_t)(Y0 - 2)*pd.w + (X0 - 2);
+#pragma unroll 1
+    for (int b = b0 + warp; b < b1; b += kRegWarps) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        int c = 2*(lane + 32*k);
+        if (c >= c0 && c < c1) {
+          *reinterpret_cast<int2 *>(g + (ptrdiff_t)b*pd.w + c) =
+              *reinterpret_cast<int2 *>(s.A + b*kAP + c + 2);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace tdlt

@@ -1,0 +1,460 @@
+// Region kernels: shared geometry, shared-memory layout and the task code the
+// forward and inverse TDLT kernels are assembled from.  sm_100a only.
+//
+// A CTA (8 warps) owns one REGION of one plane of one frame: 128 x 64 samples =
+// 4 x 2 tiles of 32 x 32 = 16 x 8 UNITS of 8 x 8.  All the work of a region is
+// first sorted into lists of equal-shaped tasks, so that every warp instruction
+// runs the same code on 32 busy lanes whatever the block-size map looks like:
+//
+//   lapping    4x4 CELLS centred on the multiples of 4 (tdlt_device.cuh), one
+//              lane per cell, lists by kind: vertical-only, horizontal-only,
+//              crossing (column filter first), crossing (row filter first)
+//   transforms class 0: an 8x8 unit split into four 4x4 blocks  (2 lanes)
+//              class 1: an 8x8 block                            (2 lanes)
+//              class 2: a 16x16 block                           (8 lanes)
+//              class 3: a 32x32 block                           (32 lanes)
+//              every lane always carries 32 samples in registers.
+//
+// Shared memory of a CTA:
+//   B   8 tiles x 4096 B, each in the TMA SWIZZLE_128B pattern (what the tiled
+//       TMA load / store of a 32x32 int32 box produces / consumes)
+//   A   68 rows x 140 words: region rows -2..65, columns -4..135 (one TMA box;
+//       the innermost TMA coordinate must be 16-byte aligned, hence 4 columns
+//       of halo where the lapping needs 2; 140 words = 35 16-byte chunks, an
+//       odd number, so that 8 consecutive rows of one chunk column fall in 8
+//       different bank groups)
+//   unit table, cell lists, task lists, counters.
+#pragma once
+#include "tdlt_device.cuh"
+#include "tdlt_tasks.cuh"
+
+namespace tdlt {
+
+constexpr int kRegW = 128, kRegH = 64;       // region size in samples
+constexpr int kRegTX = 4, kRegTY = 2;        // tiles across / down
+constexpr int kRegTiles = kRegTX*kRegTY;
+constexpr int kRegUX = 16, kRegUY = 8;       // units across / down
+constexpr int kAP = 140;                     // words per row of the region buffer A
+constexpr int kARegRows = kRegH + 4;
+constexpr int kARegBytes = kAP*kARegRows*4;  // 38080, what the TMA load delivers
+constexpr int kRegThreads = 256;
+constexpr int kRegWarps = kRegThreads/32;
+constexpr int kUS = 20;                      // row stride of the unit tables (18 used)
+constexpr int kUTab = kUS*(kRegUY + 2);      // 200 entries: units -1..16 x -1..8
+
+// Shared-memory carve-up (bytes from a 1024-aligned base).
+constexpr int kOffB = 0;
+constexpr int kOffA = kRegTiles*kBBytes;                 // 32768
+constexpr int kOffLs = kOffA + kARegBytes;               // 70848
+constexpr int kOffUb = kOffLs + kUTab;                   // unit edge bits
+constexpr int kOffTasks = kOffUb + kUTab;
+constexpr int kTaskListStride = 128;                     // bytes per class list
+constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints
+constexpr int kOffBar = kOffCnt + 32;
+constexpr int kRegSmemBytes = kOffBar + 16;
+static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0, "alignment");
+static_assert(kRegSmemBytes <= 76800, "three CTAs per SM need <= 75 KB each");
+
+struct RegionPlane {
+  int w, h;          // plane size in samples
+  int dec;           // 0 or 1
+  int nrx, nry;      // regions across / down
+  int reg0;          // index of this plane's first region within a frame
+  float inv_nrx;     // 1 / nrx
+};
+
+struct RegionBatch {
+  RegionPlane pl[kMaxPlanes];
+  int nplanes;
+  int regs_per_frame;
+  int nframes;
+  int pic_w, pic_h;      // LUMA picture size (gates the split filters)
+  int bw, bh;            // block-size map: entries across / down (8x8 luma units)
+  int flags;             // OD_TDLT_KEYFRAME | OD_TDLT_HAAR
+};
+
+struct RegionId {
+  int frame, pli, rx, ry;
+};
+
+// r = region index within its frame.
+__device__ __forceinline__ RegionId decode_region(const RegionBatch &bd, int frame, int r) {
+  RegionId id;
+  id.frame = frame;
+  int p = 0;
+#pragma unroll
+  for (int q = 1; q < kMaxPlanes; q++) {
+    if (q < bd.nplanes && r >= bd.pl[q].reg0) p = q;
+  }
+  id.pli = p;
+  r -= bd.pl[p].reg0;
+  // r / nrx without an integer division (r < 2^16, nrx <= 2^9: the float quotient of
+  // r + 0.5 is never within rounding distance of an integer)
+  id.ry = __float2int_rz((r + 0.5f)*bd.pl[p].inv_nrx);
+  id.rx = r - id.ry*bd.pl[p].nrx;
+  return id;
+}
+
+struct RegionSmem {
+  int *B;
+  int *A;
+  unsigned char *ls;      // leaf log-size per unit, 0xFF outside the plane
+  unsigned char *ub;      // edge bits per unit (kUb*)
+  unsigned char *tasks;   // 4 lists
+  int *cnt;               // [4..7] task classes
+  unsigned long long *bar;
+};
+
+__device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
+  RegionSmem s;
+  s.B = reinterpret_cast<int *>(base + kOffB);
+  s.A = reinterpret_cast<int *>(base + kOffA);
+  s.ls = base + kOffLs;
+  s.ub = base + kOffUb;
+  s.tasks = base + kOffTasks;
+  s.cnt = reinterpret_cast<int *>(base + kOffCnt);
+  s.bar = reinterpret_cast<unsigned long long *>(base + kOffBar);
+  return s;
+}
+
+// Unit-table index of region unit (uy, ux), uy in [-1, 8], ux in [-1, 16].
+__device__ __forceinline__ int ut(int uy, int ux) { return (uy + 1)*kUS + ux + 1; }
+
+// Edge bits of a unit (all zero outside the plane).
+//  kUbTop   the horizontal edge along the unit's top side is filtered
+//  kUbLeft  the vertical edge along its left side is filtered
+//  kUbMidH  the unit is split into 4x4 blocks and its horizontal mid-edge is filtered
+//  kUbMidV  ... and its vertical mid-edge
+constexpr int kUbTop = 1, kUbLeft = 2, kUbMidH = 4, kUbMidV = 8;
+
+// One lane appends `item` to the list `which` (0..3, or -1 for none) of a
+// family of 4 lists; warp-aggregated (one shared-memory atomic per list and call).
+template <typename T>
+__device__ __forceinline__ void list_push4(T *lists, int stride, int *cnt, int which, T item,
+                                           int lane) {
+  unsigned peers = __match_any_sync(0xffffffffu, which);
+  int leader = __ffs(peers) - 1;
+  int base = 0;
+  if (lane == leader && which >= 0) base = atomicAdd(cnt + which, __popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (which >= 0) lists[which*stride + base + __popc(peers & ((1u << lane) - 1))] = item;
+}
+
+// ---------------------------------------------------------------------------
+// Unit tables.  One thread per unit of the 18 x 10 grid around the region:
+//  - leaf size: OD_BLOCK_SIZE4x4 (reference src/block_size.h:32-35), bs =
+//    OD_MAXI(obs, xdec) - xdec (src/encode.c:1297-1301); lossless mode forces
+//    32x32 (src/encode.c:3090);
+//  - which of the unit's edges are filtered: superblock edges always, over the
+//    whole padded plane (src/filter.c:1567-1584); split mid-edges gated by
+//    hfilter / vfilter = the split block's right / bottom side lies inside the
+//    LUMA picture, compared in plane-local coordinates (src/encode.c:1318-1319,
+//    src/filter.c:1494-1508).
+// Returns the leaf size (0xFF outside the plane).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const unsigned char *bsize,
+                                                  const RegionBatch &bd, const RegionPlane &pd,
+                                                  const RegionId &id, int r, int c) {
+  const unsigned char *map = bsize + (size_t)id.frame*bd.bw*bd.bh;
+  int uy = id.ry*kRegUY + r - 1;     // plane unit coordinates
+  int ux = id.rx*kRegUX + c - 1;
+  int L = 0xFF, bits = 0;
+  if (uy >= 0 && ux >= 0 && 8*uy < pd.h && 8*ux < pd.w) {
+    int my = min(uy << pd.dec, bd.bh - 1);
+    int mx = min(ux << pd.dec, bd.bw - 1);
+    L = map[my*bd.bw + mx];
+    L = (bd.flags & 2) ? 3 : L;
+    L = max(L, pd.dec) - pd.dec;
+    if (!(bd.flags & 2)) {
+      int Y = 8*uy, X = 8*ux;
+      int sb = 32 >> pd.dec;
+      int n = 4 << L;
+      if (Y > 0) {
+        bool e;
+        if ((Y & (sb - 1)) == 0) e = true;
+        else if (Y & (n - 1)) e = false;
+        else {
+          int nb = 2*(Y & -Y);
+          e = (X & ~(nb - 1)) + nb <= bd.pic_w;
+        }
+        if (e) bits |= kUbTop;
+      }
+      if (X > 0) {
+        bool e;
+        if ((X & (sb - 1)) == 0) e = true;
+        else if (X & (n - 1)) e = false;
+        else {
+          int nb = 2*(X & -X);
+          e = (Y & ~(nb - 1)) + nb <= bd.pic_h;
+        }
+        if (e) bits |= kUbLeft;
+      }
+      if (L == 0) {
+        if (X + 8 <= bd.pic_w) bits |= kUbMidH;
+        if (Y + 8 <= bd.pic_h) bits |= kUbMidV;
+      }
+    }
+  }
+  s.ls[r*kUS + c] = (unsigned char)L;
+  s.ub[r*kUS + c] = (unsigned char)bits;
+  return L;
+}
+
+// Threads 0..191 (six whole warps): unit tables, and the transforms of the
+// region sorted into the four task lists.
+__device__ __forceinline__ void region_setup_units(const RegionSmem &s, const unsigned char *bsize,
+                                                   const RegionBatch &bd, const RegionPlane &pd,
+                                                   const RegionId &id, int tid, int lane) {
+  if (tid < 192) {
+    int which = -1, item = 0;
+    if (tid < 18*10) {
+      int r = tid/18, c = tid - r*18;
+      int L = region_unit_tables(s, bsize, bd, pd, id, r, c);
+      int UR = r - 1, UC = c - 1;
+      if (UR >= 0 && UR < kRegUY && UC >= 0 && UC < kRegUX && !(bd.flags & 2)) {
+        if (L == 0 || L == 1) which = L;
+        else if (L == 2 && !(UR & 1) && !(UC & 1)) which = 2;
+        else if (L == 3 && !(UR & 3) && !(UC & 3)) which = 3;
+        item = (UR << 4) | UC;
+      }
+    }
+    list_push4(s.tasks, kTaskListStride, s.cnt + 4, which, (unsigned char)item, lane);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Lapping.  The filtered edges of a plane lie on lines at multiples of 4; the
+// LEVEL of a line is the largest power of two dividing its coordinate, capped
+// at the superblock size (multiples of 32 -> the SB edges / 32x32 splits, 16,
+// 8, and 4 = the mid-edges of 8x8 units split into 4x4).  The reference filters
+// level by level, coarse to fine, and inside a level first across all
+// horizontal edges (down the columns), then across all vertical edges
+// (src/filter.c:1493-1508, 1567-1584; recursion src/encode.c:1311-1327); the
+// inverse runs the same sequence backwards.  One phase = one (level, direction):
+//   down the columns:  a task is a 16-byte chunk (4 columns) of one line: 4 rows
+//                      x int4, four filters side by side.  8 consecutive lanes
+//                      read 8 consecutive chunks: no bank conflicts.
+//   along the rows:    a task is one row of one line: the last two words of the
+//                      chunk left of the edge and the first two of the chunk
+//                      right of it.  8 consecutive lanes read 8 consecutive rows
+//                      (35 chunks per row, odd): no bank conflicts.
+// Region lines: rows / columns 0, 8, .., 64 / 128 (levels >= 8) and 4, 12, ..
+// (level 4).  Regions start at multiples of 64 / 128, so the level of a line
+// follows from its region-local coordinate.
+// ---------------------------------------------------------------------------
+// Forward: the region needs its 128 x 64 samples lapped; the lines on its far
+// sides (row 64, column 128) and the halo are recomputed from input samples.
+// Inverse: the region OWNS the cells centred on rows 0..60 and columns 0..124,
+// i.e. output rows -2..61 and columns -2..125 (plus the last two rows / columns
+// of the plane where it ends there).
+template <bool kInverse>
+__device__ __forceinline__ void region_lap_cols(int *A, const unsigned char *ub, int lv, int sb,
+                                                int tid) {
+  const bool top = lv == sb;
+  const int nlines = top ? kRegH/sb + (kInverse ? 0 : 1) : (kRegH/2)/lv;
+  const int first = top ? 0 : lv, step = top ? sb : 2*lv;
+  const int bit = (lv == 4) ? kUbMidH : kUbTop;
+  // chunks per line: forward 0..33 at the superblock level (the halo columns feed
+  // the row filters of that level), 1..32 below it; inverse 0..32
+  const int m0 = kInverse ? 0 : (top ? 0 : 1);
+  const int npl = kInverse ? 33 : (top ? 34 : 32);
+  const int inv = (65536 + npl - 1)/npl;
+  const int ntask = nlines*npl;
+#pragma unroll 1
+  for (int t = tid; t < ntask; t += kRegThreads) {
+    int line = (t*inv) >> 16;
+    int m = m0 + t - line*npl;
+    int yl = first + line*step;
+    if (ub[ut(yl >> 3, (m - 1) >> 1)] & bit) {
+      int4 *p = reinterpret_cast<int4 *>(A + yl*kAP + 4*m);   // buffer row yl = region row yl - 2
+      constexpr int S = kAP/4;
+      int4 r0 = p[0], r1 = p[S], r2 = p[2*S], r3 = p[3*S];
+      if (kInverse) {
+        post4(r0.x, r1.x, r2.x, r3.x); post4(r0.y, r1.y, r2.y, r3.y);
+        post4(r0.z, r1.z, r2.z, r3.z); post4(r0.w, r1.w, r2.w, r3.w);
+      }
+      else {
+        pre4(r0.x, r1.x, r2.x, r3.x); pre4(r0.y, r1.y, r2.y, r3.y);
+        pre4(r0.z, r1.z, r2.z, r3.z); pre4(r0.w, r1.w, r2.w, r3.w);
+      }
+      p[0] = r0; p[S] = r1; p[2*S] = r2; p[3*S] = r3;
+    }
+  }
+}
+
+// A warp takes 32 consecutive rows of one line.  Forward: region rows 0..63.
+// Inverse: region rows -2..61, and 62..63 as well where the plane ends.
+template <bool kInverse>
+__device__ __forceinline__ void region_lap_rows(int *A, const unsigned char *ub, int lv, int sb,
+                                                int warp, int lane, bool last_row) {
+  const bool top = lv == sb;
+  const int nlines = top ? kRegW/sb + (kInverse ? 0 : 1) : (kRegW/2)/lv;
+  const int first = top ? 0 : lv, step = top ? sb : 2*lv;
+  const int bit = (lv == 4) ? kUbMidV : kUbLeft;
+  const int parts = (kInverse && last_row) ? 3 : 2;
+#pragma unroll 1
+  for (int wt = warp; wt < nlines*parts; wt += kRegWarps) {
+    int line = (parts == 2) ? wt >> 1 : wt/3;
+    int part = wt - line*parts;
+    int row = part*32 + lane + (kInverse ? 0 : 2);          // buffer row = region row + 2
+    int xl = first + line*step;
+    if (row < kARegRows - 2 && (ub[ut((row - 2) >> 3, xl >> 3)] & bit)) {
+      int2 *p = reinterpret_cast<int2 *>(A + row*kAP + xl + 2);   // region columns xl-2 .. xl+1
+      int2 lo = p[0], hi = p[1];
+      if (kInverse) post4(lo.x, lo.y, hi.x, hi.y); else pre4(lo.x, lo.y, hi.x, hi.y);
+      p[0] = lo; p[1] = hi;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Transform tasks.  A unit is named by its region unit coordinates (UR, UC),
+// UR in 0..7, UC in 0..15; a task list entry is (UR << 4) | UC.
+//   A side: sample (r, c) of the region at A[(r + 2)*kAP + c + 4]
+//   B side: tile (UR >> 2)*4 + (UC >> 2); inside a tile the byte address of
+//           sample (r, c) is r*128 + (((c >> 2) ^ (r & 7)) << 4) + (c & 3)*4.
+// B addresses are formed as   lane constant XOR compile-time constant   (the
+// tile buffers are 4096-byte aligned), one LOP3 per access.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int *b_ptr(unsigned char *base, unsigned x) {
+  return reinterpret_cast<int *>(base + x);
+}
+
+// -- 8 rows x 4 columns from A: element (r, q) <-> v[8*q + r] ----------------
+__device__ __forceinline__ void ld_a_8x4(const int *a, int *v) {
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    int4 t = *reinterpret_cast<const int4 *>(a + r*kAP);
+    v[r] = t.x; v[8 + r] = t.y; v[16 + r] = t.z; v[24 + r] = t.w;
+  }
+}
+__device__ __forceinline__ void st_a_8x4(int *a, const int *v) {
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    *reinterpret_cast<int4 *>(a + r*kAP) = make_int4(v[r], v[8 + r], v[16 + r], v[24 + r]);
+  }
+}
+
+// -- the same strip on B: unit rows 8*ur + r, chunk 2*uc + h ----------------
+// q = byte address of the tile + ur*1024 + ((2*uc + h) << 4)
+template <bool kStore>
+__device__ __forceinline__ void b_8x4(unsigned char *tile, int ur, int uc, int h, int *v) {
+  unsigned q = (unsigned)(ur*1024) | (unsigned)((2*uc + h) << 4);
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)((r << 7) | (r << 4))));
+    if (kStore) *p = make_int4(v[r], v[8 + r], v[16 + r], v[24 + r]);
+    else { int4 t = *p; v[r] = t.x; v[8 + r] = t.y; v[16 + r] = t.z; v[24 + r] = t.w; }
+  }
+}
+
+// -- rows of an 8x8 block on B: register group a (8 words) holds unit row
+//    2*(a ^ mu) + h, all 8 columns.  mu is a per-lane rotation of the four
+//    independent rows that keeps the 8 lanes of a quarter warp on 8 different
+//    bank groups whatever units they hold.
+template <bool kStore>
+__device__ __forceinline__ void b_rows8(unsigned char *tile, int ur, int uc, int h, int mu,
+                                        int *v) {
+  // row7 = (2a) ^ c1, chunk = (j ^ 2a) ^ c2, with c1 = 2mu | h, c2 = 2uc ^ c1
+  unsigned c1 = (unsigned)(2*mu | h), c2 = (unsigned)(2*uc) ^ c1;
+  unsigned q = (unsigned)(ur*1024) | (c1 << 7) | (c2 << 4);
+#pragma unroll
+  for (int a = 0; a < 4; a++) {
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(((2*a) << 7) | ((j ^ (2*a)) << 4))));
+      int *w = v + 8*a + 4*j;
+      if (kStore) *p = make_int4(w[0], w[1], w[2], w[3]);
+      else { int4 t = *p; w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w; }
+    }
+  }
+}
+
+// -- 16x16 block, 8 lanes: lane k holds columns 2k, 2k+1 (v[r], v[16 + r]) ---
+template <bool kStore>
+__device__ __forceinline__ void a_cols16(int *a, int *v) {   // a -> (row 0, column 2k)
+#pragma unroll
+  for (int r = 0; r < 16; r++) {
+    int2 *p = reinterpret_cast<int2 *>(a + r*kAP);
+    if (kStore) *p = make_int2(v[r], v[16 + r]);
+    else { int2 t = *p; v[r] = t.x; v[16 + r] = t.y; }
+  }
+}
+// r16, c16 in {0, 16}: origin of the block inside its tile
+template <bool kStore>
+__device__ __forceinline__ void b_cols16(unsigned char *tile, int r16, int c16, int k, int *v) {
+  unsigned q = (unsigned)(r16*128) | (unsigned)(((c16 >> 2) + (k >> 1)) << 4) |
+               (unsigned)((k & 1) << 3);
+#pragma unroll
+  for (int r = 0; r < 16; r++) {
+    int2 *p = reinterpret_cast<int2 *>(tile + (q ^ (unsigned)((r << 7) | ((r & 7) << 4))));
+    if (kStore) *p = make_int2(v[r], v[16 + r]);
+    else { int2 t = *p; v[r] = t.x; v[16 + r] = t.y; }
+  }
+}
+// lane k holds rows k and k + 8 (v[0..15], v[16..31])
+template <bool kStore>
+__device__ __forceinline__ void b_rows16(unsigned char *tile, int r16, int c16, int k, int *v) {
+  unsigned q = (unsigned)((r16 + k)*128) | (unsigned)(((c16 >> 2) ^ k) << 4);
+#pragma unroll
+  for (int a = 0; a < 2; a++) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(((8*a) << 7) | (j << 4))));
+      int *w = v + 16*a + 4*j;
+      if (kStore) *p = make_int4(w[0], w[1], w[2], w[3]);
+      else { int4 t = *p; w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w; }
+    }
+  }
+}
+
+// -- 32x32 block, one warp: lane = column, then lane = row -------------------
+template <bool kStore>
+__device__ __forceinline__ void a_col32(int *a, int *v) {     // a -> (row 0, column lane)
+#pragma unroll
+  for (int r = 0; r < 32; r++) {
+    if (kStore) a[r*kAP] = v[r]; else v[r] = a[r*kAP];
+  }
+}
+template <bool kStore>
+__device__ __forceinline__ void b_col32(unsigned char *tile, int lane, int *v) {
+  unsigned q = (unsigned)((lane >> 2) << 4) | (unsigned)((lane & 3) << 2);
+#pragma unroll
+  for (int r = 0; r < 32; r++) {
+    int *p = reinterpret_cast<int *>(tile + (q ^ (unsigned)((r << 7) | ((r & 7) << 4))));
+    if (kStore) *p = v[r]; else v[r] = *p;
+  }
+}
+template <bool kStore>
+__device__ __forceinline__ void b_row32(unsigned char *tile, int lane, int *v) {
+  unsigned q = (unsigned)(lane << 7) | (unsigned)((lane & 7) << 4);
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(j << 4)));
+    if (kStore) *p = make_int4(v[4*j], v[4*j + 1], v[4*j + 2], v[4*j + 3]);
+    else { int4 t = *p; v[4*j] = t.x; v[4*j + 1] = t.y; v[4*j + 2] = t.z; v[4*j + 3] = t.w; }
+  }
+}
+
+// ---- keyframe DC pyramid on one tile (reference src/encode.c:1328-1341,
+// src/decode.c:733).  ls0 -> unit table entry of the tile's first unit.
+template <bool kInverse>
+__device__ __forceinline__ void region_dc_level(int *Bt, const unsigned char *ls0, int lane,
+                                                int n) {
+  int per = 32/n;
+  if (lane < per*per) {
+    int r0 = (lane/per)*n, c0 = (lane%per)*n;
+    int lsz = ls0[(r0 >> 3)*kUS + (c0 >> 3)];
+    if ((4 << lsz) < n) {
+      int hn = n >> 1;
+      int o0 = b_off(r0, c0), o1 = b_off(r0, c0 + hn);
+      int o2 = b_off(r0 + hn, c0), o3 = b_off(r0 + hn, c0 + hn);
+      int x0 = Bt[o0], x1 = Bt[o1], x2 = Bt[o2], x3 = Bt[o3];
+      if (kInverse) haar2x2(x0, x1, x2, x3); else haar2x2(x0, x2, x1, x3);
+      Bt[o0] = x0; Bt[o1] = x1; Bt[o2] = x2; Bt[o3] = x3;
+    }
+  }
+  __syncwarp();
+}
+
+}  // namespace tdlt

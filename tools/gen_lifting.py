@@ -430,7 +430,12 @@ def run_inverse(p, y):
 # --------------------------------------------------------------------------
 # Emitters
 # --------------------------------------------------------------------------
-def _c_step(op, d, s, k, sh, half="tdlt_half"):
+def _c_step(op, d, s, k, sh, half="tdlt_half", cuda=False):
+    if cuda and op == LSUB:
+        # d - ((s*K + R) >> S) == d + ((s*-K + R - 1) >> S) for R = 2^(S-1)
+        # (-(x >> S) == (-x + 2^S - 1) >> S): one IMAD + one LEA.HI.SX32 instead
+        # of IMAD + SHF + IADD.
+        return "%s += (%s*%d + %d) >> %d;" % (d, s, -k, (1 << (sh - 1)) - 1, sh)
     if op == ADD: return "%s += %s;" % (d, s)
     if op == SUB: return "%s -= %s;" % (d, s)
     if op == RSUB: return "%s = %s - %s;" % (d, s, d)
@@ -479,14 +484,14 @@ def emit_cuda(progs):
                 for k, r in enumerate(p.in_regs):
                     out.append("  int %s = v[%d];\n" % (r, k))
                 for st in p.steps:
-                    out.append("  " + _c_step(*st) + "\n")
+                    out.append("  " + _c_step(*st, cuda=True) + "\n")
                 for i, r in enumerate(names):
                     out.append("  v[%d] = %s;\n" % (i, r))
             else:
                 for i, r in enumerate(names):
                     out.append("  int %s = v[%d];\n" % (r, i))
                 for op, d, s, k, sh in reversed(p.steps):
-                    out.append("  " + _c_step(INVERSE[op], d, s, k, sh) + "\n")
+                    out.append("  " + _c_step(INVERSE[op], d, s, k, sh, cuda=True) + "\n")
                 for k, r in enumerate(p.in_regs):
                     out.append("  v[%d] = %s;\n" % (k, r))
             out.append("}\n\n")
