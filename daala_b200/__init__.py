@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdaala_tdlt_cuda.so")
+LIB_PATH = os.environ.get("DAALA_TDLT_LIB", os.path.join(_HERE, "libdaala_tdlt_cuda.so"))
 
 OD_TDLT_KEYFRAME = 1
 OD_TDLT_HAAR = 2

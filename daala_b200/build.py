@@ -21,7 +21,11 @@ def _stale():
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, trace=False):
+    """trace=True builds libdaala_tdlt_cuda_trace.so with -DTDLT_TRACE -rdc (phase
+    timestamps for tools/trace_phases.py); never used by tests or bench."""
+    if trace:
+        return _build_trace()
     if not force and not _stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -44,5 +48,17 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def _build_trace():
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    lib = os.path.join(HERE, "libdaala_tdlt_cuda_trace.so")
+    cmd = [nvcc] + NVCC_FLAGS + ["-DTDLT_TRACE", "-rdc=true", "-shared", "-o", lib] + \
+          [os.path.join(CSRC, f) for f in SOURCES] + ["-lcudart"]
+    subprocess.check_call(cmd)
+    return lib
+
+
 if __name__ == "__main__":
+    if "--trace" in sys.argv:
+        print(build(trace=True))
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -26,8 +26,7 @@ struct od_tdlt_ctx {
   RegionBatch rb;               // the same for the region kernels
   long long plane_size[kMaxPlanes];
   // strip exchange of the inverse kernel
-  int *strips;
-  int *flags;
+  int2 *strips;                 // (sample, epoch) pairs, kRegionStripInts per region
   int *ticket;
   long long scratch_tiles;
   int epoch;
@@ -201,7 +200,6 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   }
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->strips);
-  cudaFree(ctx->flags);
   cudaFree(ctx->ticket);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   free(ctx);
@@ -217,6 +215,11 @@ long long od_tdlt_plane_size(const od_tdlt_ctx *ctx, int pli) {
 long long od_tdlt_bsize_size(const od_tdlt_ctx *ctx) { return (long long)ctx->bd.bw*ctx->bd.bh; }
 const char *od_tdlt_last_error(const od_tdlt_ctx *ctx) { return ctx ? ctx->err : "null context"; }
 long long od_tdlt_launch_count(void) { return g_launches.load(); }
+#ifdef TDLT_TRACE
+int od_tdlt_debug_set_trace(long long *dev_buf) {
+  return cudaMemcpyToSymbol(tdlt::g_tdlt_trace, &dev_buf, sizeof(dev_buf)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 // ---------------------------------------------------------------- batches --
 int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
@@ -247,13 +250,11 @@ static int ensure_scratch(od_tdlt_ctx *ctx, long long tiles) {
   if (tiles <= ctx->scratch_tiles) return OD_TDLT_SUCCESS;
   CK(ctx, cudaDeviceSynchronize());
   cudaFree(ctx->strips);
-  cudaFree(ctx->flags);
   ctx->strips = nullptr;
-  ctx->flags = nullptr;
   ctx->scratch_tiles = 0;
-  CK(ctx, cudaMalloc(&ctx->strips, (size_t)tiles*kRegionStripInts*sizeof(int)));
-  CK(ctx, cudaMalloc(&ctx->flags, (size_t)tiles*sizeof(int)));
-  CK(ctx, cudaMemset(ctx->flags, 0, (size_t)tiles*sizeof(int)));
+  size_t bytes = (size_t)tiles*kRegionStripInts*sizeof(int2);
+  CK(ctx, cudaMalloc(&ctx->strips, bytes));
+  CK(ctx, cudaMemset(ctx->strips, 0, bytes));    // epoch 0 = nothing published yet
   ctx->scratch_tiles = tiles;
   ctx->epoch = 0;
   return OD_TDLT_SUCCESS;
@@ -283,7 +284,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
   tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      maps, rb, bsize, out, ctx->strips, ctx->flags, ctx->ticket, ctx->epoch);
+      maps, rb, bsize, out, ctx->strips, ctx->ticket, ctx->epoch);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

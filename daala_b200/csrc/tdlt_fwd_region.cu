@@ -12,6 +12,10 @@
 
 namespace tdlt {
 
+#ifdef TDLT_TRACE
+__device__ long long *g_tdlt_trace = nullptr;
+#endif
+
 // ---- lossless mode: multi-level Haar wavelet of each superblock of a tile
 // (reference src/dct.c:1960-1997).  T = the tile's part of A, Y = its B tile.
 __device__ __forceinline__ void region_haar_fwd_tile(int *At, int *Bt, int lane, int sb) {
@@ -60,6 +64,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ bsize) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 0);
   const RegionSmem s = carve_region(smem);
   const RegionId id = decode_region(bd, blockIdx.y, blockIdx.x);
   const RegionPlane &pd = bd.pl[id.pli];
@@ -76,21 +81,24 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   __syncthreads();
   region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
+  TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 1);
   mbar_wait(s.bar, 0);
+  TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 2);
 
   if (!haar) {
-    // ---- lapping, level by level, coarse to fine --------------------------
+    // ---- lapping, level by level, coarse to fine (level 4 is done in registers
+    // by the transform tasks of the units it concerns) ---------------------------
     {
       const int sb = 32 >> pd.dec;
 #pragma unroll 1
-      for (int lv = sb; lv >= 4; lv >>= 1) {
-        region_lap_cols<false>(s.A, s.ub, lv, sb, tid);
+      for (int lv = sb; lv >= 8; lv >>= 1) {
+        region_lap_cols<false>(s.A, s.ub, lv, sb, warp, lane);
         __syncthreads();
         region_lap_rows<false>(s.A, s.ub, lv, sb, warp, lane, false);
         __syncthreads();
       }
     }
-
+    TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 4);
     // ---- transforms ---------------------------------------------------------
     {
       const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
@@ -99,7 +107,12 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       unsigned char *Bb = reinterpret_cast<unsigned char *>(s.B);
       int v[32];
 #pragma unroll 1
-      for (int g = warp; g < ntask; g += kRegWarps) {
+      for (;;) {
+        // longest tasks first; a warp that is done draws the next one
+        int g = 0;
+        if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ntask) break;
         if (g < n3) {
           // 32x32: lane = column, then lane = row
           int e = s.tasks[3*kTaskListStride + g];
@@ -159,13 +172,17 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
           }
         }
         else {
-          // 8x8 unit of four 4x4 blocks: each lane holds two stacked blocks
+          // 8x8 unit of four 4x4 blocks: each lane holds two stacked blocks; the
+          // unit's own mid-edges are lapped here, in registers
           int idx = (g - n3 - q2 - q1)*16 + (lane >> 1), h = lane & 1;
-          if (idx < n0) {
-            int e = s.tasks[idx];
-            int UR = e >> 4, UC = e & 15;
-            unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
-            ld_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+          bool on = idx < n0;
+          int e = s.tasks[on ? idx : 0];
+          int UR = e >> 4, UC = e & 15;
+          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+          int bits = on ? s.ub[ut(UR, UC)] : 0;
+          if (on) ld_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+          lap4_unit<false>(v, h, bits);
+          if (on) {
             fdct4x4_pair(v);
             b_8x4<true>(tile, UR & 3, UC & 3, h, v);
           }
@@ -174,6 +191,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
     }
     fence_proxy_async_smem();   // B is read by the TMA store (async proxy) below
     __syncthreads();
+    TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 5);
   }
 
   // ---- per tile: DC pyramid (or the Haar wavelet), then one TMA store ------
@@ -199,6 +217,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       }
     }
   }
+  TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 6);
 }
 
 }  // namespace tdlt

@@ -9,11 +9,13 @@
 // rectangle shifted by (-2, -2) -- plane rows Y0-2..Y0+61, columns
 // X0-2..X0+125, a whole number of lapping cells -- and needs the two bottom
 // rows / right columns of raw iDCT output of its upper / left / upper-left
-// neighbours.  Every region publishes those strips (1.5 KB) to global memory
-// and raises a flag; consumers wait on the flags of regions that precede them
-// in a TICKET order (CTAs draw tickets in the order they start running, so a
-// region only ever waits on work that is already resident: no deadlock, and on
-// average the producer is ahead because it started first).
+// neighbours.  Every region publishes those strips to global memory as 8-byte
+// (sample, epoch) pairs -- an aligned 8-byte store is indivisible, so a reader
+// that sees the epoch of this launch has the sample too: no flag, no fence --
+// and consumers poll the pairs of regions that precede them in a TICKET order
+// (CTAs draw tickets in the order they start running, so a region only ever
+// waits on work that is already resident: no deadlock, and on average the
+// producer is ahead because it started first).
 #include <cuda.h>
 #include "tdlt_tasks.cuh"
 #include "tdlt_region.cuh"
@@ -23,13 +25,13 @@ namespace tdlt {
 
 constexpr int kStripInts = 2*kRegW + 2*kRegH;   // bottom rows 62, 63; right columns 126, 127
 
-__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ int2 ld_pair(const int2 *p) {
+  int2 v;
+  asm volatile("ld.volatile.global.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_gpu(int *p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_pair(int2 *p, int sample, int epoch) {
+  asm volatile("st.volatile.global.v2.s32 [%0], {%1, %2};" :: "l"(p), "r"(sample), "r"(epoch) : "memory");
 }
 
 // ---- lossless mode: inverse multi-level Haar wavelet of each superblock of a
@@ -75,19 +77,58 @@ __device__ __forceinline__ void region_haar_inv_tile(int *At, int *Bt, int lane,
   }
 }
 
+// The two samples of the ring this thread is responsible for (threads 0..193):
+// src -> two (sample, epoch) pairs of a neighbour's strip, dst -> their place in A.
+struct RingSlot {
+  const int2 *src;
+  int2 *dst;
+  bool need;
+};
+__device__ __forceinline__ RingSlot ring_slot(int *A, const int2 *strips, int t, int nrx,
+                                              bool has_l, bool has_u, int tid) {
+  RingSlot r;
+  r.src = nullptr; r.dst = nullptr; r.need = false;
+  if (tid < 128) {                    // rows -2, -1 <- bottom rows of the region above
+    int a = tid >> 6, c = 2*(tid & 63);
+    r.src = strips + (size_t)(t - nrx)*kStripInts + a*kRegW + c;
+    r.dst = reinterpret_cast<int2 *>(A + a*kAP + c + 4);
+    r.need = has_u;
+  }
+  else if (tid < 192) {               // columns -2, -1 <- right columns of the left region
+    int row = tid - 128;
+    r.src = strips + (size_t)(t - 1)*kStripInts + 2*kRegW + 2*row;
+    r.dst = reinterpret_cast<int2 *>(A + (row + 2)*kAP + 2);
+    r.need = has_l;
+  }
+  else if (tid < 194) {               // the corner
+    int a = tid - 192;
+    r.src = strips + (size_t)(t - nrx - 1)*kStripInts + a*kRegW + 126;
+    r.dst = reinterpret_cast<int2 *>(A + a*kAP + 2);
+    r.need = has_u && has_l;
+  }
+  return r;
+}
+// One look; true (and the samples stored into A) when both pairs carry this epoch.
+__device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
+  int2 p0 = ld_pair(r.src), p1 = ld_pair(r.src + 1);
+  bool ok = p0.y == epoch && p1.y == epoch;
+  if (ok) *r.dst = make_int2(p0.x, p1.x);
+  return ok;
+}
+
 __global__ void __launch_bounds__(kRegThreads, 3)
 tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ bsize, InvOut out,
-                       int *__restrict__ strips, int *__restrict__ flags,
-                       int *__restrict__ ticket, int epoch) {
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
   if (tid == 0) s.cnt[0] = atomicAdd(ticket, 1);
-  if (tid >= 252) s.cnt[tid - 248] = 0;
+  if (tid >= 249) s.cnt[tid - 248] = 0;
   __syncthreads();
   const int t = s.cnt[0];
+  TDLT_MARK(t, 0);
   const int frame = t / bd.regs_per_frame;
   const RegionId id = decode_region(bd, frame, t - frame*bd.regs_per_frame);
   const RegionPlane &pd = bd.pl[id.pli];
@@ -110,9 +151,22 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       }
     }
   }
+  // ---- the ring of raw samples from the regions above / left / above-left: one
+  // int2 per thread.  The regions above finished long ago as a rule: their part is
+  // fetched now, into the halo of A (nothing else writes there); what is not
+  // there yet (the left neighbour, which started just before this region) is
+  // waited for after the transforms.
+  bool ring_done;
+  {
+    RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
+    ring_done = !rs.need;
+    if (rs.need && (tid < 128 || tid >= 192)) ring_done = ring_try(rs, epoch);
+  }
   region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
+  TDLT_MARK(t, 1);
   mbar_wait(s.bar, 0);
+  TDLT_MARK(t, 2);
 
   int *gout = out.c[id.pli] + (size_t)id.frame*pd.w*pd.h;
   const int tx = warp & 3, ty = warp >> 2;
@@ -139,6 +193,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     region_dc_level<true>(Bt, ls0, lane, 8);
   }
   __syncthreads();
+  TDLT_MARK(t, 3);
 
   // ---- inverse transforms: rows first, then columns (src/dct.c:144-149) --------
   {
@@ -148,7 +203,12 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     unsigned char *Bb = reinterpret_cast<unsigned char *>(s.B);
     int v[32];
 #pragma unroll 1
-    for (int g = warp; g < ntask; g += kRegWarps) {
+    for (;;) {
+      // longest tasks first; a warp that is done draws the next one
+      int g = 0;
+      if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
+      g = __shfl_sync(0xffffffffu, g, 0);
+      if (g >= ntask) break;
       if (g < n3) {
         int e = s.tasks[3*kTaskListStride + g];
         int UR = e >> 4, UC = e & 15;
@@ -205,105 +265,92 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
         }
       }
       else {
+        // 4x4 blocks: inverse transforms, then the unit's own mid-edges un-lapped
+        // in registers
         int idx = (g - n3 - q2 - q1)*16 + (lane >> 1), h = lane & 1;
-        if (idx < n0) {
-          int e = s.tasks[idx];
-          int UR = e >> 4, UC = e & 15;
-          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        bool on = idx < n0;
+        int e = s.tasks[on ? idx : 0];
+        int UR = e >> 4, UC = e & 15;
+        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        int bits = on ? s.ub[ut(UR, UC)] : 0;
+        if (on) {
           b_8x4<false>(tile, UR & 3, UC & 3, h, v);
           idct4x4_pair(v);
-          st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
         }
+        lap4_unit<true>(v, h, bits);
+        if (on) st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
       }
     }
   }
   __syncthreads();
+  TDLT_MARK(t, 4);
 
   // ---- publish my bottom rows / right columns (raw iDCT output) ---------------
-  {
-    int *mine = strips + (size_t)t*kStripInts;
-    if (tid < 128) {          // rows 62, 63: 2 x 128 words as 128 int2
+  if (tid < 192) {
+    int2 *mine = strips + (size_t)t*kStripInts;
+    int2 val;
+    int at;
+    if (tid < 128) {          // rows 62, 63: 2 x 128 samples
       int a = tid >> 6, c = 2*(tid & 63);
-      *reinterpret_cast<int2 *>(mine + a*kRegW + c) =
-          *reinterpret_cast<int2 *>(s.A + (62 + a + 2)*kAP + c + 4);
+      val = *reinterpret_cast<int2 *>(s.A + (62 + a + 2)*kAP + c + 4);
+      at = a*kRegW + c;
     }
-    else if (tid < 192) {     // columns 126, 127 of rows 0..63
+    else {                    // columns 126, 127 of rows 0..63
       int r = tid - 128;
-      *reinterpret_cast<int2 *>(mine + 2*kRegW + 2*r) =
-          *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 126 + 4);
+      val = *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 126 + 4);
+      at = 2*kRegW + 2*r;
     }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) st_release_gpu(flags + t, epoch);
+    st_pair(mine + at, val.x, epoch);
+    st_pair(mine + at + 1, val.y, epoch);
   }
+  TDLT_MARK(t, 5);
 
-  // ---- fetch the ring from the regions above / left / above-left ---------------
-  {
-    const bool has_l = id.rx > 0, has_u = id.ry > 0;
-    if (tid < 3) {
-      int nb = (tid == 0) ? t - 1 : (tid == 1) ? t - pd.nrx : t - pd.nrx - 1;
-      bool need = (tid == 0) ? has_l : (tid == 1) ? has_u : (has_l && has_u);
-      if (need) {
-        while (ld_acquire_gpu(flags + nb) != epoch) __nanosleep(64);
-      }
-    }
-    __syncthreads();
-    if (tid < 128) {
-      if (has_u) {
-        const int *up = strips + (size_t)(t - pd.nrx)*kStripInts;
-        int a = tid >> 6, c = 2*(tid & 63);
-        int2 val = __ldcg(reinterpret_cast<const int2 *>(up + a*kRegW + c));
-        *reinterpret_cast<int2 *>(s.A + a*kAP + c + 4) = val;
-      }
-    }
-    else if (tid < 192) {
-      if (has_l) {
-        const int *left = strips + (size_t)(t - 1)*kStripInts;
-        int r = tid - 128;
-        int2 val = __ldcg(reinterpret_cast<const int2 *>(left + 2*kRegW + 2*r));
-        *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 2) = val;
-      }
-    }
-    else if (tid < 194) {
-      if (has_u && has_l) {
-        const int *ul = strips + (size_t)(t - pd.nrx - 1)*kStripInts;
-        int a = tid - 192;
-        int2 val = __ldcg(reinterpret_cast<const int2 *>(ul + a*kRegW + 126));
-        *reinterpret_cast<int2 *>(s.A + a*kAP + 2) = val;
-      }
-    }
-    __syncthreads();
+  // ---- the ring: whatever was not there yet when the region started --------------
+  if (!ring_done) {
+    RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
+    while (!ring_try(rs, epoch)) __nanosleep(20);
   }
+  __syncthreads();      // the ring is in A, and the strips were read before anyone laps them
+  TDLT_MARK(t, 6);
 
   // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
 #pragma unroll 1
-  for (int lv = 4; lv <= sb; lv <<= 1) {
+  for (int lv = 8; lv <= sb; lv <<= 1) {
     region_lap_rows<true>(s.A, s.ub, lv, sb, warp, lane, last_r);
     __syncthreads();
-    region_lap_cols<true>(s.A, s.ub, lv, sb, tid);
+    region_lap_cols<true>(s.A, s.ub, lv, sb, warp, lane);
     __syncthreads();
   }
-
+  TDLT_MARK(t, 7);
   // ---- store the owned rectangle: buffer row b <-> plane row Y0 - 2 + b ---------
+  // Region columns 0.. go out as 16-byte vectors (they are 16-byte aligned in
+  // the plane and in A); the two columns left of the region and, where the
+  // rectangle ends at column 125, the two after column 123 as 8-byte vectors.
   {
     const int b0 = (id.ry == 0) ? 2 : 0;
     const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
-    const int c0 = (id.rx == 0) ? 2 : 0;                                  // in int2 units of
-    const int c1 = last_c ? min(kRegW, pd.w - X0) + 2 : kRegW;            // buffer column - 2
-    int *g = gout + (ptrdiff_t)(Y0 - 2)*pd.w + (X0 - 2);
-#pragma unroll 1
+    const int q1 = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;   // end of the owned columns
+    const int nq = q1 >> 2;
+    // second instruction: lane 0 = columns -2, -1; lane 1 = columns 4*nq, 4*nq + 1
+    const bool side = (lane == 0 && id.rx > 0) || (lane == 1 && (q1 & 2));
+    const int scol = (lane == 0) ? -2 : 4*nq;
+    const size_t pitch = (size_t)pd.w;
+    int *grow = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pitch + X0;
+    const int *arow = s.A + (b0 + warp)*kAP + 4;
+#pragma unroll 2
     for (int b = b0 + warp; b < b1; b += kRegWarps) {
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        int c = 2*(lane + 32*k);
-        if (c >= c0 && c < c1) {
-          *reinterpret_cast<int2 *>(g + (ptrdiff_t)b*pd.w + c) =
-              *reinterpret_cast<int2 *>(s.A + b*kAP + c + 2);
-        }
+      if (lane < nq) {
+        *reinterpret_cast<int4 *>(grow + 4*lane) = *reinterpret_cast<const int4 *>(arow + 4*lane);
       }
+      if (side) {
+        *reinterpret_cast<int2 *>(grow + scol) = *reinterpret_cast<const int2 *>(arow + scol);
+      }
+      grow += kRegWarps*pitch;
+      arow += kRegWarps*kAP;
     }
   }
+  TDLT_MARK(t, 8);
 }
 
 }  // namespace tdlt

@@ -33,8 +33,8 @@ __global__ void tdlt_inv_kernel(const __grid_constant__ TmapSet maps,
 __global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ bsize, InvOut out,
-                                       int *__restrict__ strips, int *__restrict__ flags,
-                                       int *__restrict__ ticket, int epoch);
+                                       int2 *__restrict__ strips, int *__restrict__ ticket,
+                                       int epoch);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;
 
 }  // namespace tdlt

@@ -30,6 +30,17 @@
 
 namespace tdlt {
 
+// Phase timestamps for tools/trace_phases.py (debug builds only: -DTDLT_TRACE).
+#ifdef TDLT_TRACE
+extern __device__ long long *g_tdlt_trace;
+#define TDLT_MARK(cta, k) \
+  do { \
+    if (threadIdx.x == 0 && g_tdlt_trace && (cta) < 4096) g_tdlt_trace[(cta)*16 + (k)] = clock64(); \
+  } while (0)
+#else
+#define TDLT_MARK(cta, k) do { } while (0)
+#endif
+
 constexpr int kRegW = 128, kRegH = 64;       // region size in samples
 constexpr int kRegTX = 4, kRegTY = 2;        // tiles across / down
 constexpr int kRegTiles = kRegTX*kRegTY;
@@ -247,63 +258,141 @@ __device__ __forceinline__ void region_setup_units(const RegionSmem &s, const un
 // Inverse: the region OWNS the cells centred on rows 0..60 and columns 0..124,
 // i.e. output rows -2..61 and columns -2..125 (plus the last two rows / columns
 // of the plane where it ends there).
+// Level 4 (the mid-edges of units split into 4x4 blocks) never leaves its unit
+// and is filtered in registers by the transform task of that unit (lap4_unit
+// below), so the phases here run over the levels 8 .. superblock only.
+template <bool kInverse>
+__device__ __forceinline__ void lap_chunk(int *A, int yl, int m) {
+  int4 *p = reinterpret_cast<int4 *>(A + yl*kAP + 4*m);   // buffer row yl = region row yl - 2
+  constexpr int S = kAP/4;
+  int4 r0 = p[0], r1 = p[S], r2 = p[2*S], r3 = p[3*S];
+  if (kInverse) {
+    post4(r0.x, r1.x, r2.x, r3.x); post4(r0.y, r1.y, r2.y, r3.y);
+    post4(r0.z, r1.z, r2.z, r3.z); post4(r0.w, r1.w, r2.w, r3.w);
+  }
+  else {
+    pre4(r0.x, r1.x, r2.x, r3.x); pre4(r0.y, r1.y, r2.y, r3.y);
+    pre4(r0.z, r1.z, r2.z, r3.z); pre4(r0.w, r1.w, r2.w, r3.w);
+  }
+  p[0] = r0; p[S] = r1; p[2*S] = r2; p[3*S] = r3;
+}
+
+// Block-wide phases: one (level, direction) at a time, a barrier between phases.
+// Columns: a warp takes one line, lane = chunk 1 + lane (region columns 4*lane
+// ..).  The chunks outside 1..32 (0: the two columns left of the region; 33:
+// forward, superblock level, the two right of it) go to one extra partial warp
+// task.
 template <bool kInverse>
 __device__ __forceinline__ void region_lap_cols(int *A, const unsigned char *ub, int lv, int sb,
-                                                int tid) {
+                                                int warp, int lane) {
   const bool top = lv == sb;
   const int nlines = top ? kRegH/sb + (kInverse ? 0 : 1) : (kRegH/2)/lv;
   const int first = top ? 0 : lv, step = top ? sb : 2*lv;
-  const int bit = (lv == 4) ? kUbMidH : kUbTop;
-  // chunks per line: forward 0..33 at the superblock level (the halo columns feed
-  // the row filters of that level), 1..32 below it; inverse 0..32
-  const int m0 = kInverse ? 0 : (top ? 0 : 1);
-  const int npl = kInverse ? 33 : (top ? 34 : 32);
-  const int inv = (65536 + npl - 1)/npl;
-  const int ntask = nlines*npl;
+  const int nextra = kInverse ? 1 : (top ? 2 : 0);         // extra chunks per line
 #pragma unroll 1
-  for (int t = tid; t < ntask; t += kRegThreads) {
-    int line = (t*inv) >> 16;
-    int m = m0 + t - line*npl;
+  for (int wt = warp; wt < nlines + (nextra ? 1 : 0); wt += kRegWarps) {
+    int line, m;
+    bool on;
+    if (wt < nlines) { line = wt; m = lane + 1; on = true; }
+    else { line = lane >> 1; m = (lane & 1) ? 33 : 0; on = lane < 2*nlines && (lane & 1) < nextra; }
     int yl = first + line*step;
-    if (ub[ut(yl >> 3, (m - 1) >> 1)] & bit) {
-      int4 *p = reinterpret_cast<int4 *>(A + yl*kAP + 4*m);   // buffer row yl = region row yl - 2
-      constexpr int S = kAP/4;
-      int4 r0 = p[0], r1 = p[S], r2 = p[2*S], r3 = p[3*S];
-      if (kInverse) {
-        post4(r0.x, r1.x, r2.x, r3.x); post4(r0.y, r1.y, r2.y, r3.y);
-        post4(r0.z, r1.z, r2.z, r3.z); post4(r0.w, r1.w, r2.w, r3.w);
-      }
-      else {
-        pre4(r0.x, r1.x, r2.x, r3.x); pre4(r0.y, r1.y, r2.y, r3.y);
-        pre4(r0.z, r1.z, r2.z, r3.z); pre4(r0.w, r1.w, r2.w, r3.w);
-      }
-      p[0] = r0; p[S] = r1; p[2*S] = r2; p[3*S] = r3;
-    }
+    if (on && (ub[ut(yl >> 3, (m - 1) >> 1)] & kUbTop)) lap_chunk<kInverse>(A, yl, m);
   }
 }
 
-// A warp takes 32 consecutive rows of one line.  Forward: region rows 0..63.
-// Inverse: region rows -2..61, and 62..63 as well where the plane ends.
+// Rows: a warp takes 32 consecutive rows of TWO lines (two independent filter
+// chains per lane).  Forward: region rows 0..63.  Inverse: region rows -2..61,
+// and 62..63 as well where the plane ends.
 template <bool kInverse>
 __device__ __forceinline__ void region_lap_rows(int *A, const unsigned char *ub, int lv, int sb,
                                                 int warp, int lane, bool last_row) {
   const bool top = lv == sb;
   const int nlines = top ? kRegW/sb + (kInverse ? 0 : 1) : (kRegW/2)/lv;
   const int first = top ? 0 : lv, step = top ? sb : 2*lv;
-  const int bit = (lv == 4) ? kUbMidV : kUbLeft;
   const int parts = (kInverse && last_row) ? 3 : 2;
+  const int npairs = (nlines + 1) >> 1;
 #pragma unroll 1
-  for (int wt = warp; wt < nlines*parts; wt += kRegWarps) {
-    int line = (parts == 2) ? wt >> 1 : wt/3;
-    int part = wt - line*parts;
+  for (int wt = warp; wt < npairs*parts; wt += kRegWarps) {
+    int pr = (parts == 2) ? wt >> 1 : wt/3;
+    int part = wt - pr*parts;
     int row = part*32 + lane + (kInverse ? 0 : 2);          // buffer row = region row + 2
-    int xl = first + line*step;
-    if (row < kARegRows - 2 && (ub[ut((row - 2) >> 3, xl >> 3)] & bit)) {
-      int2 *p = reinterpret_cast<int2 *>(A + row*kAP + xl + 2);   // region columns xl-2 .. xl+1
-      int2 lo = p[0], hi = p[1];
-      if (kInverse) post4(lo.x, lo.y, hi.x, hi.y); else pre4(lo.x, lo.y, hi.x, hi.y);
-      p[0] = lo; p[1] = hi;
+    int xa = first + 2*pr*step, xb = xa + step;
+    const unsigned char *u = ub + ut((row - 2) >> 3, 0);
+    bool rok = row < kARegRows - 2;
+    bool ona = rok && (u[xa >> 3] & kUbLeft);
+    bool onb = rok && 2*pr + 1 < nlines && (u[xb >> 3] & kUbLeft);
+    int2 *pa = reinterpret_cast<int2 *>(A + row*kAP + xa + 2);   // region columns xa-2 .. xa+1
+    int2 *pb = reinterpret_cast<int2 *>(A + row*kAP + xb + 2);
+    int2 la, ha, lb, hb;
+    if (ona) { la = pa[0]; ha = pa[1]; }
+    if (onb) { lb = pb[0]; hb = pb[1]; }
+    if (ona) {
+      if (kInverse) post4(la.x, la.y, ha.x, ha.y); else pre4(la.x, la.y, ha.x, ha.y);
     }
+    if (onb) {
+      if (kInverse) post4(lb.x, lb.y, hb.x, hb.y); else pre4(lb.x, lb.y, hb.x, hb.y);
+    }
+    if (ona) { pa[0] = la; pa[1] = ha; }
+    if (onb) { pb[0] = lb; pb[1] = hb; }
+  }
+}
+
+// Level 4, in registers.  The two lanes of a unit hold it as v[8*q + r] = sample
+// (row r, column 4*h + q).  The filter across the horizontal mid-edge (rows
+// 2..5 of every column) is local; the one across the vertical mid-edge (columns
+// 2..5 of every row) needs the neighbour lane's two adjacent columns: lane 0
+// filters rows 0..3, lane 1 rows 4..7, and the halves travel by shuffle.
+// Forward: columns first, then rows (src/filter.c:1493-1508); inverse: rows,
+// then columns (:1537-1552).
+template <bool kInverse>
+__device__ __forceinline__ void lap4_rows(int *v, int h, unsigned mask) {
+  int ra[4], rb[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    int sa = h ? v[j] : v[20 + j];          // lane 1 sends columns 4, 5 of rows 0..3,
+    int sc = h ? v[8 + j] : v[28 + j];      // lane 0 columns 2, 3 of rows 4..7
+    ra[j] = __shfl_xor_sync(mask, sa, 1);
+    rb[j] = __shfl_xor_sync(mask, sc, 1);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    int x0 = h ? ra[j] : v[16 + j];
+    int x1 = h ? rb[j] : v[24 + j];
+    int x2 = h ? v[4 + j] : ra[j];
+    int x3 = h ? v[12 + j] : rb[j];
+    if (kInverse) post4(x0, x1, x2, x3); else pre4(x0, x1, x2, x3);
+    int ta = h ? x0 : x2, tb = h ? x1 : x3;   // the neighbour's half goes back
+    int ua = __shfl_xor_sync(mask, ta, 1);
+    int uc = __shfl_xor_sync(mask, tb, 1);
+    v[4 + j] = h ? x2 : v[4 + j];
+    v[12 + j] = h ? x3 : v[12 + j];
+    v[16 + j] = h ? v[16 + j] : x0;
+    v[24 + j] = h ? v[24 + j] : x1;
+    v[j] = h ? ua : v[j];
+    v[8 + j] = h ? uc : v[8 + j];
+    v[20 + j] = h ? v[20 + j] : ua;
+    v[28 + j] = h ? v[28 + j] : uc;
+  }
+}
+template <bool kInverse>
+__device__ __forceinline__ void lap4_cols(int *v) {
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    if (kInverse) post4(v[8*q + 2], v[8*q + 3], v[8*q + 4], v[8*q + 5]);
+    else pre4(v[8*q + 2], v[8*q + 3], v[8*q + 4], v[8*q + 5]);
+  }
+}
+// bits: the unit's edge bits (0 on idle lanes).  Called by the whole warp.
+template <bool kInverse>
+__device__ __forceinline__ void lap4_unit(int *v, int h, int bits) {
+  unsigned mask = __ballot_sync(0xffffffffu, (bits & kUbMidV) != 0);
+  if (kInverse) {
+    if (bits & kUbMidV) lap4_rows<true>(v, h, mask);
+    if (bits & kUbMidH) lap4_cols<true>(v);
+  }
+  else {
+    if (bits & kUbMidH) lap4_cols<false>(v);
+    if (bits & kUbMidV) lap4_rows<false>(v, h, mask);
   }
 }
 
