@@ -64,6 +64,8 @@ __device__ __forceinline__ void pre4(int &x0, int &x1, int &x2, int &x3) {
   x3 = t0 - t3;
 }
 
+constexpr int kPostM75 = (int)(3665038760u);   // ceil(2^38/75) - 2^32
+constexpr int kPostM85 = (int)(3233857729u);   // ceil(2^38/85) - 2^32
 __device__ __forceinline__ void post4(int &y0, int &y1, int &y2, int &y3) {
   int t3 = y0 - y3;
   int t2 = y1 - y2;
@@ -71,8 +73,12 @@ __device__ __forceinline__ void post4(int &y0, int &y1, int &y2, int &y3) {
   int t0 = y0 - (t3 >> 1);
   t2 -= (t3*33 + 32) >> 6;
   t3 -= (t2*-15 + 32) >> 6;
-  t3 = (t3*64)/75;   // C division, truncating
-  t2 = (t2*64)/85;
+  // (t*64)/75 and (t*64)/85, C division (truncating), as one multiply-high each:
+  // trunc(t*64/d) = floor(t*M/2^32) + (t < 0) with M = ceil(2^38/d), exact for
+  // |t| < 2^25, the range in which the reference's own t*64 does not overflow
+  // (checked exhaustively on the host, tests/test_lifting_header.py).
+  t3 = __mulhi(t3, kPostM75) + t3 + (int)((unsigned)t3 >> 31);
+  t2 = __mulhi(t2, kPostM85) + t2 + (int)((unsigned)t2 >> 31);
   t0 += t3 >> 1;
   t1 += t2 >> 1;
   y0 = t0;

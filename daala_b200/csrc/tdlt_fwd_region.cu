@@ -77,7 +77,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
     mbar_expect_tx(s.bar, kARegBytes);
     tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
   }
-  if (tid >= 248) s.cnt[tid - 248] = 0;
+  if (tid >= 228) s.cnt[tid - 228] = 0;       // counters and edge masks
   __syncthreads();
   region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
@@ -92,9 +92,9 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       const int sb = 32 >> pd.dec;
 #pragma unroll 1
       for (int lv = sb; lv >= 8; lv >>= 1) {
-        region_lap_cols<false>(s.A, s.ub, lv, sb, warp, lane);
+        region_lap_cols<false>(s.A, s.msk, lv, sb, warp, lane);
         __syncthreads();
-        region_lap_rows<false>(s.A, s.ub, lv, sb, warp, lane, false);
+        region_lap_rows<false>(s.A, s.msk, lv, sb, warp, lane, false);
         __syncthreads();
       }
     }

@@ -125,7 +125,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
   if (tid == 0) s.cnt[0] = atomicAdd(ticket, 1);
-  if (tid >= 249) s.cnt[tid - 248] = 0;
+  if (tid >= 229) s.cnt[tid - 228] = 0;       // counters (but the ticket) and edge masks
   __syncthreads();
   const int t = s.cnt[0];
   TDLT_MARK(t, 0);
@@ -317,9 +317,9 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
 #pragma unroll 1
   for (int lv = 8; lv <= sb; lv <<= 1) {
-    region_lap_rows<true>(s.A, s.ub, lv, sb, warp, lane, last_r);
+    region_lap_rows<true>(s.A, s.msk, lv, sb, warp, lane, last_r);
     __syncthreads();
-    region_lap_cols<true>(s.A, s.ub, lv, sb, warp, lane);
+    region_lap_cols<true>(s.A, s.msk, lv, sb, warp, lane);
     __syncthreads();
   }
   TDLT_MARK(t, 7);
@@ -338,16 +338,21 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     const size_t pitch = (size_t)pd.w;
     int *grow = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pitch + X0;
     const int *arow = s.A + (b0 + warp)*kAP + 4;
-#pragma unroll 2
-    for (int b = b0 + warp; b < b1; b += kRegWarps) {
-      if (lane < nq) {
-        *reinterpret_cast<int4 *>(grow + 4*lane) = *reinterpret_cast<const int4 *>(arow + 4*lane);
+    const bool body = lane < nq;
+    // rows b0 + warp + 8k
+    const int nb = b1 - b0 - warp;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+      if (kRegWarps*k < nb) {
+        const int *ar = arow + k*kRegWarps*kAP;
+        int *gr = grow + (size_t)(k*kRegWarps)*pitch;
+        if (body) {
+          *reinterpret_cast<int4 *>(gr + 4*lane) = *reinterpret_cast<const int4 *>(ar + 4*lane);
+        }
+        if (side) {
+          *reinterpret_cast<int2 *>(gr + scol) = *reinterpret_cast<const int2 *>(ar + scol);
+        }
       }
-      if (side) {
-        *reinterpret_cast<int2 *>(grow + scol) = *reinterpret_cast<const int2 *>(arow + scol);
-      }
-      grow += kRegWarps*pitch;
-      arow += kRegWarps*kAP;
     }
   }
   TDLT_MARK(t, 8);

@@ -61,7 +61,8 @@ constexpr int kOffUb = kOffLs + kUTab;                   // unit edge bits
 constexpr int kOffTasks = kOffUb + kUTab;
 constexpr int kTaskListStride = 128;                     // bytes per class list
 constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints
-constexpr int kOffBar = kOffCnt + 32;
+constexpr int kOffMsk = kOffCnt + 32;                    // 2 x 10 edge masks, right after cnt
+constexpr int kOffBar = kOffMsk + 80;
 constexpr int kRegSmemBytes = kOffBar + 16;
 static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0, "alignment");
 static_assert(kRegSmemBytes <= 76800, "three CTAs per SM need <= 75 KB each");
@@ -113,6 +114,7 @@ struct RegionSmem {
   unsigned char *ub;      // edge bits per unit (kUb*)
   unsigned char *tasks;   // 4 lists
   int *cnt;               // [4..7] task classes
+  unsigned *msk;          // [r]: bit c = unit (r-1, c-1) has kUbTop; [10 + r]: kUbLeft
   unsigned long long *bar;
 };
 
@@ -124,6 +126,7 @@ __device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
   s.ub = base + kOffUb;
   s.tasks = base + kOffTasks;
   s.cnt = reinterpret_cast<int *>(base + kOffCnt);
+  s.msk = reinterpret_cast<unsigned *>(base + kOffMsk);
   s.bar = reinterpret_cast<unsigned long long *>(base + kOffBar);
   return s;
 }
@@ -208,6 +211,8 @@ __device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const uns
   }
   s.ls[r*kUS + c] = (unsigned char)L;
   s.ub[r*kUS + c] = (unsigned char)bits;
+  if (bits & kUbTop) atomicOr(s.msk + r, 1u << c);
+  if (bits & kUbLeft) atomicOr(s.msk + 10 + r, 1u << c);
   return L;
 }
 
@@ -278,62 +283,75 @@ __device__ __forceinline__ void lap_chunk(int *A, int yl, int m) {
 }
 
 // Block-wide phases: one (level, direction) at a time, a barrier between phases.
+// Which edges are filtered comes from the per-unit-row bit masks s.msk.
 // Columns: a warp takes one line, lane = chunk 1 + lane (region columns 4*lane
 // ..).  The chunks outside 1..32 (0: the two columns left of the region; 33:
 // forward, superblock level, the two right of it) go to one extra partial warp
 // task.
 template <bool kInverse>
-__device__ __forceinline__ void region_lap_cols(int *A, const unsigned char *ub, int lv, int sb,
+__device__ __forceinline__ void region_lap_cols(int *A, const unsigned *msk, int lv, int sb,
                                                 int warp, int lane) {
   const bool top = lv == sb;
   const int nlines = top ? kRegH/sb + (kInverse ? 0 : 1) : (kRegH/2)/lv;
   const int first = top ? 0 : lv, step = top ? sb : 2*lv;
   const int nextra = kInverse ? 1 : (top ? 2 : 0);         // extra chunks per line
-#pragma unroll 1
-  for (int wt = warp; wt < nlines + (nextra ? 1 : 0); wt += kRegWarps) {
-    int line, m;
-    bool on;
-    if (wt < nlines) { line = wt; m = lane + 1; on = true; }
-    else { line = lane >> 1; m = (lane & 1) ? 33 : 0; on = lane < 2*nlines && (lane & 1) < nextra; }
+  if (warp < nlines) {
+    int yl = first + warp*step;
+    // chunk m = lane + 1 lies in unit column lane >> 1, mask bit (lane >> 1) + 1
+    if ((msk[(yl >> 3) + 1] >> ((lane >> 1) + 1)) & 1) lap_chunk<kInverse>(A, yl, lane + 1);
+  }
+  else if (warp == nlines && nextra) {
+    int line = lane >> 1, m = (lane & 1) ? 33 : 0;
     int yl = first + line*step;
-    if (on && (ub[ut(yl >> 3, (m - 1) >> 1)] & kUbTop)) lap_chunk<kInverse>(A, yl, m);
+    bool on = lane < 2*nlines && (lane & 1) < nextra;
+    if (on && ((msk[(yl >> 3) + 1] >> ((lane & 1) ? 17 : 0)) & 1)) lap_chunk<kInverse>(A, yl, m);
   }
 }
 
-// Rows: a warp takes 32 consecutive rows of TWO lines (two independent filter
-// chains per lane).  Forward: region rows 0..63.  Inverse: region rows -2..61,
-// and 62..63 as well where the plane ends.
+// Rows: warp w takes the rows 32*(w & 1) .. +31 and the line pairs w >> 1, +4,
+// .. (two independent filter chains per lane).  Forward: region rows 0..63.
+// Inverse: region rows -2..61, and where the plane ends 62..63 as well (warp 0,
+// lanes 0 and 1, in a second sweep).
 template <bool kInverse>
-__device__ __forceinline__ void region_lap_rows(int *A, const unsigned char *ub, int lv, int sb,
+__device__ __forceinline__ void lap_row_pair(int *arow, unsigned m, int ja, int jb, bool hasb) {
+  bool ona = (m >> (ja + 1)) & 1;
+  bool onb = hasb && ((m >> (jb + 1)) & 1);
+  int2 *pa = reinterpret_cast<int2 *>(arow + 8*ja + 2);   // region columns 8j-2 .. 8j+1
+  int2 *pb = reinterpret_cast<int2 *>(arow + 8*jb + 2);
+  int2 la, ha, lb, hb;
+  if (ona) { la = pa[0]; ha = pa[1]; }
+  if (onb) { lb = pb[0]; hb = pb[1]; }
+  if (ona) {
+    if (kInverse) post4(la.x, la.y, ha.x, ha.y); else pre4(la.x, la.y, ha.x, ha.y);
+  }
+  if (onb) {
+    if (kInverse) post4(lb.x, lb.y, hb.x, hb.y); else pre4(lb.x, lb.y, hb.x, hb.y);
+  }
+  if (ona) { pa[0] = la; pa[1] = ha; }
+  if (onb) { pb[0] = lb; pb[1] = hb; }
+}
+template <bool kInverse>
+__device__ __forceinline__ void region_lap_rows(int *A, const unsigned *msk, int lv, int sb,
                                                 int warp, int lane, bool last_row) {
   const bool top = lv == sb;
   const int nlines = top ? kRegW/sb + (kInverse ? 0 : 1) : (kRegW/2)/lv;
-  const int first = top ? 0 : lv, step = top ? sb : 2*lv;
-  const int parts = (kInverse && last_row) ? 3 : 2;
-  const int npairs = (nlines + 1) >> 1;
+  const int jfirst = top ? 0 : lv >> 3, jstep = top ? sb >> 3 : lv >> 2;
+  const int row = 32*(warp & 1) + lane + (kInverse ? 0 : 2);    // buffer row = region row + 2
+  int *arow = A + row*kAP;
+  const unsigned m = msk[10 + ((row - 2) >> 3) + 1];
 #pragma unroll 1
-  for (int wt = warp; wt < npairs*parts; wt += kRegWarps) {
-    int pr = (parts == 2) ? wt >> 1 : wt/3;
-    int part = wt - pr*parts;
-    int row = part*32 + lane + (kInverse ? 0 : 2);          // buffer row = region row + 2
-    int xa = first + 2*pr*step, xb = xa + step;
-    const unsigned char *u = ub + ut((row - 2) >> 3, 0);
-    bool rok = row < kARegRows - 2;
-    bool ona = rok && (u[xa >> 3] & kUbLeft);
-    bool onb = rok && 2*pr + 1 < nlines && (u[xb >> 3] & kUbLeft);
-    int2 *pa = reinterpret_cast<int2 *>(A + row*kAP + xa + 2);   // region columns xa-2 .. xa+1
-    int2 *pb = reinterpret_cast<int2 *>(A + row*kAP + xb + 2);
-    int2 la, ha, lb, hb;
-    if (ona) { la = pa[0]; ha = pa[1]; }
-    if (onb) { lb = pb[0]; hb = pb[1]; }
-    if (ona) {
-      if (kInverse) post4(la.x, la.y, ha.x, ha.y); else pre4(la.x, la.y, ha.x, ha.y);
+  for (int pr = warp >> 1; 2*pr < nlines; pr += kRegWarps/2) {
+    int ja = jfirst + 2*pr*jstep;
+    lap_row_pair<kInverse>(arow, m, ja, ja + jstep, 2*pr + 1 < nlines);
+  }
+  if (kInverse && last_row && warp == 0 && lane < 2) {
+    int *arow2 = A + (64 + lane)*kAP;
+    const unsigned m2 = msk[10 + 8];
+#pragma unroll 1
+    for (int pr = 0; 2*pr < nlines; pr++) {
+      int ja = jfirst + 2*pr*jstep;
+      lap_row_pair<kInverse>(arow2, m2, ja, ja + jstep, 2*pr + 1 < nlines);
     }
-    if (onb) {
-      if (kInverse) post4(lb.x, lb.y, hb.x, hb.y); else pre4(lb.x, lb.y, hb.x, hb.y);
-    }
-    if (ona) { pa[0] = la; pa[1] = ha; }
-    if (onb) { pb[0] = lb; pb[1] = hb; }
   }
 }
 
