@@ -219,6 +219,7 @@ def main():
 
     import torch
     import daala_b200
+    from daala_b200.sharding import mpixels_per_second, reduce_timing
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for the product path)")
     torch.cuda.set_device(local_rank)
@@ -292,13 +293,10 @@ def main():
     total_ms = ev[0].elapsed_time(ev[-1])
     fwd_ms = float(np.mean([ev[2 * k].elapsed_time(ev[2 * k + 1]) for k in range(args.steps)]))
     inv_ms = float(np.mean([ev[2 * k + 1].elapsed_time(ev[2 * k + 2]) for k in range(args.steps)]))
-    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-    if dist:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
+    # whole job: max elapsed over ranks, frames summed over ranks (no data-path collective)
+    total_ms, frames_all = reduce_timing(dist, total_ms, nframes, dev)
     ms_per_step = total_ms / args.steps
-    pixels_per_step = pic_w * pic_h * nframes * world
-    value = pixels_per_step / (ms_per_step * 1e-3) / 1e6
+    value = mpixels_per_second(pic_w, pic_h, frames_all, ms_per_step)
 
     # roofline of the dominant kernel (8 algorithmic bytes per padded plane sample per launch)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -307,7 +305,8 @@ def main():
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     alg_bytes = 8.0 * samples_per_frame * nframes
-    dom, dom_ms = ("tdlt_inv_kernel", inv_ms) if inv_ms >= fwd_ms else ("tdlt_fwd_kernel", fwd_ms)
+    dom, dom_ms = (("tdlt_inv_region_kernel", inv_ms) if inv_ms >= fwd_ms
+                   else ("tdlt_fwd_region_kernel", fwd_ms))
     ach = alg_bytes / (dom_ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
             "frac": ach / peak, "traffic": None, "peak_source": peak_src,
@@ -318,7 +317,12 @@ def main():
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roof["traffic"] = json.load(open(prof)).get(dom)
+            tr = json.load(open(prof))
+            # dram bytes read + written per launch from one `ncu --set full` capture of this
+            # workload (tools/ncu_traffic.py); only meaningful for the same frames per launch
+            if tr.get("frames_per_launch") == nframes and tr.get("workload") == args.workload:
+                roof["traffic"] = tr.get(dom)
+                roof["traffic_source"] = tr.get("source")
         except Exception:
             pass
 
@@ -350,14 +354,12 @@ def main():
             e2e_step()
         torch.cuda.synchronize()
         el = time.perf_counter() - t0
-        tt = torch.tensor([el], device=dev, dtype=torch.float64)
-        if dist:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        el = float(tt.item())
+        el_ms, frames_e2e = reduce_timing(dist, el * 1e3, nframes, dev)
+        el = el_ms * 1e-3
         if not all(torch.equal(a, b) for a, b in zip(hc, hc2)):
             raise SystemExit("bench.py: e2e round trip mismatch")
         plane_bytes = 4 * samples_per_frame * nframes
-        e2e = {"value": pic_w * pic_h * nframes * world * e2e_steps / el / 1e6, "unit": "Mpixel/s",
+        e2e = {"value": pic_w * pic_h * frames_e2e * e2e_steps / el / 1e6, "unit": "Mpixel/s",
                "h2d_bytes_per_step": 2 * plane_bytes + 2 * maps_np.nbytes,
                "d2h_bytes_per_step": 2 * plane_bytes, "steps": e2e_steps,
                "api": "od_tdlt_fwd_frames + od_tdlt_inv_frames (pinned host od_coeff planes)"}

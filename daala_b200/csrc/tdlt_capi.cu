@@ -16,6 +16,7 @@
 using namespace tdlt;
 
 static std::atomic<long long> g_launches{0};
+constexpr int kMaxChunks = 64;   // pipeline depth of one host-pointer call
 
 struct od_tdlt_ctx {
   od_tdlt_geometry g;
@@ -35,7 +36,9 @@ struct od_tdlt_ctx {
   od_coeff *dev_d[kMaxPlanes];
   void *dev_pix[kMaxPlanes];
   unsigned char *dev_bsize;
-  cudaStream_t stream;
+  cudaStream_t stream;          // kernels
+  cudaStream_t s_in, s_out;     // uploads / downloads of the host-pointer calls
+  cudaEvent_t ev_in[kMaxChunks], ev_run[kMaxChunks];
   char err[256];
 };
 
@@ -163,6 +166,18 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
       rc = OD_TDLT_EFAULT; break;
     }
+    if (cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking) != cudaSuccess) {
+      rc = OD_TDLT_EFAULT; break;
+    }
+    {
+      bool ok = true;
+      for (int k = 0; k < kMaxChunks && ok; k++) {
+        ok = cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->ev_run[k], cudaEventDisableTiming) == cudaSuccess;
+      }
+      if (!ok) { rc = OD_TDLT_EFAULT; break; }
+    }
     if (cudaMalloc(&ctx->ticket, 256) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
@@ -201,6 +216,12 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
+  for (int k = 0; k < kMaxChunks; k++) {
+    if (ctx->ev_in[k]) cudaEventDestroy(ctx->ev_in[k]);
+    if (ctx->ev_run[k]) cudaEventDestroy(ctx->ev_run[k]);
+  }
+  if (ctx->s_in) cudaStreamDestroy(ctx->s_in);
+  if (ctx->s_out) cudaStreamDestroy(ctx->s_out);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   free(ctx);
 }
@@ -339,52 +360,142 @@ static int check_frames(od_tdlt_ctx *ctx, int nframes) {
   return OD_TDLT_SUCCESS;
 }
 
+// One host call = a pipeline over chunks of frames on three streams: the upload
+// of chunk k+1 (host -> device), the kernels of chunk k and the download of chunk
+// k-1 (device -> host) overlap, so a call costs about max(upload, download) of
+// the PCIe link instead of their sum.  Chunks are independent (frames are), and
+// every chunk has its own slice of the staging buffers.
+struct FramesJob {
+  bool inverse;
+  bool pix;                       // the spatial side is 8/16-bit reference-buffer samples
+  od_coeff *const *coef_out;      // host planes written   (forward: d, inverse without pix: c)
+  const od_coeff *const *coef_in; // host planes read      (forward without pix: c, inverse: d)
+  void *const *pix_out;           // inverse + pix
+  const void *const *pix_in;      // forward + pix
+  const int *ystride;
+  const long long *frame_stride;
+  const unsigned char *bsize;
+  int nframes, flags, xstride, bitdepth_mode, lossless_p;
+};
+
+static int run_frames(od_tdlt_ctx *ctx, const FramesJob &j) {
+  int rc = check_frames(ctx, j.nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  const int np = ctx->g.nplanes;
+  long long frame_samples = 0;
+  for (int p = 0; p < np; p++) frame_samples += ctx->plane_size[p];
+  // chunks of about 96 MB of coefficients, at most kMaxChunks of them
+  long long per = (96ll << 20)/(frame_samples*(long long)sizeof(od_coeff));
+  int chunk = (int)(per < 1 ? 1 : per);
+  if ((j.nframes + chunk - 1)/chunk > kMaxChunks) chunk = (j.nframes + kMaxChunks - 1)/kMaxChunks;
+  const long long bsz = od_tdlt_bsize_size(ctx);
+  cudaStream_t s_in = ctx->s_in, s_run = ctx->stream, s_out = ctx->s_out;
+  int k = 0;
+  for (int f0 = 0; f0 < j.nframes; f0 += chunk, k++) {
+    const int n = (j.nframes - f0 < chunk) ? j.nframes - f0 : chunk;
+    od_coeff *dc[kMaxPlanes], *dd[kMaxPlanes];
+    for (int p = 0; p < np; p++) {
+      dc[p] = ctx->dev_c[p] + (size_t)f0*ctx->plane_size[p];
+      dd[p] = ctx->dev_d[p] + (size_t)f0*ctx->plane_size[p];
+    }
+    unsigned char *db = ctx->dev_bsize + (size_t)f0*bsz;
+    // ---- upload -----------------------------------------------------------
+    for (int p = 0; p < np; p++) {
+      const size_t bytes = (size_t)ctx->plane_size[p]*n*sizeof(od_coeff);
+      if (j.inverse) {
+        CK(ctx, cudaMemcpyAsync(dd[p], j.coef_in[p] + (size_t)f0*ctx->plane_size[p], bytes,
+                                cudaMemcpyHostToDevice, s_in));
+      }
+      else if (!j.pix) {
+        CK(ctx, cudaMemcpyAsync(dc[p], j.coef_in[p] + (size_t)f0*ctx->plane_size[p], bytes,
+                                cudaMemcpyHostToDevice, s_in));
+      }
+      else {
+        const RegionPlane &pd = ctx->rb.pl[p];
+        const size_t row = (size_t)pd.w*j.xstride;
+        for (int f = f0; f < f0 + n; f++) {
+          CK(ctx, cudaMemcpy2DAsync((char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row,
+                                    (const char *)j.pix_in[p] + f*j.frame_stride[p], j.ystride[p],
+                                    row, pd.h, cudaMemcpyHostToDevice, s_in));
+        }
+      }
+    }
+    CK(ctx, cudaMemcpyAsync(db, j.bsize + (size_t)f0*bsz, (size_t)bsz*n, cudaMemcpyHostToDevice, s_in));
+    CK(ctx, cudaEventRecord(ctx->ev_in[k], s_in));
+    // ---- kernels ------------------------------------------------------------
+    CK(ctx, cudaStreamWaitEvent(s_run, ctx->ev_in[k], 0));
+    if (!j.inverse) {
+      if (j.pix) {
+        for (int p = 0; p < np; p++) {
+          rc = od_tdlt_pix_to_coeff_batch(ctx, dc[p],
+              (char *)ctx->dev_pix[p] + (size_t)f0*ctx->plane_size[p]*j.xstride, p, n, j.xstride,
+              j.bitdepth_mode, j.lossless_p, s_run);
+          if (rc) return rc;
+        }
+      }
+      rc = od_tdlt_fwd_batch(ctx, dd, dc, db, n, j.flags, s_run);
+      if (rc) return rc;
+    }
+    else {
+      rc = od_tdlt_inv_batch(ctx, dc, dd, db, n, j.flags, s_run);
+      if (rc) return rc;
+      if (j.pix) {
+        for (int p = 0; p < np; p++) {
+          rc = od_tdlt_coeff_to_pix_batch(ctx,
+              (char *)ctx->dev_pix[p] + (size_t)f0*ctx->plane_size[p]*j.xstride, dc[p], p, n,
+              j.xstride, j.bitdepth_mode, j.lossless_p, s_run);
+          if (rc) return rc;
+        }
+      }
+    }
+    CK(ctx, cudaEventRecord(ctx->ev_run[k], s_run));
+    // ---- download -----------------------------------------------------------
+    CK(ctx, cudaStreamWaitEvent(s_out, ctx->ev_run[k], 0));
+    for (int p = 0; p < np; p++) {
+      const size_t bytes = (size_t)ctx->plane_size[p]*n*sizeof(od_coeff);
+      if (!j.inverse) {
+        CK(ctx, cudaMemcpyAsync(j.coef_out[p] + (size_t)f0*ctx->plane_size[p], dd[p], bytes,
+                                cudaMemcpyDeviceToHost, s_out));
+      }
+      else if (!j.pix) {
+        CK(ctx, cudaMemcpyAsync(j.coef_out[p] + (size_t)f0*ctx->plane_size[p], dc[p], bytes,
+                                cudaMemcpyDeviceToHost, s_out));
+      }
+      else {
+        const RegionPlane &pd = ctx->rb.pl[p];
+        const size_t row = (size_t)pd.w*j.xstride;
+        for (int f = f0; f < f0 + n; f++) {
+          CK(ctx, cudaMemcpy2DAsync((char *)j.pix_out[p] + f*j.frame_stride[p], j.ystride[p],
+                                    (const char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row, row,
+                                    pd.h, cudaMemcpyDeviceToHost, s_out));
+        }
+      }
+    }
+  }
+  CK(ctx, cudaStreamSynchronize(s_out));
+  CK(ctx, cudaStreamSynchronize(s_run));
+  CK(ctx, cudaStreamSynchronize(s_in));
+  return OD_TDLT_SUCCESS;
+}
+
 extern "C" {
 
 int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
                        const unsigned char *bsize, int nframes, int flags) {
   if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
-  int rc = check_frames(ctx, nframes);
-  if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(ctx->dev_c[p], c[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyHostToDevice, st));
-  }
-  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
-                          cudaMemcpyHostToDevice, st));
-  rc = od_tdlt_fwd_batch(ctx, ctx->dev_d, ctx->dev_c, ctx->dev_bsize, nframes, flags, st);
-  if (rc) return rc;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(d[p], ctx->dev_d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyDeviceToHost, st));
-  }
-  CK(ctx, cudaStreamSynchronize(st));
-  return OD_TDLT_SUCCESS;
+  FramesJob j = {};
+  j.coef_out = d; j.coef_in = c; j.bsize = bsize; j.nframes = nframes; j.flags = flags;
+  return run_frames(ctx, j);
 }
 
 int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
                        const unsigned char *bsize, int nframes, int flags) {
   if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
-  int rc = check_frames(ctx, nframes);
-  if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(ctx->dev_d[p], d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyHostToDevice, st));
-  }
-  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
-                          cudaMemcpyHostToDevice, st));
-  rc = od_tdlt_inv_batch(ctx, ctx->dev_c, ctx->dev_d, ctx->dev_bsize, nframes, flags, st);
-  if (rc) return rc;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(c[p], ctx->dev_c[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyDeviceToHost, st));
-  }
-  CK(ctx, cudaStreamSynchronize(st));
-  return OD_TDLT_SUCCESS;
+  FramesJob j = {};
+  j.inverse = true;
+  j.coef_out = c; j.coef_in = d; j.bsize = bsize; j.nframes = nframes; j.flags = flags;
+  return run_frames(ctx, j);
 }
 
 int od_tdlt_fwd_frames_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
@@ -392,32 +503,12 @@ int od_tdlt_fwd_frames_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *co
                            const unsigned char *bsize, int nframes, int flags, int xstride,
                            int bitdepth_mode, int lossless_p) {
   if (!ctx || !d || !pix || !ystride || !frame_stride || !bsize) return OD_TDLT_EFAULT;
-  int rc = check_frames(ctx, nframes);
-  if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    const PlaneDesc &pd = ctx->bd.pl[p];
-    size_t row = (size_t)pd.w*xstride;
-    for (int f = 0; f < nframes; f++) {
-      CK(ctx, cudaMemcpy2DAsync((char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row,
-                                (const char *)pix[p] + f*frame_stride[p], ystride[p], row, pd.h,
-                                cudaMemcpyHostToDevice, st));
-    }
-    rc = od_tdlt_pix_to_coeff_batch(ctx, ctx->dev_c[p], ctx->dev_pix[p], p, nframes, xstride,
-                                    bitdepth_mode, lossless_p, st);
-    if (rc) return rc;
-  }
-  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
-                          cudaMemcpyHostToDevice, st));
-  rc = od_tdlt_fwd_batch(ctx, ctx->dev_d, ctx->dev_c, ctx->dev_bsize, nframes, flags, st);
-  if (rc) return rc;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(d[p], ctx->dev_d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyDeviceToHost, st));
-  }
-  CK(ctx, cudaStreamSynchronize(st));
-  return OD_TDLT_SUCCESS;
+  FramesJob j = {};
+  j.pix = true;
+  j.coef_out = d; j.pix_in = pix; j.ystride = ystride; j.frame_stride = frame_stride;
+  j.bsize = bsize; j.nframes = nframes; j.flags = flags; j.xstride = xstride;
+  j.bitdepth_mode = bitdepth_mode; j.lossless_p = lossless_p;
+  return run_frames(ctx, j);
 }
 
 int od_tdlt_inv_frames_pix(od_tdlt_ctx *ctx, void *const pix[], const int ystride[],
@@ -425,32 +516,13 @@ int od_tdlt_inv_frames_pix(od_tdlt_ctx *ctx, void *const pix[], const int ystrid
                            const unsigned char *bsize, int nframes, int flags, int xstride,
                            int bitdepth_mode, int lossless_p) {
   if (!ctx || !d || !pix || !ystride || !frame_stride || !bsize) return OD_TDLT_EFAULT;
-  int rc = check_frames(ctx, nframes);
-  if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    CK(ctx, cudaMemcpyAsync(ctx->dev_d[p], d[p], ctx->plane_size[p]*nframes*sizeof(od_coeff),
-                            cudaMemcpyHostToDevice, st));
-  }
-  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, od_tdlt_bsize_size(ctx)*nframes,
-                          cudaMemcpyHostToDevice, st));
-  rc = od_tdlt_inv_batch(ctx, ctx->dev_c, ctx->dev_d, ctx->dev_bsize, nframes, flags, st);
-  if (rc) return rc;
-  for (int p = 0; p < ctx->g.nplanes; p++) {
-    const PlaneDesc &pd = ctx->bd.pl[p];
-    size_t row = (size_t)pd.w*xstride;
-    rc = od_tdlt_coeff_to_pix_batch(ctx, ctx->dev_pix[p], ctx->dev_c[p], p, nframes, xstride,
-                                    bitdepth_mode, lossless_p, st);
-    if (rc) return rc;
-    for (int f = 0; f < nframes; f++) {
-      CK(ctx, cudaMemcpy2DAsync((char *)pix[p] + f*frame_stride[p], ystride[p],
-                                (const char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row, row,
-                                pd.h, cudaMemcpyDeviceToHost, st));
-    }
-  }
-  CK(ctx, cudaStreamSynchronize(st));
-  return OD_TDLT_SUCCESS;
+  FramesJob j = {};
+  j.inverse = true;
+  j.pix = true;
+  j.pix_out = pix; j.coef_in = d; j.ystride = ystride; j.frame_stride = frame_stride;
+  j.bsize = bsize; j.nframes = nframes; j.flags = flags; j.xstride = xstride;
+  j.bitdepth_mode = bitdepth_mode; j.lossless_p = lossless_p;
+  return run_frames(ctx, j);
 }
 
 }  // extern "C"
@@ -514,6 +586,13 @@ void od_bin_fdct16x16_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct
 void od_bin_idct16x16_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(2, true, x, xs, y, ys); }
 void od_bin_fdct32x32_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(3, false, y, ys, x, xs); }
 void od_bin_idct32x32_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(3, true, x, xs, y, ys); }
+
+void od_tdlt_opt_vtbl_init_cuda(od_tdlt_dct_func_2d fdct_2d[], od_tdlt_dct_func_2d idct_2d[]) {
+  fdct_2d[0] = od_bin_fdct4x4_cuda;   idct_2d[0] = od_bin_idct4x4_cuda;
+  fdct_2d[1] = od_bin_fdct8x8_cuda;   idct_2d[1] = od_bin_idct8x8_cuda;
+  fdct_2d[2] = od_bin_fdct16x16_cuda; idct_2d[2] = od_bin_idct16x16_cuda;
+  fdct_2d[3] = od_bin_fdct32x32_cuda; idct_2d[3] = od_bin_idct32x32_cuda;
+}
 
 int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,
                          const od_coeff *in, int istride, long long iblock, int nblocks) {

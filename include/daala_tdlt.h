@@ -8,9 +8,10 @@
  * Three layers, coarsest first:
  *   1. device-resident batch calls   (od_tdlt_fwd_batch / od_tdlt_inv_batch)
  *      -- what bench.py times as `value`; pointers are DEVICE pointers.
- *   2. whole-frame host calls        (od_tdlt_fwd_frame / od_tdlt_inv_frame,
- *      od_tdlt_fwd_frame_img / od_tdlt_inv_frame_img)
- *      -- the real drop-in for encode.c / decode.c; pointers are HOST pointers.
+ *   2. whole-frame host calls        (od_tdlt_fwd_frames / od_tdlt_inv_frames,
+ *      od_tdlt_fwd_frames_pix / od_tdlt_inv_frames_pix)
+ *      -- the real drop-in for encode.c / decode.c; pointers are HOST pointers;
+ *      uploads, kernels and downloads are pipelined over chunks of frames.
  *   3. reference-signature calls     (od_bin_fdct8x8_cuda, od_prefilter_split_cuda ...)
  *      -- same prototypes as the reference functions, host pointers,
  *      synchronous; they exist so the reference's own call sites and
@@ -138,6 +139,15 @@ void od_bin_fdct16x16_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstr
 void od_bin_idct16x16_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
 void od_bin_fdct32x32_cuda(od_coeff *y, int ystride, const od_coeff *x, int xstride);
 void od_bin_idct32x32_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride);
+/* Installs the eight calls above into the reference's dispatch tables
+   (od_state.opt_vtbl.fdct_2d[] / idct_2d[], reference src/state.h:123-124), the way
+   od_state_opt_vtbl_init_x86 overrides them per CPU feature
+   (src/x86/x86state.c:39-97); entry OD_NBSIZES (the 64-point placeholder) is left
+   alone.  Call as
+     od_tdlt_opt_vtbl_init_cuda(state->opt_vtbl.fdct_2d, state->opt_vtbl.idct_2d);  */
+typedef void (*od_tdlt_dct_func_2d)(od_coeff *out, int out_stride, const od_coeff *in,
+ int in_stride);
+void od_tdlt_opt_vtbl_init_cuda(od_tdlt_dct_func_2d fdct_2d[], od_tdlt_dct_func_2d idct_2d[]);
 /* Many blocks in one launch: nblocks blocks of (4<<bs)^2, block i at x + i*xblock
    (resp. y + i*yblock); the useful form of the above for parity sweeps. */
 int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,

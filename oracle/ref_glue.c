@@ -275,6 +275,7 @@ int ref_encode_keyframe_bsize(void *h, const unsigned char *y,
   img.planes[2].xdec = img.planes[2].ydec = 1;
   img.planes[2].xstride = 1;
   img.planes[2].ystride = (r->pic_width + 1) >> 1;
+  for (i = 0; i < 3; i++) img.planes[i].bitdepth = 8;
   daala_encode_ctl(r->enc, OD_SET_QUANT, &quality, sizeof(quality));
   daala_encode_ctl(r->enc, OD_SET_COMPLEXITY, &complexity, sizeof(complexity));
   bframes = 0;

@@ -157,3 +157,139 @@ def test_pixel_paths_match_checker(xstride, mode, lossless):
             border[:, pad:pad + h, pad:pad + w] = 7
             assert (border == 7).all()
     chk.close()
+
+
+# ---- reference-signature entry points (include/daala_tdlt.h section 3) --------
+def _selftest_vectors(n, rng, count):
+    """The ranges of the reference's self-test (src/dct.c:3322-3391) plus impulses
+    and the +-extreme patterns (:3759-3830)."""
+    rows = [rng.integers(lo, hi + 1, size=(count, n)) * 16 for lo, hi in ((-256, 255), (-5, 5), (-300, 300))]
+    rows.append(rng.integers(-(1 << 15), 1 << 15, size=(count, n)))
+    rows.append(np.where(rng.integers(0, 2, size=(count, n)) > 0, 255 * 16, -256 * 16))
+    return np.ascontiguousarray(np.concatenate(rows, 0), dtype=np.int32)
+
+
+@pytest.mark.parametrize("bs", [0, 1, 2, 3])
+def test_dct_block_sweep(bs):
+    import daala_b200
+    L, port = daala_b200.lib(), ol.port()
+    n = 4 << bs
+    rng = np.random.default_rng(1000 + bs)
+    X = _selftest_vectors(n * n, rng, 40 if bs < 3 else 12).reshape(-1, n, n)
+    nb = X.shape[0]
+    F = np.zeros_like(X)
+    I = np.zeros_like(X)
+    assert L.od_tdlt_dct2d_blocks(bs, 0, F.ctypes.data, n, n * n, X.ctypes.data, n, n * n, nb) == 0
+    assert L.od_tdlt_dct2d_blocks(bs, 1, I.ctypes.data, n, n * n, X.ctypes.data, n, n * n, nb) == 0
+    for k in range(nb):
+        y = np.zeros((n, n), np.int32)
+        port.oc_fdct2d(bs, ol.ptr(y), n, ol.ptr(X[k]), n)
+        assert np.array_equal(F[k], y)
+        port.oc_idct2d(bs, ol.ptr(y), n, ol.ptr(X[k]), n)
+        assert np.array_equal(I[k], y)
+    # perfect reconstruction, and strided single-block calls inside a larger plane
+    R = np.zeros_like(X)
+    assert L.od_tdlt_dct2d_blocks(bs, 1, R.ctypes.data, n, n * n, F.ctypes.data, n, n * n, nb) == 0
+    assert np.array_equal(R, X)
+    plane = rng.integers(-2048, 2048, size=(2 * n, 3 * n)).astype(np.int32)
+    out = np.full_like(plane, 7)
+    fw = getattr(L, "od_bin_fdct%dx%d_cuda" % (n, n))
+    off = n * plane.shape[1] + n
+    fw(out.ctypes.data + 4 * off, plane.shape[1], plane.ctypes.data + 4 * off, plane.shape[1])
+    y = np.zeros((n, n), np.int32)
+    src = np.ascontiguousarray(plane[n:2 * n, n:2 * n])
+    port.oc_fdct2d(bs, ol.ptr(y), n, ol.ptr(src), n)
+    assert np.array_equal(out[n:2 * n, n:2 * n], y)
+    out[n:2 * n, n:2 * n] = 7
+    assert (out == 7).all()
+
+
+@pytest.mark.parametrize("f", [0, 1, 2, 3])
+def test_lap_filter_sweep(f):
+    import daala_b200
+    L, port = daala_b200.lib(), ol.port()
+    n = 4 << f
+    rng = np.random.default_rng(1100 + f)
+    X = [_selftest_vectors(n, rng, 300)]
+    if n <= 8:   # every sign pattern of +-676 (reference src/filter.c:2041-2116)
+        X.append(np.array([[676 if (m >> k) & 1 else -676 for k in range(n)] for m in range(1 << n)], np.int32))
+    else:
+        X.append(np.where(rng.integers(0, 2, size=(2048, n)) > 0, 676, -676).astype(np.int32))
+    X = np.ascontiguousarray(np.concatenate(X, 0))
+    P = np.zeros_like(X)
+    Q = np.zeros_like(X)
+    assert L.od_tdlt_lap_filter_vectors(f, 0, P.ctypes.data, X.ctypes.data, X.shape[0]) == 0
+    assert L.od_tdlt_lap_filter_vectors(f, 1, Q.ctypes.data, X.ctypes.data, X.shape[0]) == 0
+    y = np.zeros(n, np.int32)
+    for k in range(X.shape[0]):
+        port.oc_pre_filter(f, ol.ptr(y), ol.ptr(X[k]))
+        assert np.array_equal(P[k], y)
+        port.oc_post_filter(f, ol.ptr(y), ol.ptr(X[k]))
+        assert np.array_equal(Q[k], y)
+    R = np.zeros_like(X)
+    assert L.od_tdlt_lap_filter_vectors(f, 1, R.ctypes.data, P.ctypes.data, X.shape[0]) == 0
+    assert np.array_equal(R, X)
+
+
+def test_split_and_sb_edge_filters():
+    """od_prefilter_split / od_postfilter_split / od_apply_*filter_frame_sbs with the
+    reference's own signatures (host pointers, in place)."""
+    import daala_b200
+    L, port = daala_b200.lib(), ol.port()
+    rng = np.random.default_rng(1200)
+    for bs in (1, 2, 3):
+        n = 4 << bs
+        for hf, vf in ((1, 1), (1, 0), (0, 1), (0, 0)):
+            stride = n + 9
+            a = rng.integers(-2048, 2048, size=(n, stride)).astype(np.int32)
+            b = a.copy()
+            L.od_prefilter_split_cuda(a.ctypes.data, stride, bs, 0, hf, vf)
+            port.oc_prefilter_split(ol.ptr(b), stride, bs, 0, hf, vf)
+            assert np.array_equal(a, b)
+            L.od_postfilter_split_cuda(a.ctypes.data, stride, bs, 0, 0, None, 0, hf, vf)
+            port.oc_postfilter_split(ol.ptr(b), stride, bs, 0, hf, vf)
+            assert np.array_equal(a, b)
+    for nhsb, nvsb, dec in ((5, 3, 0), (6, 4, 1), (1, 1, 0), (1, 3, 1)):
+        w, h = (nhsb * 32) >> dec, (nvsb * 32) >> dec
+        a = rng.integers(-2048, 2048, size=(h, w)).astype(np.int32)
+        b = a.copy()
+        L.od_apply_prefilter_frame_sbs_cuda(a.ctypes.data, w, nhsb, nvsb, dec, dec)
+        port.oc_apply_prefilter_frame_sbs(ol.ptr(b), w, nhsb, nvsb, dec, dec)
+        assert np.array_equal(a, b)
+        L.od_apply_postfilter_frame_sbs_cuda(a.ctypes.data, w, nhsb, nvsb, dec, dec, 0, None, 0)
+        port.oc_apply_postfilter_frame_sbs(ol.ptr(b), w, nhsb, nvsb, dec, dec)
+        assert np.array_equal(a, b)
+
+
+def test_full_size_properties():
+    """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
+    size, where the CPU checker is too slow to be run on every frame: (1) the round
+    trip is the identity, (2) frame 0 matches the checker, (3) identical inputs at
+    two batch positions give identical coefficients (frames are independent)."""
+    import daala_b200
+    rng = np.random.default_rng(4000)
+    pic_w, pic_h, nframes = 3840, 2160, 3
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        bsize = make_maps("quad", 1, ctx.nhsb, ctx.nvsb, rng)
+        bsize = np.ascontiguousarray(np.repeat(bsize, nframes, 0))
+        bsize[1] = make_maps("deep", 1, ctx.nhsb, ctx.nvsb, rng)[0]
+        pix = [rng.integers(0, 1024, size=(nframes,) + s).astype(np.int16) for s in ctx.plane_shapes]
+        for p in range(3):
+            pix[p][2] = pix[p][0]
+        d = [np.zeros((nframes,) + s, np.int32) for s in ctx.plane_shapes]
+        # 16-bit reference buffers, lossy: (src - 2048 + rnd) >> shift with mode 2 -> coeff
+        ctx.fwd_frames_pix(d, pix, bsize, 1, xstride=2, bitdepth_mode=2, lossless=0)
+        port = ol.port()
+        for p, dec in enumerate(DECS):
+            h, w = ctx.plane_shapes[p]
+            c0 = np.zeros((h, w), np.int32)
+            src = np.ascontiguousarray(pix[p][0])
+            port.oc_buf_to_coeff(2, ol.ptr(c0), w, 0, ol.ptr(src.view(np.uint8)), 2, 2 * w, w, h)
+            assert np.array_equal(d[p][0], chk.fwd_plane(c0, bsize[0], dec, 1))
+            assert np.array_equal(d[p][2], d[p][0])
+        out = [np.zeros_like(a) for a in pix]
+        ctx.inv_frames_pix(out, d, bsize, 1, xstride=2, bitdepth_mode=2, lossless=0)
+        for p in range(3):
+            assert np.array_equal(out[p], pix[p])
+    chk.close()
