@@ -6,9 +6,12 @@
 // first sorted into lists of equal-shaped tasks, so that every warp instruction
 // runs the same code on 32 busy lanes whatever the block-size map looks like:
 //
-//   lapping    4x4 CELLS centred on the multiples of 4 (tdlt_device.cuh), one
-//              lane per cell, lists by kind: vertical-only, horizontal-only,
-//              crossing (column filter first), crossing (row filter first)
+//   lapping    block-wide phases, one per (level, direction), levels = the edge
+//              alignments superblock / 16 / 8; a lane filters four columns of
+//              one edge line (int4 per row) or one row of two edge lines; which
+//              edges are filtered is a bit test against per-unit-row masks.
+//              Level 4 (mid-edges of a unit split into 4x4) is filtered in
+//              registers by the transform task of that unit.
 //   transforms class 0: an 8x8 unit split into four 4x4 blocks  (2 lanes)
 //              class 1: an 8x8 block                            (2 lanes)
 //              class 2: a 16x16 block                           (8 lanes)
@@ -23,7 +26,7 @@
 //       of halo where the lapping needs 2; 140 words = 35 16-byte chunks, an
 //       odd number, so that 8 consecutive rows of one chunk column fall in 8
 //       different bank groups)
-//   unit table, cell lists, task lists, counters.
+//   unit tables (leaf size, edge bits), edge masks, task lists, counters.
 #pragma once
 #include "tdlt_device.cuh"
 #include "tdlt_tasks.cuh"
