@@ -74,6 +74,13 @@ def lib():
         for f in ("od_tf_up_hv_cuda", "od_tf_down_hv_cuda"):
             getattr(L, f).argtypes = [vp, ci, vp, ci, ci]
             getattr(L, f).restype = None
+        for f, na in (("od_tf_up_h_lp_cuda", 2), ("od_tf_up_v_lp_cuda", 2), ("od_tf_up_hv_lp_cuda", 3),
+                      ("od_tf_filter_2d_cuda", 1), ("od_tf_filter_inv_2d_cuda", 1),
+                      ("od_convert_block_down_cuda", 3)):
+            getattr(L, f).argtypes = [vp, ci, vp, ci] + [ci] * na
+            getattr(L, f).restype = None
+        L.od_tdlt_opt_vtbl_init_cuda.argtypes = [vp, vp]
+        L.od_tdlt_opt_vtbl_init_cuda.restype = None
         L.od_prefilter_split_cuda.argtypes = [vp, ci, ci, ci, ci, ci]
         L.od_prefilter_split_cuda.restype = None
         L.od_postfilter_split_cuda.argtypes = [vp, ci, ci, ci, ci, vp, ci, ci, ci]

@@ -348,6 +348,134 @@ void launch_tf_hv(bool down, int *dst, int dstride, const int *src, int sstride,
   tf_hv_kernel<<<grid, blk, 0, st>>>(dst, dstride, src, sstride, n, down ? 1 : 0);
 }
 
+// ---------------------------------------------------------------------------
+// The remaining time-frequency helpers of reference src/tf.c, one CTA per call
+// (a block is at most 32x32): the low-pass-only merges od_tf_up_{h,v,hv}_lp
+// (:38-108), the TF smoothing filters od_tf_filter_2d / _inv_2d (:171-235) and
+// od_convert_block_down (:237-277).  Parity surface; nothing here is hot.
+// ---------------------------------------------------------------------------
+enum { kTfUpH = 0, kTfUpV = 1, kTfUpHV = 2, kTfFilt = 3, kTfFiltInv = 4, kTfDown = 5 };
+
+// One line of the TF filter: a chain over the odd positions (src/tf.c:171-199).
+__device__ __forceinline__ void tf_filter_line(int *v, int stride, int n, bool inverse) {
+  int m = (n >> 1) - 1;
+  if (!inverse) {
+    int *q = v + stride;
+    for (int i = 0; i < m; i++) {
+      int *u = q;
+      q += 2*stride;
+      *u += *q >> 1;
+      *q -= *u >> 1;
+    }
+  }
+  else {
+    int *u = v + stride*(n - 1);
+    for (int i = 0; i < m; i++) {
+      int *q = u;
+      u -= 2*stride;
+      *q += *u >> 1;
+      *u -= *q >> 1;
+    }
+  }
+}
+
+__global__ void tf_ops_kernel(int op, int *__restrict__ dst, int dstride,
+                              const int *__restrict__ src, int sstride, int n, int p0, int p1,
+                              int p2) {
+  __shared__ int buf[2][32*32];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  if (op == kTfUpH) {                // p0 = dx
+    for (int e = tid; e < n*(n >> 1); e += nt) {
+      int y = e/(n >> 1), x = e - y*(n >> 1);
+      int ll = src[y*sstride + x];
+      int lh = ll - src[y*sstride + x + p0];
+      int hs = x & 1;
+      ll -= tdlt_half(lh);
+      dst[y*dstride + 2*x + hs] = ll;
+      dst[y*dstride + 2*x + 1 - hs] = lh;
+    }
+  }
+  else if (op == kTfUpV) {           // p0 = dy
+    for (int e = tid; e < n*(n >> 1); e += nt) {
+      int y = e/n, x = e - y*n;
+      int vs = y & 1;
+      int ll = src[y*sstride + x];
+      int hl = ll - src[(y + p0)*sstride + x];
+      ll -= tdlt_half(hl);
+      dst[(2*y + vs)*dstride + x] = ll;
+      dst[(2*y + 1 - vs)*dstride + x] = hl;
+    }
+  }
+  else if (op == kTfUpHV) {          // p0 = dx, p1 = dy
+    int h = n >> 1;
+    for (int e = tid; e < h*h; e += nt) {
+      int y = e/h, x = e - y*h;
+      int ll = src[y*sstride + x], lh = src[y*sstride + x + p0];
+      int hl = src[(y + p1)*sstride + x], hh = src[(y + p1)*sstride + x + p0];
+      haar2x2(ll, hl, lh, hh);
+      int hs = x & 1, vs = y & 1;
+      dst[(2*y + vs)*dstride + 2*x + hs] = ll;
+      dst[(2*y + vs)*dstride + 2*x + 1 - hs] = lh;
+      dst[(2*y + 1 - vs)*dstride + 2*x + hs] = hl;
+      dst[(2*y + 1 - vs)*dstride + 2*x + 1 - hs] = hh;
+    }
+  }
+  else {
+    // in shared memory: buf[cur] holds the n x n block, row stride 32
+    int cur = 0;
+    for (int e = tid; e < n*n; e += nt) buf[0][(e/n)*32 + e%n] = src[(e/n)*sstride + e%n];
+    __syncthreads();
+    if (op == kTfFilt || op == kTfFiltInv) {
+      bool inv = op == kTfFiltInv;
+      // forward: rows then columns; inverse: columns then rows
+      for (int step = 0; step < 2; step++) {
+        bool rows = (step == 0) != inv;
+        if (tid < n) tf_filter_line(rows ? buf[0] + 32*tid : buf[0] + tid, rows ? 1 : 32, n, inv);
+        __syncthreads();
+      }
+    }
+    else {                           // od_convert_block_down: p0 = curr, p1 = dest, p2 = filter
+      int s = n;                     // current block size
+      for (int lvl = p0; lvl > p1; lvl--, s >>= 1) {
+        int nb = n/s;                // blocks per side at this level
+        if (p2) {
+          for (int step = 0; step < 2; step++) {      // inverse filter: columns, then rows
+            for (int e = tid; e < nb*nb*s; e += nt) {
+              int blk = e/s, l = e - blk*s;
+              int *b0 = buf[cur] + (blk/nb)*s*32 + (blk%nb)*s;
+              tf_filter_line(step == 0 ? b0 + l : b0 + 32*l, step == 0 ? 32 : 1, s, true);
+            }
+            __syncthreads();
+          }
+        }
+        int h = s >> 1;
+        for (int e = tid; e < nb*nb*h*h; e += nt) {
+          int blk = e/(h*h), r = e - blk*h*h;
+          int y = r/h, x = r - y*h;
+          const int *a = buf[cur] + (blk/nb)*s*32 + (blk%nb)*s;
+          int *o = buf[cur ^ 1] + (blk/nb)*s*32 + (blk%nb)*s;
+          int hs = x & 1, vs = y & 1;
+          int ll = a[(2*y + vs)*32 + 2*x + hs], lh = a[(2*y + vs)*32 + 2*x + 1 - hs];
+          int hl = a[(2*y + 1 - vs)*32 + 2*x + hs], hh = a[(2*y + 1 - vs)*32 + 2*x + 1 - hs];
+          haar2x2(ll, lh, hl, hh);
+          o[y*32 + x] = ll;
+          o[y*32 + x + h] = lh;
+          o[(y + h)*32 + x] = hl;
+          o[(y + h)*32 + x + h] = hh;
+        }
+        __syncthreads();
+        cur ^= 1;
+      }
+    }
+    for (int e = tid; e < n*n; e += nt) dst[(e/n)*dstride + e%n] = buf[cur][(e/n)*32 + e%n];
+  }
+}
+
+void launch_tf_op(int op, int *dst, int dstride, const int *src, int sstride, int n, int p0,
+                  int p1, int p2, cudaStream_t st) {
+  tf_ops_kernel<<<1, 256, 0, st>>>(op, dst, dstride, src, sstride, n, p0, p1, p2);
+}
+
 void launch_pix_to_coeff(int *c, const void *pix, long long nsamples, int xstride, int shift,
                          cudaStream_t st) {
   long long n4 = nsamples/4;

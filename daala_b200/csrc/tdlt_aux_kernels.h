@@ -18,5 +18,9 @@ void launch_haar_block(bool inverse, int *y, int ystride, const int *x, int xstr
                        cudaStream_t st);
 void launch_tf_hv(bool down, int *dst, int dstride, const int *src, int sstride, int n,
                   cudaStream_t st);
+// op: 0 up_h_lp(p0 = dx), 1 up_v_lp(p0 = dy), 2 up_hv_lp(p0 = dx, p1 = dy), 3 filter_2d,
+// 4 filter_inv_2d, 5 convert_block_down(p0 = curr_size, p1 = dest_size, p2 = filter)
+void launch_tf_op(int op, int *dst, int dstride, const int *src, int sstride, int n, int p0,
+                  int p1, int p2, cudaStream_t st);
 
 }  // namespace tdlt

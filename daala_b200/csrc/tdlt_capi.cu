@@ -650,6 +650,42 @@ static void tf_one(bool down, od_coeff *dst, int dstride, const od_coeff *src, i
 void od_tf_up_hv_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) { tf_one(false, dst, ds, src, ss, n); }
 void od_tf_down_hv_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) { tf_one(true, dst, ds, src, ss, n); }
 
+// The other helpers of src/tf.c: source extent sw x sh, result n x n.
+static void tf_op(int op, od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n,
+                  int sw, int sh, int p0, int p1, int p2) {
+  if (n < 2 || n > 32 || sw > 64 || sh > 64) die("od_tf_*: block too large", cudaErrorInvalidValue);
+  int *din = g_scratch.A((size_t)sw*sh), *dout = g_scratch.B((size_t)n*n);
+  h2d_rect(din, src, sstride, sh, sw);
+  launch_tf_op(op, dout, n, din, sw, n, p0, p1, p2, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(dst, dstride, dout, n, n);
+}
+void od_tf_up_h_lp_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int dx, int n) {
+  tf_op(0, dst, ds, src, ss, n, (n >> 1) + dx, n, dx, 0, 0);
+}
+void od_tf_up_v_lp_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int dy, int n) {
+  tf_op(1, dst, ds, src, ss, n, n, (n >> 1) + dy, dy, 0, 0);
+}
+void od_tf_up_hv_lp_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int dx, int dy,
+                         int n) {
+  tf_op(2, dst, ds, src, ss, n, (n >> 1) + dx, (n >> 1) + dy, dx, dy, 0);
+}
+void od_tf_filter_2d_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) {
+  tf_op(3, dst, ds, src, ss, n, n, n, 0, 0, 0);
+}
+void od_tf_filter_inv_2d_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) {
+  tf_op(4, dst, ds, src, ss, n, n, n, 0, 0, 0);
+}
+void od_convert_block_down_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int curr_size,
+                                int dest_size, int filter) {
+  if (curr_size < dest_size || curr_size > 3 || dest_size < 0) {
+    die("od_convert_block_down: bad sizes", cudaErrorInvalidValue);
+  }
+  int n = 4 << curr_size;
+  tf_op(5, dst, ds, src, ss, n, n, n, curr_size, dest_size, filter);
+}
+
 // General f is supported through the N-tap vector kernel only for f == 0 here:
 // the codec never uses another size on this path (OD_FILT_SIZE == 0,
 // reference src/filter.h:99), and the reference asserts nothing else either.

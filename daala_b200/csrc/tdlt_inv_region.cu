@@ -324,34 +324,30 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   }
   TDLT_MARK(t, 7);
   // ---- store the owned rectangle: buffer row b <-> plane row Y0 - 2 + b ---------
-  // Region columns 0.. go out as 16-byte vectors (they are 16-byte aligned in
-  // the plane and in A); the two columns left of the region and, where the
-  // rectangle ends at column 125, the two after column 123 as 8-byte vectors.
+  // The owned columns cs .. ce-1 (cs = -2, or 0 in the first region column; ce = 126,
+  // or where the plane ends) are at most 128 and start on an 8-byte boundary: every
+  // row goes out as two warp-wide runs of 8-byte vectors, lane = column pair (plus
+  // one more pair in the last region column of a plane wider than one region).
   {
     const int b0 = (id.ry == 0) ? 2 : 0;
     const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
-    const int q1 = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;   // end of the owned columns
-    const int nq = q1 >> 2;
-    // second instruction: lane 0 = columns -2, -1; lane 1 = columns 4*nq, 4*nq + 1
-    const bool side = (lane == 0 && id.rx > 0) || (lane == 1 && (q1 & 2));
-    const int scol = (lane == 0) ? -2 : 4*nq;
+    const int cs = (id.rx > 0) ? -2 : 0;
+    const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
+    const int c0 = cs + 2*lane, c1 = c0 + 64;
+    const bool on0 = c0 < ce, on1 = c1 < ce;
+    const bool on2 = c0 + 128 < ce;     // lane 0 of the last region column: columns 126, 127
     const size_t pitch = (size_t)pd.w;
-    int *grow = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pitch + X0;
-    const int *arow = s.A + (b0 + warp)*kAP + 4;
-    const bool body = lane < nq;
-    // rows b0 + warp + 8k
+    int *grow = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pitch + X0 + c0;
+    const int *arow = s.A + (b0 + warp)*kAP + 4 + c0;
     const int nb = b1 - b0 - warp;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
       if (kRegWarps*k < nb) {
         const int *ar = arow + k*kRegWarps*kAP;
         int *gr = grow + (size_t)(k*kRegWarps)*pitch;
-        if (body) {
-          *reinterpret_cast<int4 *>(gr + 4*lane) = *reinterpret_cast<const int4 *>(ar + 4*lane);
-        }
-        if (side) {
-          *reinterpret_cast<int2 *>(gr + scol) = *reinterpret_cast<const int2 *>(ar + scol);
-        }
+        if (on0) *reinterpret_cast<int2 *>(gr) = *reinterpret_cast<const int2 *>(ar);
+        if (on1) *reinterpret_cast<int2 *>(gr + 64) = *reinterpret_cast<const int2 *>(ar + 64);
+        if (on2) *reinterpret_cast<int2 *>(gr + 128) = *reinterpret_cast<const int2 *>(ar + 128);
       }
     }
   }

@@ -161,6 +161,20 @@ void od_haar_inv_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystride, 
 /* reference src/tf.h:53-56, src/tf.c:112-169 */
 void od_tf_up_hv_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
 void od_tf_down_hv_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
+/* reference src/tf.h:46-53, src/tf.c:38-108 (low-pass-only merges; the live caller is
+   od_resample_luma_coeffs, src/intra.c:81-94) */
+void od_tf_up_h_lp_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int dx,
+ int n);
+void od_tf_up_v_lp_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int dy,
+ int n);
+void od_tf_up_hv_lp_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int dx,
+ int dy, int n);
+/* reference src/tf.h:60-66, src/tf.c:171-277 */
+void od_tf_filter_2d_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
+void od_tf_filter_inv_2d_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride,
+ int n);
+void od_convert_block_down_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride,
+ int curr_size, int dest_size, int filter);
 /* reference src/filter.h:121-128, src/filter.c:1486-1646 (OD_DEBLOCKING == 0:
    q, skip and skip_stride are ignored, as in the reference) */
 void od_prefilter_split_cuda(od_coeff *c0, int stride, int bs, int f, int hfilter, int vfilter);

@@ -147,6 +147,14 @@ def main():
             getattr(R, "od_" + name)(ptr(out), m, ptr(src), m, *args)
             G["tf_%d_%s" % (n, name)] = out
 
+    for curr, dest, filt in ((1, 0, 0), (2, 0, 1), (3, 1, 0), (3, 0, 1), (2, 2, 0), (3, 2, 1)):
+        n = 4 << curr
+        src = np.ascontiguousarray(lcg_ints(55 + curr * 8 + dest * 2 + filt, n * n, -30000, 30000).reshape(n, n))
+        out = np.zeros((n, n), np.int32)
+        R.od_convert_block_down(ptr(out), n, ptr(src), n, curr, dest, filt)
+        G["cbd_%d_%d_%d_src" % (curr, dest, filt)] = src
+        G["cbd_%d_%d_%d_out" % (curr, dest, filt)] = out
+
     # ---- whole planes: 100x60 picture -> 128x64 frame, 4:2:0 ------------------------
     pic_w, pic_h = 100, 60
     with ol.RefCtx(pic_w, pic_h) as rc:

@@ -89,6 +89,15 @@ def test_port_haar_and_tf(G):
             out = np.zeros((m, m), np.int32)
             getattr(P, "oc_" + name)(ptr(out), m, ptr(src), m, *args)
             assert np.array_equal(out, G["tf_%d_%s" % (n, name)]), name
+    for curr, dest, filt in CBD_CASES:
+        n = 4 << curr
+        src = np.ascontiguousarray(G["cbd_%d_%d_%d_src" % (curr, dest, filt)])
+        out = np.zeros((n, n), np.int32)
+        P.oc_convert_block_down(ptr(out), n, ptr(src), n, curr, dest, filt)
+        assert np.array_equal(out, G["cbd_%d_%d_%d_out" % (curr, dest, filt)])
+
+
+CBD_CASES = [(1, 0, 0), (2, 0, 1), (3, 1, 0), (3, 0, 1), (2, 2, 0), (3, 2, 1)]
 
 
 def test_port_planes(G):
@@ -193,6 +202,17 @@ def test_cuda_haar_and_tf(G):
         assert np.array_equal(out, G["tf_%d_tf_up_hv" % n])
         L.od_tf_down_hv_cuda(out.ctypes.data, m, src.ctypes.data, m, m)
         assert np.array_equal(out, G["tf_%d_tf_down_hv" % n])
+        for name, args in (("tf_up_hv_lp", (n, n, m)), ("tf_up_h_lp", (n, m)), ("tf_up_v_lp", (n, m)),
+                           ("tf_filter_2d", (m,)), ("tf_filter_inv_2d", (m,))):
+            out = np.full((m, m), 7, np.int32)
+            getattr(L, "od_%s_cuda" % name)(out.ctypes.data, m, src.ctypes.data, m, *args)
+            assert np.array_equal(out, G["tf_%d_%s" % (n, name)]), name
+    for curr, dest, filt in CBD_CASES:
+        n = 4 << curr
+        src = np.ascontiguousarray(G["cbd_%d_%d_%d_src" % (curr, dest, filt)])
+        out = np.zeros((n, n), np.int32)
+        L.od_convert_block_down_cuda(out.ctypes.data, n, src.ctypes.data, n, curr, dest, filt)
+        assert np.array_equal(out, G["cbd_%d_%d_%d_out" % (curr, dest, filt)])
 
 
 @pytest.mark.gpu
