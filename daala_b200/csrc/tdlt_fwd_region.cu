@@ -58,7 +58,7 @@ __device__ __forceinline__ void region_haar_fwd_tile(int *At, int *Bt, int lane,
   }
 }
 
-__global__ void __launch_bounds__(kRegThreads, 3)
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ bsize) {
@@ -71,7 +71,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
   const bool haar = (bd.flags & 2) != 0;
 
-  if (tid == 0) {
+  if (tid == 0 && !(TDLT_ABLATE & 16)) {
     mbar_init(s.bar, 1);
     fence_mbar_init();
     mbar_expect_tx(s.bar, kARegBytes);
@@ -79,16 +79,16 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   }
   if (tid >= 228) s.cnt[tid - 228] = 0;       // counters and edge masks
   __syncthreads();
-  region_setup_units(s, bsize, bd, pd, id, tid, lane);
+  if (!(TDLT_ABLATE & 8)) region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 1);
-  mbar_wait(s.bar, 0);
+  if (!(TDLT_ABLATE & 16)) mbar_wait(s.bar, 0);
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 2);
 
   if (!haar) {
     // ---- lapping, level by level, coarse to fine (level 4 is done in registers
     // by the transform tasks of the units it concerns) ---------------------------
-    {
+    if (!(TDLT_ABLATE & 1)) {
       const int sb = 32 >> pd.dec;
 #pragma unroll 1
       for (int lv = sb; lv >= 8; lv >>= 1) {
@@ -100,7 +100,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
     }
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 4);
     // ---- transforms ---------------------------------------------------------
-    {
+    if (!(TDLT_ABLATE & 2)) {
       const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
       const int q0 = (n0 + 15) >> 4, q1 = (n1 + 15) >> 4, q2 = (n2 + 3) >> 2;
       const int ntask = q0 + q1 + q2 + n3;
@@ -203,7 +203,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       if (haar) {
         region_haar_fwd_tile(s.A + (32*ty + 2)*kAP + 32*tx + 4, Bt, lane, 32 >> pd.dec);
       }
-      else if (bd.flags & 1) {
+      else if ((bd.flags & 1) && !(TDLT_ABLATE & 4)) {
         const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
         region_dc_level<false>(Bt, ls0, lane, 8);
         region_dc_level<false>(Bt, ls0, lane, 16);
@@ -211,7 +211,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && !(TDLT_ABLATE & 16)) {
         tma_store_3d(&maps.out[id.pli], Bt, TX, TY, id.frame);
         tma_store_commit_and_wait_read();
       }

@@ -116,7 +116,7 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
-__global__ void __launch_bounds__(kRegThreads, 3)
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ bsize, InvOut out,
@@ -124,7 +124,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
-  if (tid == 0) s.cnt[0] = atomicAdd(ticket, 1);
+  if (tid == 0) s.cnt[0] = (TDLT_ABLATE & 64) ? (int)blockIdx.x : atomicAdd(ticket, 1);
   if (tid >= 229) s.cnt[tid - 228] = 0;       // counters (but the ticket) and edge masks
   __syncthreads();
   const int t = s.cnt[0];
@@ -159,10 +159,10 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   bool ring_done;
   {
     RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
-    ring_done = !rs.need;
+    ring_done = !rs.need || (TDLT_ABLATE & 32);
     if (rs.need && (tid < 128 || tid >= 192)) ring_done = ring_try(rs, epoch);
   }
-  region_setup_units(s, bsize, bd, pd, id, tid, lane);
+  if (!(TDLT_ABLATE & 8)) region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
   TDLT_MARK(t, 1);
   mbar_wait(s.bar, 0);
@@ -185,7 +185,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   }
 
   // ---- keyframe: undo the DC pyramid, top-down --------------------------------
-  if ((bd.flags & 1) && tile_on) {
+  if ((bd.flags & 1) && tile_on && !(TDLT_ABLATE & 4)) {
     int *Bt = s.B + warp*(kBBytes/4);
     const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
     if (pd.dec == 0) region_dc_level<true>(Bt, ls0, lane, 32);
@@ -196,7 +196,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   TDLT_MARK(t, 3);
 
   // ---- inverse transforms: rows first, then columns (src/dct.c:144-149) --------
-  {
+  if (!(TDLT_ABLATE & 2)) {
     const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
     const int q0 = (n0 + 15) >> 4, q1 = (n1 + 15) >> 4, q2 = (n2 + 3) >> 2;
     const int ntask = q0 + q1 + q2 + n3;
@@ -300,8 +300,10 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       val = *reinterpret_cast<int2 *>(s.A + (r + 2)*kAP + 126 + 4);
       at = 2*kRegW + 2*r;
     }
-    st_pair(mine + at, val.x, epoch);
-    st_pair(mine + at + 1, val.y, epoch);
+    if (!(TDLT_ABLATE & 32)) {
+      st_pair(mine + at, val.x, epoch);
+      st_pair(mine + at + 1, val.y, epoch);
+    }
   }
   TDLT_MARK(t, 5);
 
@@ -316,7 +318,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
 #pragma unroll 1
-  for (int lv = 8; lv <= sb; lv <<= 1) {
+  for (int lv = (TDLT_ABLATE & 1) ? 64 : 8; lv <= sb; lv <<= 1) {
     region_lap_rows<true>(s.A, s.msk, lv, sb, warp, lane, last_r);
     __syncthreads();
     region_lap_cols<true>(s.A, s.msk, lv, sb, warp, lane);
@@ -345,6 +347,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       if (kRegWarps*k < nb) {
         const int *ar = arow + k*kRegWarps*kAP;
         int *gr = grow + (size_t)(k*kRegWarps)*pitch;
+        if (TDLT_ABLATE & 128) continue;
         if (on0) *reinterpret_cast<int2 *>(gr) = *reinterpret_cast<const int2 *>(ar);
         if (on1) *reinterpret_cast<int2 *>(gr + 64) = *reinterpret_cast<const int2 *>(ar + 64);
         if (on2) *reinterpret_cast<int2 *>(gr + 128) = *reinterpret_cast<const int2 *>(ar + 128);

@@ -44,6 +44,16 @@ extern __device__ long long *g_tdlt_trace;
 #define TDLT_MARK(cta, k) do { } while (0)
 #endif
 
+// Experiment switches (tools/variants.py builds libraries with them; the product
+// build leaves them at their defaults): minimum CTAs per SM the kernels are compiled
+// for, and phases to skip when measuring what a phase costs (results are then wrong).
+#ifndef TDLT_MINB
+#define TDLT_MINB 3
+#endif
+#ifndef TDLT_ABLATE
+#define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores
+#endif
+
 constexpr int kRegW = 128, kRegH = 64;       // region size in samples
 constexpr int kRegTX = 4, kRegTY = 2;        // tiles across / down
 constexpr int kRegTiles = kRegTX*kRegTY;
