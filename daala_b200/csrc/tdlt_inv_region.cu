@@ -317,6 +317,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
 
   // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
+#ifndef TDLT_LAP_BLOCKS
 #pragma unroll 1
   for (int lv = (TDLT_ABLATE & 1) ? 64 : 8; lv <= sb; lv <<= 1) {
     region_lap_rows<true>(s.A, s.msk, lv, sb, warp, lane, last_r);
@@ -324,6 +325,12 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     region_lap_cols<true>(s.A, s.msk, lv, sb, warp, lane);
     __syncthreads();
   }
+#else
+  if (!(TDLT_ABLATE & 1)) {
+    region_lap_blocks<true>(s.A, s.ub, sb, warp, lane, last_r ? 9 : 8, last_c ? 17 : 16, 8, 16);
+  }
+  __syncthreads();
+#endif
   TDLT_MARK(t, 7);
   // ---- store the owned rectangle: buffer row b <-> plane row Y0 - 2 + b ---------
   // The owned columns cs .. ce-1 (cs = -2, or 0 in the first region column; ce = 126,
