@@ -128,19 +128,29 @@ def cpu_reference_run(pic_w, pic_h, kind, steps, warmup, budget_s=20.0):
     nthreads = max(1, min(cores, 32))
     rng = np.random.default_rng(11)
     maps = make_maps_np(kind, 1, nhsb, nvsb, 7)[0]
-    planes = [rng.integers(-2048, 2048, size=(fh >> d, fw >> d)).astype(np.int32) for d in DECS]
+    pix = [rng.integers(0, 256, size=(fh >> d, fw >> d)).astype(np.uint8) for d in DECS]
+    lib = ol.ref() if use_ref else ol.port()
+    to_coeff = lib.ref_buf_to_coeff if use_ref else lib.oc_buf_to_coeff
+    to_buf = lib.ref_coeff_to_buf if use_ref else lib.oc_coeff_to_buf
 
     def make_worker():
         ctx = ol.RefCtx(pic_w, pic_h) if use_ref else None
+        cbuf = [np.empty(p.shape, np.int32) for p in pix]
+        obuf = [np.empty_like(p) for p in pix]
 
         def one_frame():
+            # pixels -> od_coeff (src/state.c:1209), forward stage, inverse stage,
+            # od_coeff -> pixels (:1274): SURVEY 8d's CPU baseline, one frame
             for p, dec in enumerate(DECS):
+                h, w = pix[p].shape
+                to_coeff(1, ol.ptr(cbuf[p]), w, 0, ol.ptr(pix[p]), 1, w, w, h)
                 if ctx:
-                    d, _ = ctx.fwd_plane(planes[p], maps, dec, 1, impl=1)
-                    ctx.inv_plane(d, maps, dec, 1, impl=1)
+                    d, _ = ctx.fwd_plane(cbuf[p], maps, dec, 1, impl=1)
+                    c2 = ctx.inv_plane(d, maps, dec, 1, impl=1)
                 else:
-                    d, _ = ol.port_fwd_plane(planes[p], maps, dec, pic_w, pic_h, 1)
-                    ol.port_inv_plane(d, maps, dec, pic_w, pic_h, 1)
+                    d, _ = ol.port_fwd_plane(cbuf[p], maps, dec, pic_w, pic_h, 1)
+                    c2 = ol.port_inv_plane(d, maps, dec, pic_w, pic_h, 1)
+                to_buf(1, ol.ptr(obuf[p]), 1, w, ol.ptr(c2), w, 0, w, h)
         return one_frame
 
     workers = [make_worker() for _ in range(nthreads)]
@@ -169,8 +179,9 @@ def cpu_reference_run(pic_w, pic_h, kind, steps, warmup, budget_s=20.0):
     mpix = pic_w * pic_h * frames / el / 1e6
     return {"value": mpix, "unit": "Mpixel/s", "cores": nthreads,
             "kind": "reference" if use_ref else "port",
-            "sample": "%d frames of %dx%d per step (%d threads x %d), fwd+inv, gcc -O2, "
-                      "x86 SIMD dispatch for 4x4/8x8" % (frames, pic_w, pic_h, nthreads, per_thread),
+            "sample": "%d frames of %dx%d per step (%d threads x %d), 8-bit pixels -> coeff -> fwd -> inv -> "
+                      "pixels, gcc -O2, x86 SIMD dispatch for 4x4/8x8" % (frames, pic_w, pic_h, nthreads,
+                                                                            per_thread),
             "ms_per_step": el * 1e3, "host_cores": cores}
 
 
@@ -326,23 +337,28 @@ def main():
         except Exception:
             pass
 
-    # end to end: host (pinned) buffers through the frame-level C-ABI calls
+    # end to end: host (pinned) buffers through the frame-level C-ABI calls the codec would
+    # make: 8-bit reference-buffer pixels in -> od_coeff d out (encoder side), d in -> pixels
+    # out (decoder side); every byte crosses PCIe inside the timed region
     e2e = None
     if not args.no_e2e:
-        hc = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
+        hp = [torch.empty(t.shape, dtype=torch.uint8, pin_memory=True) for t in c]
         hd = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
-        hc2 = [torch.empty(t.shape, dtype=torch.int32, pin_memory=True) for t in c]
-        for a, b in zip(hc, c):
-            a.copy_(b)
+        hp2 = [torch.empty(t.shape, dtype=torch.uint8, pin_memory=True) for t in c]
+        for a_, b_ in zip(hp, c):
+            a_.copy_(((b_ >> 4) + 128).clamp_(0, 255).to(torch.uint8))
         hmaps = torch.from_numpy(maps_np).pin_memory()
         L = ctx.L
         arr = daala_b200._ptr_array
+        import ctypes as C
+        ys = (C.c_int * 4)(*[t.shape[2] for t in hp] + [0] * (4 - len(hp)))
+        fs = (C.c_longlong * 4)(*[t.shape[1] * t.shape[2] for t in hp] + [0] * (4 - len(hp)))
 
         def e2e_step():
-            rc = L.od_tdlt_fwd_frames(ctx._h, arr([x.data_ptr() for x in hd]), arr([x.data_ptr() for x in hc]),
-                                      hmaps.data_ptr(), nframes, FL)
-            rc |= L.od_tdlt_inv_frames(ctx._h, arr([x.data_ptr() for x in hc2]), arr([x.data_ptr() for x in hd]),
-                                       hmaps.data_ptr(), nframes, FL)
+            rc = L.od_tdlt_fwd_frames_pix(ctx._h, arr([x.data_ptr() for x in hd]), arr([x.data_ptr() for x in hp]),
+                                          ys, fs, hmaps.data_ptr(), nframes, FL, 1, 1, 0)
+            rc |= L.od_tdlt_inv_frames_pix(ctx._h, arr([x.data_ptr() for x in hp2]), ys, fs,
+                                           arr([x.data_ptr() for x in hd]), hmaps.data_ptr(), nframes, FL, 1, 1, 0)
             if rc:
                 raise SystemExit("e2e call failed: %s" % L.od_tdlt_last_error(ctx._h).decode())
 
@@ -356,13 +372,15 @@ def main():
         el = time.perf_counter() - t0
         el_ms, frames_e2e = reduce_timing(dist, el * 1e3, nframes, dev)
         el = el_ms * 1e-3
-        if not all(torch.equal(a, b) for a, b in zip(hc, hc2)):
+        if not all(torch.equal(a_, b_) for a_, b_ in zip(hp, hp2)):
             raise SystemExit("bench.py: e2e round trip mismatch")
-        plane_bytes = 4 * samples_per_frame * nframes
+        coeff_bytes = 4 * samples_per_frame * nframes
+        pix_bytes = samples_per_frame * nframes
         e2e = {"value": pic_w * pic_h * frames_e2e * e2e_steps / el / 1e6, "unit": "Mpixel/s",
-               "h2d_bytes_per_step": 2 * plane_bytes + 2 * maps_np.nbytes,
-               "d2h_bytes_per_step": 2 * plane_bytes, "steps": e2e_steps,
-               "api": "od_tdlt_fwd_frames + od_tdlt_inv_frames (pinned host od_coeff planes)"}
+               "h2d_bytes_per_step": pix_bytes + coeff_bytes + 2 * maps_np.nbytes,
+               "d2h_bytes_per_step": coeff_bytes + pix_bytes, "steps": e2e_steps,
+               "api": "od_tdlt_fwd_frames_pix (8-bit pixels -> od_coeff) + od_tdlt_inv_frames_pix "
+                      "(od_coeff -> 8-bit pixels), pinned host buffers, synchronous calls"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
