@@ -236,6 +236,9 @@ def main():
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version banner (printed to stdout
+        # at NCCL_DEBUG=VERSION / INFO) out of it
+        os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
