@@ -281,6 +281,8 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()          # samples through warm-up and the timed region: always under load
     for _ in range(args.warmup):
         fwd()
         inv()
@@ -290,9 +292,7 @@ def main():
         raise SystemExit("bench.py: round trip is not the identity -- refusing to report a number")
 
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
-    sampler = ClockSampler(local_rank)
     barrier()
-    sampler.start()
     l0 = daala_b200.launch_count()
     ev[0].record()
     for k in range(args.steps):
@@ -302,6 +302,13 @@ def main():
         ev[2 * k + 2].record()
     torch.cuda.synchronize()
     launches = daala_b200.launch_count() - l0
+    # a short timed region may end before nvidia-smi's first sample: keep the same load
+    # running (untimed) until a few samples are in
+    t_end = time.perf_counter() + 1.5
+    while len(sampler.lines) < 4 and time.perf_counter() < t_end:
+        fwd()
+        inv()
+        torch.cuda.synchronize()
     clocks = sampler.stop()
     barrier()
     total_ms = ev[0].elapsed_time(ev[-1])
