@@ -23,8 +23,7 @@ struct od_tdlt_ctx {
   int device;
   int max_frames;
   int fw, fh, nhsb, nvsb;
-  BatchDesc bd;                 // template: nframes / flags filled per call
-  RegionBatch rb;               // the same for the region kernels
+  RegionBatch rb;               // template: nframes / flags filled per call
   long long plane_size[kMaxPlanes];
   // strip exchange of the inverse kernel
   int2 *strips;                 // (sample, epoch) pairs, kRegionStripInts per region
@@ -121,31 +120,12 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
   ctx->fh = (g->pic_height + 63) & ~63;
   ctx->nhsb = ctx->fw >> 5;
   ctx->nvsb = ctx->fh >> 5;
-  BatchDesc &bd = ctx->bd;
-  bd.nplanes = g->nplanes;
-  bd.pic_w = g->pic_width;
-  bd.pic_h = g->pic_height;
-  bd.bw = ctx->nhsb*4;
-  bd.bh = ctx->nvsb*4;
-  int tile0 = 0;
-  for (int p = 0; p < g->nplanes; p++) {
-    PlaneDesc &pd = bd.pl[p];
-    pd.dec = g->xdec[p];
-    pd.w = ctx->fw >> pd.dec;
-    pd.h = ctx->fh >> pd.dec;
-    pd.ntx = pd.w/kTile;
-    pd.nty = pd.h/kTile;
-    pd.tile0 = tile0;
-    tile0 += pd.ntx*pd.nty;
-    ctx->plane_size[p] = (long long)pd.w*pd.h;
-  }
-  bd.tiles_per_frame = tile0;
   RegionBatch &rb = ctx->rb;
   rb.nplanes = g->nplanes;
   rb.pic_w = g->pic_width;
   rb.pic_h = g->pic_height;
-  rb.bw = bd.bw;
-  rb.bh = bd.bh;
+  rb.bw = ctx->nhsb*4;
+  rb.bh = ctx->nvsb*4;
   int reg0 = 0;
   for (int p = 0; p < g->nplanes; p++) {
     RegionPlane &rp = rb.pl[p];
@@ -157,6 +137,7 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     rp.reg0 = reg0;
     rp.inv_nrx = 1.0f/(float)rp.nrx;
     reg0 += rp.nrx*rp.nry;
+    ctx->plane_size[p] = (long long)rp.w*rp.h;
   }
   rb.regs_per_frame = reg0;
   *out = ctx;
@@ -191,7 +172,7 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
              cudaMalloc(&ctx->dev_d[p], bytes) == cudaSuccess &&
              cudaMalloc(&ctx->dev_pix[p], (size_t)ctx->plane_size[p]*max_frames*2) == cudaSuccess;
       }
-      ok = ok && cudaMalloc(&ctx->dev_bsize, (size_t)bd.bw*bd.bh*max_frames) == cudaSuccess;
+      ok = ok && cudaMalloc(&ctx->dev_bsize, (size_t)rb.bw*rb.bh*max_frames) == cudaSuccess;
       if (!ok) { rc = OD_TDLT_EFAULT; break; }
     }
   } while (0);
@@ -233,7 +214,7 @@ int od_tdlt_nvsb(const od_tdlt_ctx *ctx) { return ctx->nvsb; }
 long long od_tdlt_plane_size(const od_tdlt_ctx *ctx, int pli) {
   return (pli >= 0 && pli < ctx->g.nplanes) ? ctx->plane_size[pli] : 0;
 }
-long long od_tdlt_bsize_size(const od_tdlt_ctx *ctx) { return (long long)ctx->bd.bw*ctx->bd.bh; }
+long long od_tdlt_bsize_size(const od_tdlt_ctx *ctx) { return (long long)ctx->rb.bw*ctx->rb.bh; }
 const char *od_tdlt_last_error(const od_tdlt_ctx *ctx) { return ctx ? ctx->err : "null context"; }
 long long od_tdlt_launch_count(void) { return g_launches.load(); }
 #ifdef TDLT_TRACE

@@ -18,18 +18,9 @@ struct InvOut {
   int *c[kMaxPlanes];
 };
 
-constexpr int kCtaSmemBytes = kWarpsPerCta*(kBBytes + kAAlloc + kLsBytes + 8);
-constexpr int kCtaSmemAlloc = kCtaSmemBytes + 16;   // + the inverse kernel's ticket slot
-
 __global__ void tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ bsize);
-__global__ void tdlt_inv_kernel(const __grid_constant__ TmapSet maps,
-                                const __grid_constant__ BatchDesc bd,
-                                const unsigned char *__restrict__ bsize, InvOut out,
-                                int *__restrict__ strips, int *__restrict__ flags,
-                                int *__restrict__ ticket, int epoch);
-
 __global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ bsize, InvOut out,
