@@ -234,15 +234,20 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.flags = flags;
+  PlanePtrs out;
+  memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
+    if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
+    }
     int rc = make_tmap(ctx, &maps.in[p], c[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
     if (rc) return rc;
-    rc = make_tmap(ctx, &maps.out[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kTile, kTile, true);
-    if (rc) return rc;
+    out.p[p] = d[p];
   }
   if (nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes > 65535");
   dim3 grid((unsigned)rb.regs_per_frame, (unsigned)nframes);
-  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(maps, rb, bsize);
+  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(maps, rb, bsize,
+                                                                                    out);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
@@ -267,17 +272,18 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
   CK(ctx, cudaSetDevice(ctx->device));
-  TmapSet maps;
-  memset(&maps, 0, sizeof(maps));
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.flags = flags;
-  InvOut out;
+  PlanePtrs in, out;
+  memset(&in, 0, sizeof(in));
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
-    int rc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kTile, kTile, true);
-    if (rc) return rc;
-    out.c[p] = c[p];
+    if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
+    }
+    in.p[p] = const_cast<od_coeff *>(d[p]);
+    out.p[p] = c[p];
   }
   long long total = (long long)rb.regs_per_frame*nframes;
   int rc = ensure_scratch(ctx, total);
@@ -286,7 +292,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
   tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      maps, rb, bsize, out, ctx->strips, ctx->ticket, ctx->epoch);
+      rb, bsize, in, out, ctx->strips, ctx->ticket, ctx->epoch);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

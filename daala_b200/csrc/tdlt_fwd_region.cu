@@ -3,8 +3,10 @@
 //   (:1486-1510), leaf DCTs (src/dct.c), keyframe Haar-DC merge
 //   (src/encode.c:1286-1343); lossless mode: od_haar (src/dct.c:1960-1997).
 // One CTA per 128x64 region of one plane; see tdlt_region.cuh for the layout
-// and the task vocabulary.  The input tile needs only INPUT samples from the
-// neighbouring regions (a 2-sample ring), so regions are independent.
+// and the task vocabulary.  A region needs only INPUT samples from its
+// neighbours (a 2-sample ring), so regions are independent.  Everything happens
+// in place in one shared-memory buffer: TMA load with halo -> lapping ->
+// transforms -> DC pyramid -> 16-byte stores.
 #include <cuda.h>
 #include "tdlt_tasks.cuh"
 #include "tdlt_region.cuh"
@@ -16,52 +18,10 @@ namespace tdlt {
 __device__ long long *g_tdlt_trace = nullptr;
 #endif
 
-// ---- lossless mode: multi-level Haar wavelet of each superblock of a tile
-// (reference src/dct.c:1960-1997).  T = the tile's part of A, Y = its B tile.
-__device__ __forceinline__ void region_haar_fwd_tile(int *At, int *Bt, int lane, int sb) {
-  int ln = (sb == 32) ? 5 : 4;
-  int nb = 32/sb;                         // superblocks per tile side
-  for (int level = 0; level < ln; level++) {
-    int np = sb >> level >> 1;
-    int items = nb*nb*np*np;
-    int a[8], b[8], c[8], d[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      int it = lane + 32*k;
-      if (it < items) {
-        int blk = it/(np*np), e = it - blk*np*np;
-        int i = e/np, j = e - i*np;
-        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        a[k] = At[(r0 + 2*i)*kAP + c0 + 2*j];
-        b[k] = At[(r0 + 2*i + 1)*kAP + c0 + 2*j];
-        c[k] = At[(r0 + 2*i)*kAP + c0 + 2*j + 1];
-        d[k] = At[(r0 + 2*i + 1)*kAP + c0 + 2*j + 1];
-      }
-    }
-    __syncwarp();
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      int it = lane + 32*k;
-      if (it < items) {
-        int blk = it/(np*np), e = it - blk*np*np;
-        int i = e/np, j = e - i*np;
-        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        haar2x2(a[k], b[k], c[k], d[k]);
-        At[(r0 + i)*kAP + c0 + j] = a[k];
-        Bt[b_off(r0 + i, c0 + j + np)] = b[k];
-        Bt[b_off(r0 + i + np, c0 + j)] = c[k];
-        Bt[b_off(r0 + i + np, c0 + j + np)] = d[k];
-        if (np == 1) Bt[b_off(r0, c0)] = a[k];
-      }
-    }
-    __syncwarp();
-  }
-}
-
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
-                       const unsigned char *__restrict__ bsize) {
+                       const unsigned char *__restrict__ bsize, PlanePtrs out) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 0);
@@ -104,12 +64,11 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
 #endif
     }
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 4);
-    // ---- transforms ---------------------------------------------------------
+    // ---- transforms, in place: columns first, then rows (src/dct.c:137-142) ----
     if (!(TDLT_ABLATE & 2)) {
       const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
       const int q0 = (n0 + 15) >> 4, q1 = (n1 + 15) >> 4, q2 = (n2 + 3) >> 2;
       const int ntask = q0 + q1 + q2 + n3;
-      unsigned char *Bb = reinterpret_cast<unsigned char *>(s.B);
       int v[32];
 #pragma unroll 1
       for (;;) {
@@ -118,18 +77,16 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
         if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ntask) break;
-        if (g < n3) {
+        if (g < n3 && !(TDLT_ABLATE & 256)) {
           // 32x32: lane = column, then lane = row
           int e = s.tasks[3*kTaskListStride + g];
-          int UR = e >> 4, UC = e & 15;
-          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+          int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
 #pragma unroll 1
           for (int pass = 0; pass < 2; pass++) {
-            if (pass == 0) a_col32<false>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + lane, v);
-            else b_row32<false>(tile, lane, v);
+            int *line = pass == 0 ? blk + lane : blk + lane*kAP;
+            if (pass == 0) a_col32<false>(line, v); else a_row32<false>(line, v);
             tdlt_fdct32(v);
-            if (pass == 0) b_col32<true>(tile, lane, v);
-            else b_row32<true>(tile, lane, v);
+            if (pass == 0) a_col32<true>(line, v); else a_row32<true>(line, v);
             __syncwarp();
           }
         }
@@ -138,18 +95,14 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
           int idx = (g - n3)*4 + (lane >> 3), k = lane & 7;
           bool on = idx < n2;
           int e = s.tasks[2*kTaskListStride + (on ? idx : 0)];
-          int UR = e >> 4, UC = e & 15;
-          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
-          int r16 = (UR & 2)*8, c16 = (UC & 2)*8;
+          int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
 #pragma unroll 1
           for (int pass = 0; pass < 2; pass++) {
             if (on) {
-              if (pass == 0) a_cols16<false>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 2*k, v);
-              else b_rows16<false>(tile, r16, c16, k, v);
+              if (pass == 0) a_cols16<false>(blk + 2*k, v); else a_rows16<false>(blk, k, v);
               tdlt_fdct16(v);
               tdlt_fdct16(v + 16);
-              if (pass == 0) b_cols16<true>(tile, r16, c16, k, v);
-              else b_rows16<true>(tile, r16, c16, k, v);
+              if (pass == 0) a_cols16<true>(blk + 2*k, v); else a_rows16<true>(blk, k, v);
             }
             __syncwarp();
           }
@@ -159,19 +112,15 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
           int idx = (g - n3 - q2)*16 + (lane >> 1), h = lane & 1;
           bool on = idx < n1;
           int e = s.tasks[1*kTaskListStride + (on ? idx : 0)];
-          int UR = e >> 4, UC = e & 15;
-          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
-          int ur = UR & 3, uc = UC & 3;
-          int mu = (uc ^ (lane >> 1)) & 3;
+          int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
+          int mu = ((e & 15) - (lane >> 1)) & 3;
 #pragma unroll 1
           for (int pass = 0; pass < 2; pass++) {
             if (on) {
-              if (pass == 0) ld_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
-              else b_rows8<false>(tile, ur, uc, h, mu, v);
+              if (pass == 0) ld_a_8x4(blk + 4*h, v); else a_rows8<false>(blk, h, mu, v);
 #pragma unroll
               for (int q = 0; q < 4; q++) tdlt_fdct8(v + 8*q);
-              if (pass == 0) b_8x4<true>(tile, ur, uc, h, v);
-              else b_rows8<true>(tile, ur, uc, h, mu, v);
+              if (pass == 0) st_a_8x4(blk + 4*h, v); else a_rows8<true>(blk, h, mu, v);
             }
             __syncwarp();
           }
@@ -183,42 +132,45 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
           bool on = idx < n0;
           int e = s.tasks[on ? idx : 0];
           int UR = e >> 4, UC = e & 15;
-          unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+          int *blk = s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h;
           int bits = on ? s.ub[ut(UR, UC)] : 0;
-          if (on) ld_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+          if (on) ld_a_8x4(blk, v);
           lap4_unit<false>(v, h, bits);
           if (on) {
             fdct4x4_pair(v);
-            b_8x4<true>(tile, UR & 3, UC & 3, h, v);
+            st_a_8x4(blk, v);
           }
         }
       }
     }
-    fence_proxy_async_smem();   // B is read by the TMA store (async proxy) below
     __syncthreads();
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 5);
   }
 
-  // ---- per tile: DC pyramid (or the Haar wavelet), then one TMA store ------
+  // ---- per tile (warp w <-> tile w): DC pyramid (or the Haar wavelet), then the tile
+  // goes out: 4 rows of 128 bytes per warp instruction ---------------------------
   {
     const int tx = warp & 3, ty = warp >> 2;
     const int TX = X0 + 32*tx, TY = Y0 + 32*ty;
     if (TX < pd.w && TY < pd.h) {
-      int *Bt = s.B + warp*(kBBytes/4);
+      int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;
       if (haar) {
-        region_haar_fwd_tile(s.A + (32*ty + 2)*kAP + 32*tx + 4, Bt, lane, 32 >> pd.dec);
+        region_haar_tile<false>(At, lane, 32 >> pd.dec);
       }
       else if ((bd.flags & 1) && !(TDLT_ABLATE & 4)) {
         const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-        region_dc_level<false>(Bt, ls0, lane, 8);
-        region_dc_level<false>(Bt, ls0, lane, 16);
-        if (pd.dec == 0) region_dc_level<false>(Bt, ls0, lane, 32);
+        region_dc_level<false>(At, ls0, lane, 8);
+        region_dc_level<false>(At, ls0, lane, 16);
+        if (pd.dec == 0) region_dc_level<false>(At, ls0, lane, 32);
       }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0 && !(TDLT_ABLATE & 16)) {
-        tma_store_3d(&maps.out[id.pli], Bt, TX, TY, id.frame);
-        tma_store_commit_and_wait_read();
+      if (!(TDLT_ABLATE & 16)) {
+        int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + TY + (lane >> 3))*pd.w + TX + 4*(lane & 7);
+        const int *a = At + (lane >> 3)*kAP + 4*(lane & 7);
+#pragma unroll
+        for (int it = 0; it < 8; it++) {
+          *reinterpret_cast<int4 *>(g + (size_t)(4*it)*pd.w) =
+              *reinterpret_cast<const int4 *>(a + 4*it*kAP);
+        }
       }
     }
   }

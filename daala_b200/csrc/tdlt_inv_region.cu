@@ -2,7 +2,8 @@
 //   keyframe Haar-DC split (reference src/decode.c:697-738), leaf iDCTs
 //   (src/dct.c), split postfilters bottom-up (src/filter.c:1512-1554) and the
 //   SB-edge postfilter (:1588-1646); lossless mode: od_haar_inv (src/dct.c:1999).
-// One CTA per 128x64 region of one plane (tdlt_region.cuh).
+// One CTA per 128x64 region of one plane (tdlt_region.cuh); everything happens in
+// place in one shared-memory buffer.
 //
 // The post-filter of a block edge needs reconstructed samples from both sides
 // of it, so a region cannot finish alone: region (rx, ry) owns the OUTPUT
@@ -16,7 +17,6 @@
 // (CTAs draw tickets in the order they start running, so a region only ever
 // waits on work that is already resident: no deadlock, and on average the
 // producer is ahead because it started first).
-#include <cuda.h>
 #include "tdlt_tasks.cuh"
 #include "tdlt_region.cuh"
 #include "tdlt_kernels.h"
@@ -32,49 +32,6 @@ __device__ __forceinline__ int2 ld_pair(const int2 *p) {
 }
 __device__ __forceinline__ void st_pair(int2 *p, int sample, int epoch) {
   asm volatile("st.volatile.global.v2.s32 [%0], {%1, %2};" :: "l"(p), "r"(sample), "r"(epoch) : "memory");
-}
-
-// ---- lossless mode: inverse multi-level Haar wavelet of each superblock of a
-// tile (reference src/dct.c:1999-2026).  Y = the B tile, output in the tile's
-// part of A.
-__device__ __forceinline__ void region_haar_inv_tile(int *At, int *Bt, int lane, int sb) {
-  int ln = (sb == 32) ? 5 : 4;
-  int nb = 32/sb;
-#pragma unroll 1
-  for (int level = ln - 1; level >= 0; level--) {
-    int np = 1 << (ln - 1 - level);
-    int items = nb*nb*np*np;
-    int a[8], b[8], c[8], d[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      int it = lane + 32*k;
-      if (it < items) {
-        int blk = it/(np*np), e = it - blk*np*np;
-        int i = e/np, j = e - i*np;
-        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        a[k] = (np == 1) ? Bt[b_off(r0, c0)] : At[(r0 + i)*kAP + c0 + j];
-        b[k] = Bt[b_off(r0 + i, c0 + j + np)];
-        c[k] = Bt[b_off(r0 + i + np, c0 + j)];
-        d[k] = Bt[b_off(r0 + i + np, c0 + j + np)];
-      }
-    }
-    __syncwarp();     // every read of the level precedes every write
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      int it = lane + 32*k;
-      if (it < items) {
-        int blk = it/(np*np), e = it - blk*np*np;
-        int i = e/np, j = e - i*np;
-        int r0 = (blk/nb)*sb, c0 = (blk%nb)*sb;
-        haar2x2(a[k], b[k], c[k], d[k]);
-        At[(r0 + 2*i)*kAP + c0 + 2*j] = a[k];
-        At[(r0 + 2*i + 1)*kAP + c0 + 2*j] = b[k];
-        At[(r0 + 2*i)*kAP + c0 + 2*j + 1] = c[k];
-        At[(r0 + 2*i + 1)*kAP + c0 + 2*j + 1] = d[k];
-      }
-    }
-    __syncwarp();
-  }
 }
 
 // The two samples of the ring this thread is responsible for (threads 0..193):
@@ -116,15 +73,25 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
+// One 512-byte (or shorter) row of coefficients, global -> shared, completing on `bar`.
+__device__ __forceinline__ void bulk_row_g2s(void *dst, const void *src, int bytes, void *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
-tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
-                       const __grid_constant__ RegionBatch bd,
-                       const unsigned char *__restrict__ bsize, InvOut out,
+tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ bsize, PlanePtrs in, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
-  if (tid == 0) s.cnt[0] = (TDLT_ABLATE & 64) ? (int)blockIdx.x : atomicAdd(ticket, 1);
+  if (tid == 0) {
+    s.cnt[0] = (TDLT_ABLATE & 64) ? (int)blockIdx.x : atomicAdd(ticket, 1);
+    mbar_init(s.bar, 1);
+    fence_mbar_init();
+  }
   if (tid >= 229) s.cnt[tid - 228] = 0;       // counters (but the ticket) and edge masks
   __syncthreads();
   const int t = s.cnt[0];
@@ -136,19 +103,14 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   const bool haar = (bd.flags & 2) != 0;
   const int sb = 32 >> pd.dec;
 
-  if (tid == 0) {
-    mbar_init(s.bar, 1);
-    fence_mbar_init();
-    int ntiles = 0;
-    for (int k = 0; k < kRegTiles; k++) {
-      ntiles += (X0 + 32*(k & 3) < pd.w && Y0 + 32*(k >> 2) < pd.h) ? 1 : 0;
-    }
-    mbar_expect_tx(s.bar, ntiles*kBBytes);
-    for (int k = 0; k < kRegTiles; k++) {
-      int TX = X0 + 32*(k & 3), TY = Y0 + 32*(k >> 2);
-      if (TX < pd.w && TY < pd.h) {
-        tma_load_3d(s.B + k*(kBBytes/4), &maps.in[id.pli], s.bar, TX, TY, id.frame);
-      }
+  // ---- the region's coefficients, row by row, into the inside of A (the halo is
+  // filled from the neighbours' strips below) -----------------------------------
+  {
+    const int nrows = min(kRegH, pd.h - Y0), rowbytes = 4*min(kRegW, pd.w - X0);
+    if (tid == 0) mbar_expect_tx(s.bar, nrows*rowbytes);
+    if (tid < nrows) {
+      const int *src = in.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + tid)*pd.w + X0;
+      bulk_row_g2s(s.A + (tid + 2)*kAP + 4, src, rowbytes, s.bar);
     }
   }
   // ---- the ring of raw samples from the regions above / left / above-left: one
@@ -168,15 +130,15 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   mbar_wait(s.bar, 0);
   TDLT_MARK(t, 2);
 
-  int *gout = out.c[id.pli] + (size_t)id.frame*pd.w*pd.h;
+  int *gout = out.p[id.pli] + (size_t)id.frame*pd.w*pd.h;
   const int tx = warp & 3, ty = warp >> 2;
   const bool tile_on = X0 + 32*tx < pd.w && Y0 + 32*ty < pd.h;
+  int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;      // warp w <-> tile w
 
   if (haar) {
     // No lapping in lossless mode: every tile is stored where it lies.
     if (tile_on) {
-      int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;
-      region_haar_inv_tile(At, s.B + warp*(kBBytes/4), lane, sb);
+      region_haar_tile<true>(At, lane, sb);
       int *g = gout + (size_t)(Y0 + 32*ty)*pd.w + X0 + 32*tx;
 #pragma unroll 1
       for (int r = 0; r < 32; r++) g[(size_t)r*pd.w + lane] = At[r*kAP + lane];
@@ -186,21 +148,19 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
 
   // ---- keyframe: undo the DC pyramid, top-down --------------------------------
   if ((bd.flags & 1) && tile_on && !(TDLT_ABLATE & 4)) {
-    int *Bt = s.B + warp*(kBBytes/4);
     const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-    if (pd.dec == 0) region_dc_level<true>(Bt, ls0, lane, 32);
-    region_dc_level<true>(Bt, ls0, lane, 16);
-    region_dc_level<true>(Bt, ls0, lane, 8);
+    if (pd.dec == 0) region_dc_level<true>(At, ls0, lane, 32);
+    region_dc_level<true>(At, ls0, lane, 16);
+    region_dc_level<true>(At, ls0, lane, 8);
   }
   __syncthreads();
   TDLT_MARK(t, 3);
 
-  // ---- inverse transforms: rows first, then columns (src/dct.c:144-149) --------
+  // ---- inverse transforms, in place: rows first, then columns (src/dct.c:144-149)
   if (!(TDLT_ABLATE & 2)) {
     const int n0 = s.cnt[4], n1 = s.cnt[5], n2 = s.cnt[6], n3 = s.cnt[7];
     const int q0 = (n0 + 15) >> 4, q1 = (n1 + 15) >> 4, q2 = (n2 + 3) >> 2;
     const int ntask = q0 + q1 + q2 + n3;
-    unsigned char *Bb = reinterpret_cast<unsigned char *>(s.B);
     int v[32];
 #pragma unroll 1
     for (;;) {
@@ -209,17 +169,15 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
       g = __shfl_sync(0xffffffffu, g, 0);
       if (g >= ntask) break;
-      if (g < n3) {
+      if (g < n3 && !(TDLT_ABLATE & 256)) {
         int e = s.tasks[3*kTaskListStride + g];
-        int UR = e >> 4, UC = e & 15;
-        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
-          if (pass == 0) b_row32<false>(tile, lane, v);
-          else b_col32<false>(tile, lane, v);
+          int *line = pass == 0 ? blk + lane*kAP : blk + lane;
+          if (pass == 0) a_row32<false>(line, v); else a_col32<false>(line, v);
           tdlt_idct32(v);
-          if (pass == 0) b_row32<true>(tile, lane, v);
-          else a_col32<true>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + lane, v);
+          if (pass == 0) a_row32<true>(line, v); else a_col32<true>(line, v);
           __syncwarp();
         }
       }
@@ -227,18 +185,14 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
         int idx = (g - n3)*4 + (lane >> 3), k = lane & 7;
         bool on = idx < n2;
         int e = s.tasks[2*kTaskListStride + (on ? idx : 0)];
-        int UR = e >> 4, UC = e & 15;
-        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
-        int r16 = (UR & 2)*8, c16 = (UC & 2)*8;
+        int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
           if (on) {
-            if (pass == 0) b_rows16<false>(tile, r16, c16, k, v);
-            else b_cols16<false>(tile, r16, c16, k, v);
+            if (pass == 0) a_rows16<false>(blk, k, v); else a_cols16<false>(blk + 2*k, v);
             tdlt_idct16(v);
             tdlt_idct16(v + 16);
-            if (pass == 0) b_rows16<true>(tile, r16, c16, k, v);
-            else a_cols16<true>(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 2*k, v);
+            if (pass == 0) a_rows16<true>(blk, k, v); else a_cols16<true>(blk + 2*k, v);
           }
           __syncwarp();
         }
@@ -247,19 +201,15 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
         int idx = (g - n3 - q2)*16 + (lane >> 1), h = lane & 1;
         bool on = idx < n1;
         int e = s.tasks[1*kTaskListStride + (on ? idx : 0)];
-        int UR = e >> 4, UC = e & 15;
-        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
-        int ur = UR & 3, uc = UC & 3;
-        int mu = (uc ^ (lane >> 1)) & 3;
+        int *blk = s.A + (8*(e >> 4) + 2)*kAP + 8*(e & 15) + 4;
+        int mu = ((e & 15) - (lane >> 1)) & 3;
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
           if (on) {
-            if (pass == 0) b_rows8<false>(tile, ur, uc, h, mu, v);
-            else b_8x4<false>(tile, ur, uc, h, v);
+            if (pass == 0) a_rows8<false>(blk, h, mu, v); else ld_a_8x4(blk + 4*h, v);
 #pragma unroll
             for (int q = 0; q < 4; q++) tdlt_idct8(v + 8*q);
-            if (pass == 0) b_rows8<true>(tile, ur, uc, h, mu, v);
-            else st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+            if (pass == 0) a_rows8<true>(blk, h, mu, v); else st_a_8x4(blk + 4*h, v);
           }
           __syncwarp();
         }
@@ -271,14 +221,14 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
         bool on = idx < n0;
         int e = s.tasks[on ? idx : 0];
         int UR = e >> 4, UC = e & 15;
-        unsigned char *tile = Bb + ((UR >> 2)*4 + (UC >> 2))*kBBytes;
+        int *blk = s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h;
         int bits = on ? s.ub[ut(UR, UC)] : 0;
         if (on) {
-          b_8x4<false>(tile, UR & 3, UC & 3, h, v);
+          ld_a_8x4(blk, v);
           idct4x4_pair(v);
         }
         lap4_unit<true>(v, h, bits);
-        if (on) st_a_8x4(s.A + (8*UR + 2)*kAP + 8*UC + 4 + 4*h, v);
+        if (on) st_a_8x4(blk, v);
       }
     }
   }

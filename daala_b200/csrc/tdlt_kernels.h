@@ -7,25 +7,23 @@
 
 namespace tdlt {
 
-// TMA descriptors, one per plane: `in` is read by tiled loads, `out` written
-// by tiled stores (forward only).
+// TMA descriptors of the forward kernel's input planes (3-D: x, y, frame).
 struct TmapSet {
   CUtensorMap in[kMaxPlanes];
-  CUtensorMap out[kMaxPlanes];
 };
 
-struct InvOut {
-  int *c[kMaxPlanes];
+// One device pointer per plane (nframes planes each, 16-byte aligned).
+struct PlanePtrs {
+  int *p[kMaxPlanes];
 };
 
 __global__ void tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
-                                       const unsigned char *__restrict__ bsize);
-__global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
-                                       const __grid_constant__ RegionBatch bd,
-                                       const unsigned char *__restrict__ bsize, InvOut out,
-                                       int2 *__restrict__ strips, int *__restrict__ ticket,
-                                       int epoch);
+                                       const unsigned char *__restrict__ bsize, PlanePtrs out);
+__global__ void tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
+                                       const unsigned char *__restrict__ bsize, PlanePtrs in,
+                                       PlanePtrs out, int2 *__restrict__ strips,
+                                       int *__restrict__ ticket, int epoch);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;
 
 }  // namespace tdlt

@@ -18,14 +18,13 @@
 //              class 3: a 32x32 block                           (32 lanes)
 //              every lane always carries 32 samples in registers.
 //
-// Shared memory of a CTA:
-//   B   8 tiles x 4096 B, each in the TMA SWIZZLE_128B pattern (what the tiled
-//       TMA load / store of a 32x32 int32 box produces / consumes)
+// Shared memory of a CTA (39 KB: five CTAs per SM together with 48 registers):
 //   A   68 rows x 140 words: region rows -2..65, columns -4..135 (one TMA box;
 //       the innermost TMA coordinate must be 16-byte aligned, hence 4 columns
 //       of halo where the lapping needs 2; 140 words = 35 16-byte chunks, an
 //       odd number, so that 8 consecutive rows of one chunk column fall in 8
-//       different bank groups)
+//       different bank groups -- for 16-byte accesses along a row AND down a
+//       column, so the two passes of every transform run in place in A)
 //   unit tables (leaf size, edge bits), edge masks, task lists, counters.
 #pragma once
 #include "tdlt_device.cuh"
@@ -48,7 +47,7 @@ extern __device__ long long *g_tdlt_trace;
 // build leaves them at their defaults): minimum CTAs per SM the kernels are compiled
 // for, and phases to skip when measuring what a phase costs (results are then wrong).
 #ifndef TDLT_MINB
-#define TDLT_MINB 3
+#define TDLT_MINB 5
 #endif
 #ifndef TDLT_ABLATE
 #define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores
@@ -67,9 +66,8 @@ constexpr int kUS = 20;                      // row stride of the unit tables (1
 constexpr int kUTab = kUS*(kRegUY + 2);      // 200 entries: units -1..16 x -1..8
 
 // Shared-memory carve-up (bytes from a 1024-aligned base).
-constexpr int kOffB = 0;
-constexpr int kOffA = kRegTiles*kBBytes;                 // 32768
-constexpr int kOffLs = kOffA + kARegBytes;               // 70848
+constexpr int kOffA = 0;
+constexpr int kOffLs = kOffA + kARegBytes;               // 38080
 constexpr int kOffUb = kOffLs + kUTab;                   // unit edge bits
 constexpr int kOffTasks = kOffUb + kUTab;
 constexpr int kTaskListStride = 128;                     // bytes per class list
@@ -77,8 +75,8 @@ constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints
 constexpr int kOffMsk = kOffCnt + 32;                    // 2 x 10 edge masks, right after cnt
 constexpr int kOffBar = kOffMsk + 80;
 constexpr int kRegSmemBytes = kOffBar + 16;
-static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0, "alignment");
-static_assert(kRegSmemBytes <= 76800, "three CTAs per SM need <= 75 KB each");
+static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0 && kOffLs % 16 == 0, "alignment");
+static_assert(5*(kRegSmemBytes + 1024) <= 232448, "five CTAs per SM");
 
 struct RegionPlane {
   int w, h;          // plane size in samples
@@ -121,7 +119,6 @@ __device__ __forceinline__ RegionId decode_region(const RegionBatch &bd, int fra
 }
 
 struct RegionSmem {
-  int *B;
   int *A;
   unsigned char *ls;      // leaf log-size per unit, 0xFF outside the plane
   unsigned char *ub;      // edge bits per unit (kUb*)
@@ -133,7 +130,6 @@ struct RegionSmem {
 
 __device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
   RegionSmem s;
-  s.B = reinterpret_cast<int *>(base + kOffB);
   s.A = reinterpret_cast<int *>(base + kOffA);
   s.ls = base + kOffLs;
   s.ub = base + kOffUb;
@@ -526,18 +522,16 @@ __device__ __forceinline__ void lap4_unit(int *v, int h, int bits) {
 
 // ---------------------------------------------------------------------------
 // Transform tasks.  A unit is named by its region unit coordinates (UR, UC),
-// UR in 0..7, UC in 0..15; a task list entry is (UR << 4) | UC.
-//   A side: sample (r, c) of the region at A[(r + 2)*kAP + c + 4]
-//   B side: tile (UR >> 2)*4 + (UC >> 2); inside a tile the byte address of
-//           sample (r, c) is r*128 + (((c >> 2) ^ (r & 7)) << 4) + (c & 3)*4.
-// B addresses are formed as   lane constant XOR compile-time constant   (the
-// tile buffers are 4096-byte aligned), one LOP3 per access.
+// UR in 0..7, UC in 0..15; a task list entry is (UR << 4) | UC.  Sample (r, c) of
+// the region lies at A[(r + 2)*kAP + c + 4].  Both passes of a transform run IN
+// PLACE in A: every lane reads the lines it owns into registers, transforms
+// them and writes them back; a __syncwarp separates the passes.  The row pitch
+// of 35 16-byte chunks makes the bank group of chunk (row, q) equal to
+// (3*row + q) mod 8, so eight lanes that read the same chunk column of eight
+// consecutive rows, or eight consecutive chunks of one row, never collide.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ int *b_ptr(unsigned char *base, unsigned x) {
-  return reinterpret_cast<int *>(base + x);
-}
 
-// -- 8 rows x 4 columns from A: element (r, q) <-> v[8*q + r] ----------------
+// -- 8 rows x 4 columns: element (r, q) <-> v[8*q + r] -----------------------
 __device__ __forceinline__ void ld_a_8x4(const int *a, int *v) {
 #pragma unroll
   for (int r = 0; r < 8; r++) {
@@ -552,35 +546,20 @@ __device__ __forceinline__ void st_a_8x4(int *a, const int *v) {
   }
 }
 
-// -- the same strip on B: unit rows 8*ur + r, chunk 2*uc + h ----------------
-// q = byte address of the tile + ur*1024 + ((2*uc + h) << 4)
+// -- rows of an 8x8 block (a -> its origin): register group g (8 words) holds unit row
+//    2*((g + mu) & 3) + h, all 8 columns.  mu = (UC - slot) & 3 rotates the four
+//    independent rows per lane so that the four units of a quarter warp (slot = their
+//    index in it) fall on four different bank groups whatever columns they lie in; the two
+//    lanes of a unit (h) differ in the parity of the group.
 template <bool kStore>
-__device__ __forceinline__ void b_8x4(unsigned char *tile, int ur, int uc, int h, int *v) {
-  unsigned q = (unsigned)(ur*1024) | (unsigned)((2*uc + h) << 4);
+__device__ __forceinline__ void a_rows8(int *a, int h, int mu, int *v) {
 #pragma unroll
-  for (int r = 0; r < 8; r++) {
-    int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)((r << 7) | (r << 4))));
-    if (kStore) *p = make_int4(v[r], v[8 + r], v[16 + r], v[24 + r]);
-    else { int4 t = *p; v[r] = t.x; v[8 + r] = t.y; v[16 + r] = t.z; v[24 + r] = t.w; }
-  }
-}
-
-// -- rows of an 8x8 block on B: register group a (8 words) holds unit row
-//    2*(a ^ mu) + h, all 8 columns.  mu is a per-lane rotation of the four
-//    independent rows that keeps the 8 lanes of a quarter warp on 8 different
-//    bank groups whatever units they hold.
-template <bool kStore>
-__device__ __forceinline__ void b_rows8(unsigned char *tile, int ur, int uc, int h, int mu,
-                                        int *v) {
-  // row7 = (2a) ^ c1, chunk = (j ^ 2a) ^ c2, with c1 = 2mu | h, c2 = 2uc ^ c1
-  unsigned c1 = (unsigned)(2*mu | h), c2 = (unsigned)(2*uc) ^ c1;
-  unsigned q = (unsigned)(ur*1024) | (c1 << 7) | (c2 << 4);
-#pragma unroll
-  for (int a = 0; a < 4; a++) {
+  for (int g = 0; g < 4; g++) {
+    int *row = a + (2*((g + mu) & 3) + h)*kAP;
 #pragma unroll
     for (int j = 0; j < 2; j++) {
-      int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(((2*a) << 7) | ((j ^ (2*a)) << 4))));
-      int *w = v + 8*a + 4*j;
+      int4 *p = reinterpret_cast<int4 *>(row + 4*j);
+      int *w = v + 8*g + 4*j;
       if (kStore) *p = make_int4(w[0], w[1], w[2], w[3]);
       else { int4 t = *p; w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w; }
     }
@@ -597,28 +576,15 @@ __device__ __forceinline__ void a_cols16(int *a, int *v) {   // a -> (row 0, col
     else { int2 t = *p; v[r] = t.x; v[16 + r] = t.y; }
   }
 }
-// r16, c16 in {0, 16}: origin of the block inside its tile
+// lane k holds rows k and k + 8 (v[0..15], v[16..31]); a -> the block's origin
 template <bool kStore>
-__device__ __forceinline__ void b_cols16(unsigned char *tile, int r16, int c16, int k, int *v) {
-  unsigned q = (unsigned)(r16*128) | (unsigned)(((c16 >> 2) + (k >> 1)) << 4) |
-               (unsigned)((k & 1) << 3);
+__device__ __forceinline__ void a_rows16(int *a, int k, int *v) {
 #pragma unroll
-  for (int r = 0; r < 16; r++) {
-    int2 *p = reinterpret_cast<int2 *>(tile + (q ^ (unsigned)((r << 7) | ((r & 7) << 4))));
-    if (kStore) *p = make_int2(v[r], v[16 + r]);
-    else { int2 t = *p; v[r] = t.x; v[16 + r] = t.y; }
-  }
-}
-// lane k holds rows k and k + 8 (v[0..15], v[16..31])
-template <bool kStore>
-__device__ __forceinline__ void b_rows16(unsigned char *tile, int r16, int c16, int k, int *v) {
-  unsigned q = (unsigned)((r16 + k)*128) | (unsigned)(((c16 >> 2) ^ k) << 4);
-#pragma unroll
-  for (int a = 0; a < 2; a++) {
+  for (int g = 0; g < 2; g++) {
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(((8*a) << 7) | (j << 4))));
-      int *w = v + 16*a + 4*j;
+      int4 *p = reinterpret_cast<int4 *>(a + (k + 8*g)*kAP + 4*j);
+      int *w = v + 16*g + 4*j;
       if (kStore) *p = make_int4(w[0], w[1], w[2], w[3]);
       else { int4 t = *p; w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w; }
     }
@@ -634,29 +600,20 @@ __device__ __forceinline__ void a_col32(int *a, int *v) {     // a -> (row 0, co
   }
 }
 template <bool kStore>
-__device__ __forceinline__ void b_col32(unsigned char *tile, int lane, int *v) {
-  unsigned q = (unsigned)((lane >> 2) << 4) | (unsigned)((lane & 3) << 2);
-#pragma unroll
-  for (int r = 0; r < 32; r++) {
-    int *p = reinterpret_cast<int *>(tile + (q ^ (unsigned)((r << 7) | ((r & 7) << 4))));
-    if (kStore) *p = v[r]; else v[r] = *p;
-  }
-}
-template <bool kStore>
-__device__ __forceinline__ void b_row32(unsigned char *tile, int lane, int *v) {
-  unsigned q = (unsigned)(lane << 7) | (unsigned)((lane & 7) << 4);
+__device__ __forceinline__ void a_row32(int *a, int *v) {     // a -> (row lane, column 0)
 #pragma unroll
   for (int j = 0; j < 8; j++) {
-    int4 *p = reinterpret_cast<int4 *>(tile + (q ^ (unsigned)(j << 4)));
+    int4 *p = reinterpret_cast<int4 *>(a + 4*j);
     if (kStore) *p = make_int4(v[4*j], v[4*j + 1], v[4*j + 2], v[4*j + 3]);
     else { int4 t = *p; v[4*j] = t.x; v[4*j + 1] = t.y; v[4*j + 2] = t.z; v[4*j + 3] = t.w; }
   }
 }
 
 // ---- keyframe DC pyramid on one tile (reference src/encode.c:1328-1341,
-// src/decode.c:733).  ls0 -> unit table entry of the tile's first unit.
+// src/decode.c:733).  At -> the tile's origin in A, ls0 -> unit table entry of the
+// tile's first unit.
 template <bool kInverse>
-__device__ __forceinline__ void region_dc_level(int *Bt, const unsigned char *ls0, int lane,
+__device__ __forceinline__ void region_dc_level(int *At, const unsigned char *ls0, int lane,
                                                 int n) {
   int per = 32/n;
   if (lane < per*per) {
@@ -664,14 +621,66 @@ __device__ __forceinline__ void region_dc_level(int *Bt, const unsigned char *ls
     int lsz = ls0[(r0 >> 3)*kUS + (c0 >> 3)];
     if ((4 << lsz) < n) {
       int hn = n >> 1;
-      int o0 = b_off(r0, c0), o1 = b_off(r0, c0 + hn);
-      int o2 = b_off(r0 + hn, c0), o3 = b_off(r0 + hn, c0 + hn);
-      int x0 = Bt[o0], x1 = Bt[o1], x2 = Bt[o2], x3 = Bt[o3];
+      int *p = At + r0*kAP + c0;
+      int x0 = p[0], x1 = p[hn], x2 = p[hn*kAP], x3 = p[hn*kAP + hn];
       if (kInverse) haar2x2(x0, x1, x2, x3); else haar2x2(x0, x2, x1, x3);
-      Bt[o0] = x0; Bt[o1] = x1; Bt[o2] = x2; Bt[o3] = x3;
+      p[0] = x0; p[hn] = x1; p[hn*kAP] = x2; p[hn*kAP + hn] = x3;
     }
   }
   __syncwarp();
+}
+
+// ---- lossless mode: the multi-level Haar wavelet of each superblock of a tile, in
+// place (reference src/dct.c:1960-2026).  At -> the tile's origin in A.  Every level
+// reads its 2x2 groups into registers before it writes anything.
+template <bool kInverse>
+__device__ __forceinline__ void region_haar_tile(int *At, int lane, int sb) {
+  const int ln = (sb == 32) ? 5 : 4;
+  const int nb = 32/sb;                   // superblocks per tile side
+#pragma unroll 1
+  for (int step = 0; step < ln; step++) {
+    const int level = kInverse ? ln - 1 - step : step;
+    const int np = sb >> level >> 1;      // half the side of this level's input
+    const int items = nb*nb*np*np;
+    int a[8], b[8], c[8], d[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int it = lane + 32*k;
+      if (it < items) {
+        int blk = it/(np*np), e = it - blk*np*np;
+        int i = e/np, j = e - i*np;
+        int *q = At + (blk/nb)*sb*kAP + (blk%nb)*sb;
+        if (!kInverse) {
+          a[k] = q[2*i*kAP + 2*j];       b[k] = q[(2*i + 1)*kAP + 2*j];
+          c[k] = q[2*i*kAP + 2*j + 1];   d[k] = q[(2*i + 1)*kAP + 2*j + 1];
+        }
+        else {
+          a[k] = q[i*kAP + j];           b[k] = q[i*kAP + j + np];
+          c[k] = q[(i + np)*kAP + j];    d[k] = q[(i + np)*kAP + j + np];
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int it = lane + 32*k;
+      if (it < items) {
+        int blk = it/(np*np), e = it - blk*np*np;
+        int i = e/np, j = e - i*np;
+        int *q = At + (blk/nb)*sb*kAP + (blk%nb)*sb;
+        haar2x2(a[k], b[k], c[k], d[k]);
+        if (!kInverse) {
+          q[i*kAP + j] = a[k];           q[i*kAP + j + np] = b[k];
+          q[(i + np)*kAP + j] = c[k];    q[(i + np)*kAP + j + np] = d[k];
+        }
+        else {
+          q[2*i*kAP + 2*j] = a[k];       q[(2*i + 1)*kAP + 2*j] = b[k];
+          q[2*i*kAP + 2*j + 1] = c[k];   q[(2*i + 1)*kAP + 2*j + 1] = d[k];
+        }
+      }
+    }
+    __syncwarp();
+  }
 }
 
 }  // namespace tdlt
