@@ -140,6 +140,7 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     ctx->plane_size[p] = (long long)rp.w*rp.h;
   }
   rb.regs_per_frame = reg0;
+  rb.inv_rpf = 1.0f/(float)reg0;
   *out = ctx;
   int rc = OD_TDLT_SUCCESS;
   do {

@@ -109,6 +109,15 @@ __device__ __forceinline__ void mbar_wait(void *bar, int parity) {
       "DONE_%=:\n"
       "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// Barrier `id` (1..15) among `nthreads` threads (whole warps) of the CTA.
+__device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+// Non-blocking arrival at barrier `id`, which completes when `nthreads` threads have
+// arrived (bar.arrive) or are waiting (bar.sync).
+__device__ __forceinline__ void bar_arrive_named(int id, int nthreads) {
+  asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
 // 3-D tiled load: coordinates (x, y, frame), innermost first.
 __device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, void *bar,
                                             int x, int y, int z) {

@@ -96,8 +96,13 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
   __syncthreads();
   const int t = s.cnt[0];
   TDLT_MARK(t, 0);
-  const int frame = t / bd.regs_per_frame;
-  const RegionId id = decode_region(bd, frame, t - frame*bd.regs_per_frame);
+  // t / regs_per_frame by a float estimate and one correction step (exact: the
+  // estimate is within 1 of the quotient for every t < 2^31)
+  int frame = __float2int_rz(__int2float_rz(t)*bd.inv_rpf);
+  int rloc = t - frame*bd.regs_per_frame;
+  if (rloc < 0) { frame--; rloc += bd.regs_per_frame; }
+  else if (rloc >= bd.regs_per_frame) { frame++; rloc -= bd.regs_per_frame; }
+  const RegionId id = decode_region(bd, frame, rloc);
   const RegionPlane &pd = bd.pl[id.pli];
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
   const bool haar = (bd.flags & 2) != 0;
@@ -295,19 +300,22 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
     const int c0 = cs + 2*lane, c1 = c0 + 64;
     const bool on0 = c0 < ce, on1 = c1 < ce;
     const bool on2 = c0 + 128 < ce;     // lane 0 of the last region column: columns 126, 127
-    const size_t pitch = (size_t)pd.w;
-    int *grow = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pitch + X0 + c0;
+    const bool any2 = last_c && id.rx > 0;                // warp-uniform
+    const size_t pitch8 = (size_t)pd.w*kRegWarps;
+    int *gr = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pd.w + X0 + c0;
     const int *arow = s.A + (b0 + warp)*kAP + 4 + c0;
     const int nb = b1 - b0 - warp;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
       if (kRegWarps*k < nb) {
         const int *ar = arow + k*kRegWarps*kAP;
-        int *gr = grow + (size_t)(k*kRegWarps)*pitch;
         if (TDLT_ABLATE & 128) continue;
         if (on0) *reinterpret_cast<int2 *>(gr) = *reinterpret_cast<const int2 *>(ar);
         if (on1) *reinterpret_cast<int2 *>(gr + 64) = *reinterpret_cast<const int2 *>(ar + 64);
-        if (on2) *reinterpret_cast<int2 *>(gr + 128) = *reinterpret_cast<const int2 *>(ar + 128);
+        if (any2 && on2) {
+          *reinterpret_cast<int2 *>(gr + 128) = *reinterpret_cast<const int2 *>(ar + 128);
+        }
+        gr += pitch8;
       }
     }
   }

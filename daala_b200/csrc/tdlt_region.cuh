@@ -90,6 +90,7 @@ struct RegionBatch {
   RegionPlane pl[kMaxPlanes];
   int nplanes;
   int regs_per_frame;
+  float inv_rpf;          // 1 / regs_per_frame
   int nframes;
   int pic_w, pic_h;      // LUMA picture size (gates the split filters)
   int bw, bh;            // block-size map: entries across / down (8x8 luma units)
@@ -301,7 +302,8 @@ template <bool kInverse>
 __device__ __forceinline__ void region_lap_cols(int *A, const unsigned *msk, int lv, int sb,
                                                 int warp, int lane) {
   const bool top = lv == sb;
-  const int nlines = top ? kRegH/sb + (kInverse ? 0 : 1) : (kRegH/2)/lv;
+  const int lg = 31 - __clz(lv);                            // lv and sb are powers of two
+  const int nlines = top ? (kRegH >> lg) + (kInverse ? 0 : 1) : (kRegH/2) >> lg;
   const int first = top ? 0 : lv, step = top ? sb : 2*lv;
   const int nextra = kInverse ? 1 : (top ? 2 : 0);         // extra chunks per line
   if (warp < nlines) {
@@ -341,17 +343,19 @@ __device__ __forceinline__ void lap_row_pair(int *arow, unsigned m, int ja, int 
 }
 template <bool kInverse>
 __device__ __forceinline__ void region_lap_rows(int *A, const unsigned *msk, int lv, int sb,
-                                                int warp, int lane, bool last_row) {
+                                                int warp, int lane, bool last_row,
+                                                int nw = kRegWarps) {
   const bool top = lv == sb;
-  const int nlines = top ? kRegW/sb + (kInverse ? 0 : 1) : (kRegW/2)/lv;
+  const int lg = 31 - __clz(lv);
+  const int nlines = top ? (kRegW >> lg) + (kInverse ? 0 : 1) : (kRegW/2) >> lg;
   const int jfirst = top ? 0 : lv >> 3, jstep = top ? sb >> 3 : lv >> 2;
-  const int row = 32*(warp & 1) + lane + (kInverse ? 0 : 2);    // buffer row = region row + 2
-  int *arow = A + row*kAP;
-  const unsigned m = msk[10 + ((row - 2) >> 3) + 1];
+  // work item i = (line pair i >> 1, upper / lower 32 rows i & 1), dealt to nw warps
 #pragma unroll 1
-  for (int pr = warp >> 1; 2*pr < nlines; pr += kRegWarps/2) {
-    int ja = jfirst + 2*pr*jstep;
-    lap_row_pair<kInverse>(arow, m, ja, ja + jstep, 2*pr + 1 < nlines);
+  for (int i = warp; i < ((nlines + 1) & ~1); i += nw) {
+    const int row = 32*(i & 1) + lane + (kInverse ? 0 : 2);     // buffer row = region row + 2
+    const unsigned m = msk[10 + ((row - 2) >> 3) + 1];
+    int ja = jfirst + (i & ~1)*jstep;
+    lap_row_pair<kInverse>(A + row*kAP, m, ja, ja + jstep, (i | 1) < nlines);
   }
   if (kInverse && last_row && warp == 0 && lane < 2) {
     int *arow2 = A + (64 + lane)*kAP;

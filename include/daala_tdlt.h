@@ -83,6 +83,8 @@ const char *od_tdlt_last_error(const od_tdlt_ctx *ctx);
    c[pli], d[pli]: DEVICE pointers to nframes contiguous planes
    ([frame][row][col], row stride = frame_width>>xdec, no padding -- the
    reference's ctmp/dtmp layout, src/state.c:409-428, repeated per frame).
+   Every plane pointer must be 16-byte aligned (cudaMalloc gives 256), else
+   OD_TDLT_EINVAL; c and d must not overlap.
    bsize: DEVICE pointer, nframes maps of od_tdlt_bsize_size() bytes.
    stream: a cudaStream_t (NULL = default stream).  Asynchronous.
 
