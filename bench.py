@@ -273,7 +273,8 @@ def main():
         ctx.fwd_batch(dp, cp, maps.data_ptr(), nframes, FL, stream)
 
     def inv():
-        ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, FL, stream)
+        # same maps as the forward call just before: its per-region plan is reused
+        ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, FL | daala_b200.OD_TDLT_SAME_MAPS, stream)
 
     def barrier():
         torch.cuda.synchronize()

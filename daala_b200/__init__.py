@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("DAALA_TDLT_LIB", os.path.join(_HERE, "libdaala_tdlt_c
 
 OD_TDLT_KEYFRAME = 1
 OD_TDLT_HAAR = 2
+OD_TDLT_SAME_MAPS = 4
 NPLANES_MAX = 4
 
 

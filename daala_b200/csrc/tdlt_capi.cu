@@ -28,6 +28,11 @@ struct od_tdlt_ctx {
   // strip exchange of the inverse kernel
   int2 *strips;                 // (sample, epoch) pairs, kRegionStripInts per region
   int *ticket;
+  unsigned char *plan;          // kPlanBytes per region of the largest batch so far
+  long long plan_regions;
+  const unsigned char *plan_maps;   // what the records in `plan` were built from
+  int plan_nframes, plan_flags;
+  cudaStream_t plan_stream;
   long long scratch_tiles;
   int epoch;
   // device staging for the host-pointer calls
@@ -198,6 +203,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
+  cudaFree(ctx->plan);
   for (int k = 0; k < kMaxChunks; k++) {
     if (ctx->ev_in[k]) cudaEventDestroy(ctx->ev_in[k]);
     if (ctx->ev_run[k]) cudaEventDestroy(ctx->ev_run[k]);
@@ -224,6 +230,38 @@ int od_tdlt_debug_set_trace(long long *dev_buf) {
 }
 #endif
 
+// Builds the plan records of a batch (one small kernel ahead of either transform
+// kernel, same stream).
+static int launch_plan(od_tdlt_ctx *ctx, const RegionBatch &rb, const unsigned char *bsize,
+                       int nframes, int flags, cudaStream_t st) {
+  if (flags & OD_TDLT_SAME_MAPS) {
+    if (!ctx->plan || ctx->plan_maps != bsize || ctx->plan_nframes != nframes ||
+        ctx->plan_flags != rb.flags || ctx->plan_stream != st) {
+      return fail(ctx, OD_TDLT_EINVAL, "OD_TDLT_SAME_MAPS without a matching previous call");
+    }
+    return OD_TDLT_SUCCESS;
+  }
+  long long total = (long long)rb.regs_per_frame*nframes;
+  if (total > ctx->plan_regions) {
+    CK(ctx, cudaDeviceSynchronize());
+    cudaFree(ctx->plan);
+    ctx->plan = nullptr;
+    ctx->plan_regions = 0;
+    CK(ctx, cudaMalloc(&ctx->plan, (size_t)total*kPlanBytes));
+    ctx->plan_regions = total;
+  }
+  dim3 grid((unsigned)((rb.regs_per_frame + kPlanPerCta - 1)/kPlanPerCta), (unsigned)nframes);
+  tdlt_plan_kernel<<<grid, 192, 0, st>>>(rb, bsize, ctx->plan);
+  g_launches++;
+  ctx->plan_maps = nullptr;
+  CK(ctx, cudaGetLastError());
+  ctx->plan_maps = bsize;
+  ctx->plan_nframes = nframes;
+  ctx->plan_flags = rb.flags;
+  ctx->plan_stream = st;
+  return OD_TDLT_SUCCESS;
+}
+
 // ---------------------------------------------------------------- batches --
 int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
                       const unsigned char *bsize, int nframes, int flags, void *stream) {
@@ -234,7 +272,7 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   memset(&maps, 0, sizeof(maps));
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
-  rb.flags = flags;
+  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
   PlanePtrs out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
@@ -246,9 +284,11 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
     out.p[p] = d[p];
   }
   if (nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes > 65535");
+  int prc = launch_plan(ctx, rb, bsize, nframes, flags, (cudaStream_t)stream);
+  if (prc) return prc;
   dim3 grid((unsigned)rb.regs_per_frame, (unsigned)nframes);
-  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(maps, rb, bsize,
-                                                                                    out);
+  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
+      maps, rb, ctx->plan, out);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
@@ -275,7 +315,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaSetDevice(ctx->device));
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
-  rb.flags = flags;
+  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
   PlanePtrs in, out;
   memset(&in, 0, sizeof(in));
   memset(&out, 0, sizeof(out));
@@ -290,10 +330,13 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   int rc = ensure_scratch(ctx, total);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if (nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes > 65535");
+  rc = launch_plan(ctx, rb, bsize, nframes, flags, st);
+  if (rc) return rc;
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
   tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      rb, bsize, in, out, ctx->strips, ctx->ticket, ctx->epoch);
+      rb, ctx->plan, in, out, ctx->strips, ctx->ticket, ctx->epoch);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

@@ -118,6 +118,13 @@ __device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
 __device__ __forceinline__ void bar_arrive_named(int id, int nthreads) {
   asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
 }
+// 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16),
+// completing on `bar`.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, int bytes, void *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 // 3-D tiled load: coordinates (x, y, frame), innermost first.
 __device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, void *bar,
                                             int x, int y, int z) {

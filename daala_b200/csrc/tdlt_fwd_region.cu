@@ -21,7 +21,7 @@ __device__ long long *g_tdlt_trace = nullptr;
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
-                       const unsigned char *__restrict__ bsize, PlanePtrs out) {
+                       const unsigned char *__restrict__ plan, PlanePtrs out) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 0);
@@ -31,18 +31,20 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
   const bool haar = (bd.flags & 2) != 0;
 
-  if (tid == 0 && !(TDLT_ABLATE & 16)) {
+  // One thread starts both loads: the samples (TMA box with the halo) and the region's
+  // plan record (tdlt_plan.cu), on one mbarrier.
+  if (tid == 0) {
     mbar_init(s.bar, 1);
     fence_mbar_init();
-    mbar_expect_tx(s.bar, kARegBytes);
+    mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
     tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    bulk_g2s(s.ls, plan + ((size_t)blockIdx.y*bd.regs_per_frame + blockIdx.x)*kPlanBytes,
+             kPlanBytes, s.bar);
+    s.dyn[1] = 0;                             // task draw counter
   }
-  if (tid >= 228) s.cnt[tid - 228] = 0;       // counters and edge masks
-  __syncthreads();
-  if (!(TDLT_ABLATE & 8)) region_setup_units(s, bsize, bd, pd, id, tid, lane);
   __syncthreads();
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 1);
-  if (!(TDLT_ABLATE & 16)) mbar_wait(s.bar, 0);
+  mbar_wait(s.bar, 0);
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 2);
 
   if (!haar) {
@@ -74,7 +76,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       for (;;) {
         // longest tasks first; a warp that is done draws the next one
         int g = 0;
-        if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
+        if (lane == 0) g = atomicAdd(s.dyn + 1, 1);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ntask) break;
         if (g < n3 && !(TDLT_ABLATE & 256)) {

@@ -73,28 +73,21 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
-// One 512-byte (or shorter) row of coefficients, global -> shared, completing on `bar`.
-__device__ __forceinline__ void bulk_row_g2s(void *dst, const void *src, int bytes, void *bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-      :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
-                       const unsigned char *__restrict__ bsize, PlanePtrs in, PlanePtrs out,
+                       const unsigned char *__restrict__ plan, PlanePtrs in, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
   if (tid == 0) {
-    s.cnt[0] = (TDLT_ABLATE & 64) ? (int)blockIdx.x : atomicAdd(ticket, 1);
+    s.dyn[0] = (TDLT_ABLATE & 64) ? (int)blockIdx.x : atomicAdd(ticket, 1);
+    s.dyn[1] = 0;                             // task draw counter
     mbar_init(s.bar, 1);
     fence_mbar_init();
   }
-  if (tid >= 229) s.cnt[tid - 228] = 0;       // counters (but the ticket) and edge masks
   __syncthreads();
-  const int t = s.cnt[0];
+  const int t = s.dyn[0];
   TDLT_MARK(t, 0);
   // t / regs_per_frame by a float estimate and one correction step (exact: the
   // estimate is within 1 of the quotient for every t < 2^31)
@@ -112,11 +105,13 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
   // filled from the neighbours' strips below) -----------------------------------
   {
     const int nrows = min(kRegH, pd.h - Y0), rowbytes = 4*min(kRegW, pd.w - X0);
-    if (tid == 0) mbar_expect_tx(s.bar, nrows*rowbytes);
+    if (tid == 0) mbar_expect_tx(s.bar, nrows*rowbytes + kPlanBytes);
     if (tid < nrows) {
       const int *src = in.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + tid)*pd.w + X0;
-      bulk_row_g2s(s.A + (tid + 2)*kAP + 4, src, rowbytes, s.bar);
+      bulk_g2s(s.A + (tid + 2)*kAP + 4, src, rowbytes, s.bar);
     }
+    // ... and the region's plan record (tdlt_plan.cu) on the same mbarrier
+    if (tid == kRegH) bulk_g2s(s.ls, plan + (size_t)t*kPlanBytes, kPlanBytes, s.bar);
   }
   // ---- the ring of raw samples from the regions above / left / above-left: one
   // int2 per thread.  The regions above finished long ago as a rule: their part is
@@ -129,8 +124,6 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
     ring_done = !rs.need || (TDLT_ABLATE & 32);
     if (rs.need && (tid < 128 || tid >= 192)) ring_done = ring_try(rs, epoch);
   }
-  if (!(TDLT_ABLATE & 8)) region_setup_units(s, bsize, bd, pd, id, tid, lane);
-  __syncthreads();
   TDLT_MARK(t, 1);
   mbar_wait(s.bar, 0);
   TDLT_MARK(t, 2);
@@ -171,7 +164,7 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
     for (;;) {
       // longest tasks first; a warp that is done draws the next one
       int g = 0;
-      if (lane == 0) g = atomicAdd(s.cnt + 2, 1);
+      if (lane == 0) g = atomicAdd(s.dyn + 1, 1);
       g = __shfl_sync(0xffffffffu, g, 0);
       if (g >= ntask) break;
       if (g < n3 && !(TDLT_ABLATE & 256)) {

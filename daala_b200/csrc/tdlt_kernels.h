@@ -17,11 +17,15 @@ struct PlanePtrs {
   int *p[kMaxPlanes];
 };
 
+// plan: one kPlanBytes record per region, index frame*regs_per_frame + region
+__global__ void tdlt_plan_kernel(const __grid_constant__ RegionBatch bd,
+                                 const unsigned char *__restrict__ bsize,
+                                 unsigned char *__restrict__ plan);
 __global__ void tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
-                                       const unsigned char *__restrict__ bsize, PlanePtrs out);
+                                       const unsigned char *__restrict__ plan, PlanePtrs out);
 __global__ void tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
-                                       const unsigned char *__restrict__ bsize, PlanePtrs in,
+                                       const unsigned char *__restrict__ plan, PlanePtrs in,
                                        PlanePtrs out, int2 *__restrict__ strips,
                                        int *__restrict__ ticket, int epoch);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;

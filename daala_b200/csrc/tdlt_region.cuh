@@ -65,17 +65,25 @@ constexpr int kRegWarps = kRegThreads/32;
 constexpr int kUS = 20;                      // row stride of the unit tables (18 used)
 constexpr int kUTab = kUS*(kRegUY + 2);      // 200 entries: units -1..16 x -1..8
 
-// Shared-memory carve-up (bytes from a 1024-aligned base).
+// Shared-memory carve-up (bytes from a 1024-aligned base).  The kPlanBytes from
+// kOffLs on are the region's PLAN -- unit tables, task lists, class counts, edge masks
+// -- which depends on the block-size map and the geometry only: tdlt_plan_kernel
+// writes one such record per region to global memory and the transform kernels
+// fetch it with one bulk copy next to the samples.
 constexpr int kOffA = 0;
 constexpr int kOffLs = kOffA + kARegBytes;               // 38080
 constexpr int kOffUb = kOffLs + kUTab;                   // unit edge bits
 constexpr int kOffTasks = kOffUb + kUTab;
 constexpr int kTaskListStride = 128;                     // bytes per class list
-constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints
+constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints, [4..7] = class counts
 constexpr int kOffMsk = kOffCnt + 32;                    // 2 x 10 edge masks, right after cnt
 constexpr int kOffBar = kOffMsk + 80;
-constexpr int kRegSmemBytes = kOffBar + 16;
+constexpr int kPlanBytes = kOffBar - kOffLs;
+constexpr int kPlanPerCta = 4;                           // regions per CTA of tdlt_plan_kernel
+constexpr int kOffDyn = kOffBar + 16;                    // [0] ticket, [1] task draw counter
+constexpr int kRegSmemBytes = kOffDyn + 16;
 static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0 && kOffLs % 16 == 0, "alignment");
+static_assert(kPlanBytes == 1024, "one plan record = 1 KB");
 static_assert(5*(kRegSmemBytes + 1024) <= 232448, "five CTAs per SM");
 
 struct RegionPlane {
@@ -127,6 +135,7 @@ struct RegionSmem {
   int *cnt;               // [4..7] task classes
   unsigned *msk;          // [r]: bit c = unit (r-1, c-1) has kUbTop; [10 + r]: kUbLeft
   unsigned long long *bar;
+  int *dyn;               // [0] ticket (inverse), [1] task draw counter
 };
 
 __device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
@@ -138,6 +147,7 @@ __device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
   s.cnt = reinterpret_cast<int *>(base + kOffCnt);
   s.msk = reinterpret_cast<unsigned *>(base + kOffMsk);
   s.bar = reinterpret_cast<unsigned long long *>(base + kOffBar);
+  s.dyn = reinterpret_cast<int *>(base + kOffDyn);
   return s;
 }
 
@@ -176,18 +186,26 @@ __device__ __forceinline__ void list_push4(T *lists, int stride, int *cnt, int w
 //    src/filter.c:1494-1508).
 // Returns the leaf size (0xFF outside the plane).
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const unsigned char *bsize,
-                                                  const RegionBatch &bd, const RegionPlane &pd,
-                                                  const RegionId &id, int r, int c) {
-  const unsigned char *map = bsize + (size_t)id.frame*bd.bw*bd.bh;
+// Index into the frame's block-size map of grid position (r, c) of the region, or -1
+// outside the plane.
+__device__ __forceinline__ int region_unit_map_index(const RegionBatch &bd, const RegionPlane &pd,
+                                                     const RegionId &id, int r, int c) {
   int uy = id.ry*kRegUY + r - 1;     // plane unit coordinates
   int ux = id.rx*kRegUX + c - 1;
+  if (uy < 0 || ux < 0 || 8*uy >= pd.h || 8*ux >= pd.w) return -1;
+  int my = min(uy << pd.dec, bd.bh - 1);
+  int mx = min(ux << pd.dec, bd.bw - 1);
+  return my*bd.bw + mx;
+}
+// raw = the map byte (ignored when inside is false).
+__device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const RegionBatch &bd,
+                                                  const RegionPlane &pd, const RegionId &id,
+                                                  int r, int c, bool inside, int raw) {
+  int uy = id.ry*kRegUY + r - 1;
+  int ux = id.rx*kRegUX + c - 1;
   int L = 0xFF, bits = 0;
-  if (uy >= 0 && ux >= 0 && 8*uy < pd.h && 8*ux < pd.w) {
-    int my = min(uy << pd.dec, bd.bh - 1);
-    int mx = min(ux << pd.dec, bd.bw - 1);
-    L = map[my*bd.bw + mx];
-    L = (bd.flags & 2) ? 3 : L;
+  if (inside) {
+    L = (bd.flags & 2) ? 3 : raw;
     L = max(L, pd.dec) - pd.dec;
     if (!(bd.flags & 2)) {
       int Y = 8*uy, X = 8*ux;
@@ -227,15 +245,16 @@ __device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const uns
 }
 
 // Threads 0..191 (six whole warps): unit tables, and the transforms of the
-// region sorted into the four task lists.
-__device__ __forceinline__ void region_setup_units(const RegionSmem &s, const unsigned char *bsize,
-                                                   const RegionBatch &bd, const RegionPlane &pd,
-                                                   const RegionId &id, int tid, int lane) {
+// region sorted into the four task lists.  Thread tid < 180 owns grid position
+// (tid / 18, tid % 18); inside / raw as above.
+__device__ __forceinline__ void region_setup_units(const RegionSmem &s, const RegionBatch &bd,
+                                                   const RegionPlane &pd, const RegionId &id,
+                                                   int tid, int lane, bool inside, int raw) {
   if (tid < 192) {
     int which = -1, item = 0;
     if (tid < 18*10) {
       int r = tid/18, c = tid - r*18;
-      int L = region_unit_tables(s, bsize, bd, pd, id, r, c);
+      int L = region_unit_tables(s, bd, pd, id, r, c, inside, raw);
       int UR = r - 1, UC = c - 1;
       if (UR >= 0 && UR < kRegUY && UC >= 0 && UC < kRegUX && !(bd.flags & 2)) {
         if (L == 0 || L == 1) which = L;

@@ -46,6 +46,13 @@ typedef int32_t od_coeff;
                                   inverse: undo it top-down (decode.c:733) */
 #define OD_TDLT_HAAR     (2)   /* lossless mode: od_haar / od_haar_inv instead of
                                   lapping + DCT (encode.c:1304-1306, decode.c:632-634) */
+#define OD_TDLT_SAME_MAPS (4)  /* device batch calls only: bsize, nframes and the mode
+                                  flags are those of the previous batch call on this
+                                  context and stream (an encoder's forward transform
+                                  followed by its reconstruction, encode.c:2492 then
+                                  :2506-2533): the per-region plan built from the maps
+                                  by that call is reused instead of rebuilt.
+                                  OD_TDLT_EINVAL if there is no such plan. */
 
 /* Geometry of a stream; mirrors the fields of daala_info / od_state the path
    reads (reference src/state.c:366-375, 393-394). */

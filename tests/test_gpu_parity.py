@@ -293,3 +293,50 @@ def test_full_size_properties():
         for p in range(3):
             assert np.array_equal(out[p], pix[p])
     chk.close()
+
+
+def test_device_batches_plan_reuse_and_stress():
+    """Device-pointer batch calls on a 16-frame 1080p batch, run three times on the same
+    buffers (the inverse kernel's strip exchange reuses its buffer with a new epoch each
+    launch): identical coefficients every time, exact round trip, frame 0 equal to the
+    checker; OD_TDLT_SAME_MAPS reuses the previous call's plan and is refused when
+    there is none to reuse."""
+    import torch
+    import daala_b200
+    pic_w, pic_h, nframes = 1920, 1080, 16
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(1616)
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        bsize = make_maps("quad", nframes, ctx.nhsb, ctx.nvsb, rng)
+        c_np = _rand_planes(ctx.plane_shapes, nframes, rng)
+        c = [torch.from_numpy(a).to(dev) for a in c_np]
+        d = [torch.empty_like(t) for t in c]
+        c2 = [torch.empty_like(t) for t in c]
+        maps = torch.from_numpy(bsize).to(dev)
+        st = torch.cuda.current_stream().cuda_stream
+        cp, dp, c2p = ([t.data_ptr() for t in x] for x in (c, d, c2))
+        KEY, SAME = daala_b200.OD_TDLT_KEYFRAME, daala_b200.OD_TDLT_SAME_MAPS
+        with pytest.raises(daala_b200.TdltError):
+            ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, KEY | SAME, st)   # nothing to reuse
+        first = None
+        for rep in range(3):
+            ctx.fwd_batch(dp, cp, maps.data_ptr(), nframes, KEY, st)
+            ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, KEY | SAME, st)
+            torch.cuda.synchronize()
+            assert all(torch.equal(a, b) for a, b in zip(c, c2)), "round trip, repetition %d" % rep
+            if first is None:
+                first = [t.clone() for t in d]
+            assert all(torch.equal(a, b) for a, b in zip(first, d))
+        with pytest.raises(daala_b200.TdltError):
+            ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes - 1, KEY | SAME, st)  # other batch
+        # without the flag the inverse builds its own plan
+        for t in c2:
+            t.zero_()
+        ctx.inv_batch(c2p, dp, maps.data_ptr(), nframes, KEY, st)
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b) for a, b in zip(c, c2))
+        d_ref = chk.fwd_frames([a[:1] for a in c_np], bsize[:1], DECS, 1)
+        for p in range(3):
+            assert np.array_equal(d[p][0].cpu().numpy(), d_ref[p][0])
+    chk.close()
