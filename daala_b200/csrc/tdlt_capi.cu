@@ -131,7 +131,7 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
   rb.pic_h = g->pic_height;
   rb.bw = ctx->nhsb*4;
   rb.bh = ctx->nvsb*4;
-  int reg0 = 0;
+  int reg0 = 0, grp0 = 0;
   for (int p = 0; p < g->nplanes; p++) {
     RegionPlane &rp = rb.pl[p];
     rp.dec = g->xdec[p];
@@ -142,10 +142,14 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     rp.reg0 = reg0;
     rp.inv_nrx = 1.0f/(float)rp.nrx;
     reg0 += rp.nrx*rp.nry;
+    rp.ngx = (rp.nrx + kPlanPerCta - 1)/kPlanPerCta;
+    rp.grp0 = grp0;
+    grp0 += rp.ngx*rp.nry;
     ctx->plane_size[p] = (long long)rp.w*rp.h;
   }
   rb.regs_per_frame = reg0;
   rb.inv_rpf = 1.0f/(float)reg0;
+  rb.groups_per_frame = grp0;
   *out = ctx;
   int rc = OD_TDLT_SUCCESS;
   do {
@@ -250,7 +254,7 @@ static int launch_plan(od_tdlt_ctx *ctx, const RegionBatch &rb, const unsigned c
     CK(ctx, cudaMalloc(&ctx->plan, (size_t)total*kPlanBytes));
     ctx->plan_regions = total;
   }
-  dim3 grid((unsigned)((rb.regs_per_frame + kPlanPerCta - 1)/kPlanPerCta), (unsigned)nframes);
+  dim3 grid((unsigned)rb.groups_per_frame, (unsigned)nframes);
   tdlt_plan_kernel<<<grid, 192, 0, st>>>(rb, bsize, ctx->plan);
   g_launches++;
   ctx->plan_maps = nullptr;

@@ -6,10 +6,24 @@
 // (layout: tdlt_region.cuh, kOffLs .. kOffBar).  It depends on the block-size map and
 // the geometry only, so the forward and the inverse kernel of the same frames read
 // the same records, each with one bulk copy while its samples are in flight.
-// One CTA builds kPlanPerCta consecutive regions of one frame: every thread first
-// issues the map-byte loads of its unit in all of them (the kernel is bound by that
-// latency), then the records are built one after the other.  Grid
-// (ceil(regions per frame / kPlanPerCta), frames).
+//
+// One thread per unit of the 18 x 10 grid around a region (the region's 16 x 8 units
+// and a ring of one):
+//  - leaf size: OD_BLOCK_SIZE4x4 (reference src/block_size.h:32-35), bs =
+//    OD_MAXI(obs, xdec) - xdec (src/encode.c:1297-1301); lossless mode forces
+//    32x32 (src/encode.c:3090); 0xFF outside the plane;
+//  - which of the unit's edges are filtered: superblock edges always, over the
+//    whole padded plane (src/filter.c:1567-1584); split mid-edges gated by
+//    hfilter / vfilter = the split block's right / bottom side lies inside the
+//    LUMA picture, compared in plane-local coordinates (src/encode.c:1318-1319,
+//    src/filter.c:1494-1508);
+//  - the unit's transform goes to the task list of its class (4x4-unit, 8x8, 16x16,
+//    32x32; blocks larger than a unit are entered by their first unit).
+//
+// One CTA builds kPlanPerCta horizontally adjacent regions (same plane, same region
+// row, so everything that depends on the row is computed once): every thread first
+// issues the map-byte loads of its unit in all of them, then the records are built.
+// Grid (groups per frame, frames).
 #include "tdlt_kernels.h"
 
 namespace tdlt {
@@ -19,48 +33,99 @@ tdlt_plan_kernel(const __grid_constant__ RegionBatch bd, const unsigned char *__
                  unsigned char *__restrict__ plan) {
   __shared__ __align__(16) unsigned char rec[kPlanPerCta][kPlanBytes];
   const int tid = threadIdx.x, lane = tid & 31;
-  const int frame = blockIdx.y, r0 = blockIdx.x*kPlanPerCta;
-  const int nreg = min(kPlanPerCta, bd.regs_per_frame - r0);
+  const int frame = blockIdx.y;
+  // group -> (plane, region row, first region column); uniform over the CTA
+  int g = blockIdx.x, p = 0;
+#pragma unroll
+  for (int q = 1; q < kMaxPlanes; q++) {
+    if (q < bd.nplanes && g >= bd.pl[q].grp0) p = q;
+  }
+  const RegionPlane &pd = bd.pl[p];
+  g -= pd.grp0;
+  const int ry = g/pd.ngx, rx0 = (g - ry*pd.ngx)*kPlanPerCta;
+  const int nreg = min(kPlanPerCta, pd.nrx - rx0);
+  const int dec = pd.dec, sb = 32 >> dec;
+  const bool haar = (bd.flags & 2) != 0;
   const unsigned char *map = bsize + (size_t)frame*bd.bw*bd.bh;
-  const int ur = tid/18, uc = tid - ur*18;
+
+  // this thread's grid position (r, c): plane unit row uy, unit columns ux0 + 16 k
+  const int r = tid/18, c = tid - r*18;
+  const bool active = tid < 18*10;
+  const int uy = ry*kRegUY + r - 1, ux0 = rx0*kRegUX + c - 1;
+  const int Y = 8*uy;
+  const bool iny = active && uy >= 0 && Y < pd.h;
+  const unsigned char *maprow = map + min(uy << dec, bd.bh - 1)*bd.bw;
 
   int raw[kPlanPerCta];
   bool inside[kPlanPerCta];
-  RegionId ids[kPlanPerCta];
 #pragma unroll
   for (int k = 0; k < kPlanPerCta; k++) {
-    raw[k] = 0;
-    inside[k] = false;
-    ids[k] = decode_region(bd, frame, min(r0 + k, bd.regs_per_frame - 1));
-    if (k < nreg && tid < 18*10) {
-      const RegionId id = ids[k];
-      int idx = region_unit_map_index(bd, bd.pl[id.pli], id, ur, uc);
-      inside[k] = idx >= 0;
-      if (inside[k]) raw[k] = map[idx];
-    }
+    int ux = ux0 + kRegUX*k;
+    inside[k] = iny && k < nreg && ux >= 0 && 8*ux < pd.w;
+    raw[k] = inside[k] ? maprow[min(ux << dec, bd.bw - 1)] : 0;
   }
   for (int i = tid; i < kPlanPerCta*kPlanBytes/16; i += 192) {
     reinterpret_cast<int4 *>(&rec[0][0])[i] = make_int4(0, 0, 0, 0);
   }
   __syncthreads();
+
+  // what depends on the row only: is the unit's top edge a superblock edge, and the
+  // size of the block whose mid-edge it would otherwise be
+  const bool top_sb = (Y & (sb - 1)) == 0;
+  const int nbY = 2*(Y & -Y);
+  const bool midv_in = Y + 8 <= bd.pic_h;
+  const int UR = r - 1, UC = c - 1;
+  const bool owned = active && UR >= 0 && UR < kRegUY && UC >= 0 && UC < kRegUX && !haar;
+  if (tid < 192) {
 #pragma unroll
-  for (int k = 0; k < kPlanPerCta; k++) {
-    if (k < nreg) {
-      RegionSmem s;
-      s.A = nullptr;
-      s.ls = rec[k];
-      s.ub = rec[k] + (kOffUb - kOffLs);
-      s.tasks = rec[k] + (kOffTasks - kOffLs);
-      s.cnt = reinterpret_cast<int *>(rec[k] + (kOffCnt - kOffLs));
-      s.msk = reinterpret_cast<unsigned *>(rec[k] + (kOffMsk - kOffLs));
-      s.bar = nullptr;
-      s.dyn = nullptr;
-      const RegionId id = ids[k];
-      region_setup_units(s, bd, bd.pl[id.pli], id, tid, lane, inside[k], raw[k]);
+    for (int k = 0; k < kPlanPerCta; k++) {
+      if (k >= nreg) break;                     // uniform
+      unsigned char *ls = rec[k];
+      unsigned char *ub = rec[k] + (kOffUb - kOffLs);
+      unsigned char *tasks = rec[k] + (kOffTasks - kOffLs);
+      int *cnt = reinterpret_cast<int *>(rec[k] + (kOffCnt - kOffLs));
+      unsigned *msk = reinterpret_cast<unsigned *>(rec[k] + (kOffMsk - kOffLs));
+      int L = 0xFF, bits = 0, which = -1;
+      if (inside[k]) {
+        L = haar ? 3 : max(raw[k], dec) - dec;
+        if (!haar) {
+          const int X = 8*(ux0 + kRegUX*k);
+          const int nm = (4 << L) - 1;          // block size - 1
+          if (Y > 0) {
+            // an edge inside the unit's block is no edge; the mid-edge of a split block
+            // is filtered along the whole block iff the block's right side is inside
+            // the picture
+            bool e = top_sb || (!(Y & nm) && (X & -nbY) + nbY <= bd.pic_w);
+            if (e) bits |= kUbTop;
+          }
+          if (X > 0) {
+            const int nbX = 2*(X & -X);
+            bool e = !(X & (sb - 1)) || (!(X & nm) && (Y & -nbX) + nbX <= bd.pic_h);
+            if (e) bits |= kUbLeft;
+          }
+          if (L == 0) {
+            if (X + 8 <= bd.pic_w) bits |= kUbMidH;
+            if (midv_in) bits |= kUbMidV;
+          }
+        }
+        if (owned) {
+          if (L <= 1) which = L;
+          else if (L == 2 && !(UR & 1) && !(UC & 1)) which = 2;
+          else if (L == 3 && !(UR & 3) && !(UC & 3)) which = 3;
+        }
+      }
+      if (active) {
+        ls[r*kUS + c] = (unsigned char)L;
+        ub[r*kUS + c] = (unsigned char)bits;
+        if (bits & kUbTop) atomicOr(msk + r, 1u << c);
+        if (bits & kUbLeft) atomicOr(msk + 10 + r, 1u << c);
+      }
+      list_push4(tasks, kTaskListStride, cnt + 4, which, (unsigned char)((UR << 4) | UC), lane);
     }
   }
   __syncthreads();
-  int4 *dst = reinterpret_cast<int4 *>(plan + ((size_t)frame*bd.regs_per_frame + r0)*kPlanBytes);
+  int4 *dst = reinterpret_cast<int4 *>(
+      plan + ((size_t)frame*bd.regs_per_frame + pd.reg0 + ry*pd.nrx + rx0)*kPlanBytes);
   for (int i = tid; i < nreg*(kPlanBytes/16); i += 192) {
     dst[i] = reinterpret_cast<const int4 *>(&rec[0][0])[i];
   }

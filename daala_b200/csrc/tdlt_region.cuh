@@ -92,6 +92,7 @@ struct RegionPlane {
   int nrx, nry;      // regions across / down
   int reg0;          // index of this plane's first region within a frame
   float inv_nrx;     // 1 / nrx
+  int ngx, grp0;     // plan kernel: groups of kPlanPerCta regions across; first group of the plane
 };
 
 struct RegionBatch {
@@ -99,6 +100,7 @@ struct RegionBatch {
   int nplanes;
   int regs_per_frame;
   float inv_rpf;          // 1 / regs_per_frame
+  int groups_per_frame;   // plan kernel grid
   int nframes;
   int pic_w, pic_h;      // LUMA picture size (gates the split filters)
   int bw, bh;            // block-size map: entries across / down (8x8 luma units)
@@ -172,99 +174,6 @@ __device__ __forceinline__ void list_push4(T *lists, int stride, int *cnt, int w
   if (lane == leader && which >= 0) base = atomicAdd(cnt + which, __popc(peers));
   base = __shfl_sync(0xffffffffu, base, leader);
   if (which >= 0) lists[which*stride + base + __popc(peers & ((1u << lane) - 1))] = item;
-}
-
-// ---------------------------------------------------------------------------
-// Unit tables.  One thread per unit of the 18 x 10 grid around the region:
-//  - leaf size: OD_BLOCK_SIZE4x4 (reference src/block_size.h:32-35), bs =
-//    OD_MAXI(obs, xdec) - xdec (src/encode.c:1297-1301); lossless mode forces
-//    32x32 (src/encode.c:3090);
-//  - which of the unit's edges are filtered: superblock edges always, over the
-//    whole padded plane (src/filter.c:1567-1584); split mid-edges gated by
-//    hfilter / vfilter = the split block's right / bottom side lies inside the
-//    LUMA picture, compared in plane-local coordinates (src/encode.c:1318-1319,
-//    src/filter.c:1494-1508).
-// Returns the leaf size (0xFF outside the plane).
-// ---------------------------------------------------------------------------
-// Index into the frame's block-size map of grid position (r, c) of the region, or -1
-// outside the plane.
-__device__ __forceinline__ int region_unit_map_index(const RegionBatch &bd, const RegionPlane &pd,
-                                                     const RegionId &id, int r, int c) {
-  int uy = id.ry*kRegUY + r - 1;     // plane unit coordinates
-  int ux = id.rx*kRegUX + c - 1;
-  if (uy < 0 || ux < 0 || 8*uy >= pd.h || 8*ux >= pd.w) return -1;
-  int my = min(uy << pd.dec, bd.bh - 1);
-  int mx = min(ux << pd.dec, bd.bw - 1);
-  return my*bd.bw + mx;
-}
-// raw = the map byte (ignored when inside is false).
-__device__ __forceinline__ int region_unit_tables(const RegionSmem &s, const RegionBatch &bd,
-                                                  const RegionPlane &pd, const RegionId &id,
-                                                  int r, int c, bool inside, int raw) {
-  int uy = id.ry*kRegUY + r - 1;
-  int ux = id.rx*kRegUX + c - 1;
-  int L = 0xFF, bits = 0;
-  if (inside) {
-    L = (bd.flags & 2) ? 3 : raw;
-    L = max(L, pd.dec) - pd.dec;
-    if (!(bd.flags & 2)) {
-      int Y = 8*uy, X = 8*ux;
-      int sb = 32 >> pd.dec;
-      int n = 4 << L;
-      if (Y > 0) {
-        bool e;
-        if ((Y & (sb - 1)) == 0) e = true;
-        else if (Y & (n - 1)) e = false;
-        else {
-          int nb = 2*(Y & -Y);
-          e = (X & ~(nb - 1)) + nb <= bd.pic_w;
-        }
-        if (e) bits |= kUbTop;
-      }
-      if (X > 0) {
-        bool e;
-        if ((X & (sb - 1)) == 0) e = true;
-        else if (X & (n - 1)) e = false;
-        else {
-          int nb = 2*(X & -X);
-          e = (Y & ~(nb - 1)) + nb <= bd.pic_h;
-        }
-        if (e) bits |= kUbLeft;
-      }
-      if (L == 0) {
-        if (X + 8 <= bd.pic_w) bits |= kUbMidH;
-        if (Y + 8 <= bd.pic_h) bits |= kUbMidV;
-      }
-    }
-  }
-  s.ls[r*kUS + c] = (unsigned char)L;
-  s.ub[r*kUS + c] = (unsigned char)bits;
-  if (bits & kUbTop) atomicOr(s.msk + r, 1u << c);
-  if (bits & kUbLeft) atomicOr(s.msk + 10 + r, 1u << c);
-  return L;
-}
-
-// Threads 0..191 (six whole warps): unit tables, and the transforms of the
-// region sorted into the four task lists.  Thread tid < 180 owns grid position
-// (tid / 18, tid % 18); inside / raw as above.
-__device__ __forceinline__ void region_setup_units(const RegionSmem &s, const RegionBatch &bd,
-                                                   const RegionPlane &pd, const RegionId &id,
-                                                   int tid, int lane, bool inside, int raw) {
-  if (tid < 192) {
-    int which = -1, item = 0;
-    if (tid < 18*10) {
-      int r = tid/18, c = tid - r*18;
-      int L = region_unit_tables(s, bd, pd, id, r, c, inside, raw);
-      int UR = r - 1, UC = c - 1;
-      if (UR >= 0 && UR < kRegUY && UC >= 0 && UC < kRegUX && !(bd.flags & 2)) {
-        if (L == 0 || L == 1) which = L;
-        else if (L == 2 && !(UR & 1) && !(UC & 1)) which = 2;
-        else if (L == 3 && !(UR & 3) && !(UC & 3)) which = 3;
-        item = (UR << 4) | UC;
-      }
-    }
-    list_push4(s.tasks, kTaskListStride, s.cnt + 4, which, (unsigned char)item, lane);
-  }
 }
 
 // ---------------------------------------------------------------------------
