@@ -320,14 +320,16 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
-  PlanePtrs in, out;
-  memset(&in, 0, sizeof(in));
+  TmapSet maps;
+  memset(&maps, 0, sizeof(maps));
+  PlanePtrs out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
     if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
     }
-    in.p[p] = const_cast<od_coeff *>(d[p]);
+    int trc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
+    if (trc) return trc;
     out.p[p] = c[p];
   }
   long long total = (long long)rb.regs_per_frame*nframes;
@@ -340,7 +342,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
   tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      rb, ctx->plan, in, out, ctx->strips, ctx->ticket, ctx->epoch);
+      maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

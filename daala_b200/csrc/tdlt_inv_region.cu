@@ -74,8 +74,9 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
 }
 
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
-tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
-                       const unsigned char *__restrict__ plan, PlanePtrs in, PlanePtrs out,
+tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -101,31 +102,35 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
   const bool haar = (bd.flags & 2) != 0;
   const int sb = 32 >> pd.dec;
 
-  // ---- the region's coefficients, row by row, into the inside of A (the halo is
-  // filled from the neighbours' strips below) -----------------------------------
-  {
-    const int nrows = min(kRegH, pd.h - Y0), rowbytes = 4*min(kRegW, pd.w - X0);
-    if (tid == 0) mbar_expect_tx(s.bar, nrows*rowbytes + kPlanBytes);
-    if (tid < nrows) {
-      const int *src = in.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + tid)*pd.w + X0;
-      bulk_g2s(s.A + (tid + 2)*kAP + 4, src, rowbytes, s.bar);
-    }
-    // ... and the region's plan record (tdlt_plan.cu) on the same mbarrier
-    if (tid == kRegH) bulk_g2s(s.ls, plan + (size_t)t*kPlanBytes, kPlanBytes, s.bar);
+  // ---- the region's coefficients: the same TMA box as the forward kernel's (the halo
+  // part of it is neighbours' coefficients, of no use here: the ring of raw samples
+  // replaces it below), and the region's plan record (tdlt_plan.cu), on one mbarrier
+  if (tid == 0) {
+    mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
+    tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    bulk_g2s(s.ls, plan + (size_t)t*kPlanBytes, kPlanBytes, s.bar);
   }
   // ---- the ring of raw samples from the regions above / left / above-left: one
   // int2 per thread.  The regions above finished long ago as a rule: their part is
-  // fetched now, into the halo of A (nothing else writes there); what is not
-  // there yet (the left neighbour, which started just before this region) is
-  // waited for after the transforms.
+  // read now and put into the halo of A once the box has landed; what is not there
+  // yet (the left neighbour, which started just before this region) is waited for
+  // after the transforms.
   bool ring_done;
+  int2 ring_val = make_int2(0, 0);
+  RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
+  bool ring_early = false;
   {
-    RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
     ring_done = !rs.need || (TDLT_ABLATE & 32);
-    if (rs.need && (tid < 128 || tid >= 192)) ring_done = ring_try(rs, epoch);
+    if (rs.need && (tid < 128 || tid >= 192)) {
+      int2 p0 = ld_pair(rs.src), p1 = ld_pair(rs.src + 1);
+      ring_early = p0.y == epoch && p1.y == epoch;
+      ring_val = make_int2(p0.x, p1.x);
+      ring_done = ring_early;
+    }
   }
   TDLT_MARK(t, 1);
   mbar_wait(s.bar, 0);
+  if (ring_early) *rs.dst = ring_val;
   TDLT_MARK(t, 2);
 
   int *gout = out.p[id.pli] + (size_t)id.frame*pd.w*pd.h;
@@ -257,7 +262,6 @@ tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
 
   // ---- the ring: whatever was not there yet when the region started --------------
   if (!ring_done) {
-    RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
     while (!ring_try(rs, epoch)) __nanosleep(20);
   }
   __syncthreads();      // the ring is in A, and the strips were read before anyone laps them

@@ -7,7 +7,7 @@
 
 namespace tdlt {
 
-// TMA descriptors of the forward kernel's input planes (3-D: x, y, frame).
+// TMA descriptors of a kernel's input planes (3-D: x, y, frame).
 struct TmapSet {
   CUtensorMap in[kMaxPlanes];
 };
@@ -24,8 +24,9 @@ __global__ void tdlt_plan_kernel(const __grid_constant__ RegionBatch bd,
 __global__ void tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ plan, PlanePtrs out);
-__global__ void tdlt_inv_region_kernel(const __grid_constant__ RegionBatch bd,
-                                       const unsigned char *__restrict__ plan, PlanePtrs in,
+__global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
+                                       const __grid_constant__ RegionBatch bd,
+                                       const unsigned char *__restrict__ plan,
                                        PlanePtrs out, int2 *__restrict__ strips,
                                        int *__restrict__ ticket, int epoch);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;
