@@ -152,9 +152,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   // ---- keyframe: undo the DC pyramid, top-down --------------------------------
   if ((bd.flags & 1) && tile_on && !(TDLT_ABLATE & 4)) {
     const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-    if (pd.dec == 0) region_dc_level<true>(At, ls0, lane, 32);
-    region_dc_level<true>(At, ls0, lane, 16);
-    region_dc_level<true>(At, ls0, lane, 8);
+    region_dc_split_tile(At, ls0, lane, pd.dec == 0);
   }
   __syncthreads();
   TDLT_MARK(t, 3);
@@ -235,6 +233,13 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       }
     }
   }
+  // the ring samples still missing (the left neighbour's columns, as a rule) are asked
+  // for now, so that the round trip to L2 overlaps the barrier and the publication
+  int2 pf0 = make_int2(0, 0), pf1 = make_int2(0, 0);
+  if (!ring_done) {
+    pf0 = ld_pair(rs.src);
+    pf1 = ld_pair(rs.src + 1);
+  }
   __syncthreads();
   TDLT_MARK(t, 4);
 
@@ -262,7 +267,8 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
 
   // ---- the ring: whatever was not there yet when the region started --------------
   if (!ring_done) {
-    while (!ring_try(rs, epoch)) __nanosleep(20);
+    if (pf0.y == epoch && pf1.y == epoch) *rs.dst = make_int2(pf0.x, pf1.x);
+    else while (!ring_try(rs, epoch)) __nanosleep(20);
   }
   __syncthreads();      // the ring is in A, and the strips were read before anyone laps them
   TDLT_MARK(t, 6);

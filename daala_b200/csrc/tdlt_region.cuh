@@ -562,6 +562,45 @@ __device__ __forceinline__ void region_dc_level(int *At, const unsigned char *ls
   __syncwarp();
 }
 
+// The inverse direction (top-down split) of a whole tile in ONE step: lane j < 16 takes
+// unit j of the tile and follows the chain superblock -> 16x16 quadrant -> its unit
+// -> (if the unit is split) its 4x4 blocks in registers, from the values as they are
+// before any split; lanes that share ancestors compute them redundantly.  Every lane
+// reads first, then writes the DC(s) at positions inside its own unit: no ordering
+// between levels through shared memory.  luma: the tile is one 32x32 superblock;
+// chroma (4:2:0): four 16x16 superblocks.
+__device__ __forceinline__ void region_dc_split_tile(int *At, const unsigned char *ls0, int lane,
+                                                     bool luma) {
+  const int uy = (lane >> 2) & 3, ux = lane & 3, qy = uy >> 1, qx = ux >> 1;
+  int *Q = At + 16*qy*kAP + 16*qx;            // my quadrant
+  int *U = At + 8*uy*kAP + 8*ux;              // my unit
+  int vq, b1, b2, b3, c1 = 0, c2 = 0, c3 = 0;
+  const bool act = lane < 16;
+  const int L = act ? ls0[uy*kUS + ux] : 3;
+  if (act) {
+    vq = Q[0];
+    if (luma && ls0[0] < 3) {
+      int a0 = At[0], a1 = At[16], a2 = At[16*kAP], a3 = At[16*kAP + 16];
+      haar2x2(a0, a1, a2, a3);
+      vq = qy ? (qx ? a3 : a2) : (qx ? a1 : a0);
+    }
+    b1 = Q[8]; b2 = Q[8*kAP]; b3 = Q[8*kAP + 8];
+    if (L == 0) { c1 = U[4]; c2 = U[4*kAP]; c3 = U[4*kAP + 4]; }
+  }
+  __syncwarp();
+  if (act) {
+    int b0 = vq;
+    if (ls0[2*qy*kUS + 2*qx] < 2) haar2x2(b0, b1, b2, b3);
+    int vu = (uy & 1) ? ((ux & 1) ? b3 : b2) : ((ux & 1) ? b1 : b0);
+    if (L == 0) {
+      haar2x2(vu, c1, c2, c3);
+      U[4] = c1; U[4*kAP] = c2; U[4*kAP + 4] = c3;
+    }
+    U[0] = vu;
+  }
+  __syncwarp();
+}
+
 // ---- lossless mode: the multi-level Haar wavelet of each superblock of a tile, in
 // place (reference src/dct.c:1960-2026).  At -> the tile's origin in A.  Every level
 // reads its 2x2 groups into registers before it writes anything.
