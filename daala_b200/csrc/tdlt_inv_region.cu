@@ -273,8 +273,31 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   __syncthreads();      // the ring is in A, and the strips were read before anyone laps them
   TDLT_MARK(t, 6);
 
-  // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
+  // ---- un-lap (levels 8 .. superblock) and store the owned rectangle, one phase ----
+  // buffer row b <-> plane row Y0 - 2 + b.  Owned: buffer rows b0 .. b1-1 and region
+  // columns cs .. ce-1 (cs = -2, or 0 in the first region column; ce = 126, or where the
+  // plane ends).  One warp task = one row of 4x4 blocks of the offset grid
+  // (unlap_block_store, tdlt_region.cuh); where the plane ends in this region the
+  // blocks holding columns 126, 127 make one more task.
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
+#ifndef TDLT_INV_PHASES
+  {
+    const int b0 = (id.ry == 0) ? 2 : 0;
+    const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
+    const int cs = (id.rx > 0) ? -2 : 0;
+    const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
+    const int nbi = (b1 + 3) >> 2;
+    int *g = gout + (ptrdiff_t)(Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
+#pragma unroll 1
+    for (int bi = warp; bi < nbi; bi += kRegWarps) {
+      unlap_block_store(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
+    }
+    if (ce > kRegW - 2 && warp == kRegWarps - 1) {
+      unlap_block_store(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);
+    }
+  }
+#else
+  // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
 #ifndef TDLT_LAP_BLOCKS
 #pragma unroll 1
   for (int lv = (TDLT_ABLATE & 1) ? 64 : 8; lv <= sb; lv <<= 1) {
@@ -322,6 +345,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       }
     }
   }
+#endif
   TDLT_MARK(t, 8);
 }
 

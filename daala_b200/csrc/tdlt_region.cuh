@@ -393,6 +393,91 @@ __device__ __forceinline__ void region_lap_blocks(int *A, const unsigned char *u
   }
 }
 
+// ---------------------------------------------------------------------------
+// Inverse tail: the un-lapping of the levels 8 .. superblock AND the store of the
+// region's owned rectangle as one barrier-free phase.  The owned rectangle (region rows
+// -2 .. 61, columns -2 .. 125) is tiled exactly by the 4x4 blocks of the offset grid
+// above -- block (bi, bj) = buffer rows 4bi .. 4bi+3, region columns 4bj-2 .. 4bj+1 --
+// and every filter lies inside one block, so a lane takes one block from shared memory
+// into registers, undoes the filters that cross it (a CELL up to four along its rows
+// and four down its columns, HF / VF blocks four of one direction, the inside of a unit
+// none) and stores the 16 samples straight to global memory: the buffer is only read,
+// nothing is written back, no barrier separates the levels.
+// A warp task is one block row (bi uniform, lane = bj): the lanes' 8-byte pieces of one
+// row form one contiguous run of 512 bytes.
+// The inverse undoes the forward order backwards: at a crossing the filters of the
+// finer line first, and on a tie those along the rows (across the vertical edge)
+// first.  The code below always runs "down the columns, then along the rows"; a lane
+// that needs the other order works on the transposed block (12 selects each way, much
+// cheaper than a second copy of the four filters).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void transpose4_if(int (&x)[4][4], bool t) {
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+#pragma unroll
+    for (int c = r + 1; c < 4; c++) {
+      int a = x[r][c], b = x[c][r];
+      x[r][c] = t ? b : a;
+      x[c][r] = t ? a : b;
+    }
+  }
+}
+// g -> plane sample (Y0 - 2, X0 - 2), i.e. buffer row 0 / region column -2 (may lie
+// before the plane: such pieces are never stored).  Stored: buffer rows b0 .. b1-1,
+// region columns cs .. ce-1.
+__device__ __forceinline__ void unlap_block_store(const int *A, const unsigned char *ub, int sb,
+                                                  int bi, int bj, bool on, int *g, size_t pitch,
+                                                  int b0, int b1, int cs, int ce) {
+  const bool ei = !(bi & 1), ej = !(bj & 1);
+  const int iu = bi >> 1, ju = bj >> 1;
+  int x[4][4];
+  bool colL = false, colR = false, rowT = false, rowB = false, tr = false;
+  if (on) {
+    const int2 *p = reinterpret_cast<const int2 *>(A + 4*bi*kAP + 4*bj + 2);
+    constexpr int S = kAP/2;
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      int2 l = p[r*S], h = p[r*S + 1];
+      x[r][0] = l.x; x[r][1] = l.y; x[r][2] = h.x; x[r][3] = h.y;
+    }
+    if (!(TDLT_ABLATE & 1)) {
+      const unsigned char *u = ub + ut(iu, ju);
+      const int u0 = u[0];
+      const int uc = ej ? u[-1] : u0;        // cell: the unit left of the crossing
+      const int ur = ei ? u[-kUS] : u0;      // cell: the unit above it
+      colR = ei && (u0 & kUbTop);
+      colL = ei && (uc & kUbTop);
+      rowB = ej && (u0 & kUbLeft);
+      rowT = ej && (ur & kUbLeft);
+      // forward: the coarser line first, the horizontal edge on a tie; so the inverse
+      // starts along the rows iff the row line is at least as coarse as the column line
+      tr = ei && ej && lap_level8(iu, sb) >= lap_level8(ju, sb);
+    }
+  }
+  if (tr) {
+    bool t = colL; colL = rowT; rowT = t;
+    t = colR; colR = rowB; rowB = t;
+  }
+  transpose4_if(x, tr);
+  if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
+  if (colR) { post4(x[0][2], x[1][2], x[2][2], x[3][2]); post4(x[0][3], x[1][3], x[2][3], x[3][3]); }
+  if (rowT) { post4(x[0][0], x[0][1], x[0][2], x[0][3]); post4(x[1][0], x[1][1], x[1][2], x[1][3]); }
+  if (rowB) { post4(x[2][0], x[2][1], x[2][2], x[2][3]); post4(x[3][0], x[3][1], x[3][2], x[3][3]); }
+  transpose4_if(x, tr);
+  if (on && !(TDLT_ABLATE & 128)) {
+    const bool lok = 4*bj - 2 >= cs && 4*bj - 2 < ce, hok = 4*bj < ce;
+    int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      const int b = 4*bi + r;
+      if (b >= b0 && b < b1) {
+        if (lok) *reinterpret_cast<int2 *>(gp + r*pitch) = make_int2(x[r][0], x[r][1]);
+        if (hok) *reinterpret_cast<int2 *>(gp + r*pitch + 2) = make_int2(x[r][2], x[r][3]);
+      }
+    }
+  }
+}
+
 // Level 4, in registers.  The two lanes of a unit hold it as v[8*q + r] = sample
 // (row r, column 4*h + q).  The filter across the horizontal mid-edge (rows
 // 2..5 of every column) is local; the one across the vertical mid-edge (columns
