@@ -133,7 +133,6 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   if (ring_early) *rs.dst = ring_val;
   TDLT_MARK(t, 2);
 
-  int *gout = out.p[id.pli] + (size_t)id.frame*pd.w*pd.h;
   const int tx = warp & 3, ty = warp >> 2;
   const bool tile_on = X0 + 32*tx < pd.w && Y0 + 32*ty < pd.h;
   int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;      // warp w <-> tile w
@@ -142,7 +141,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     // No lapping in lossless mode: every tile is stored where it lies.
     if (tile_on) {
       region_haar_tile<true>(At, lane, sb);
-      int *g = gout + (size_t)(Y0 + 32*ty)*pd.w + X0 + 32*tx;
+      int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + 32*ty)*pd.w + X0 + 32*tx;
 #pragma unroll 1
       for (int r = 0; r < 32; r++) g[(size_t)r*pd.w + lane] = At[r*kAP + lane];
     }
@@ -287,13 +286,13 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     const int cs = (id.rx > 0) ? -2 : 0;
     const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
     const int nbi = (b1 + 3) >> 2;
-    int *g = gout + (ptrdiff_t)(Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
+    int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
 #pragma unroll 1
     for (int bi = warp; bi < nbi; bi += kRegWarps) {
-      unlap_block_store(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
+      unlap_block_store<true>(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
     }
     if (ce > kRegW - 2 && warp == kRegWarps - 1) {
-      unlap_block_store(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);
+      unlap_block_store<false>(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);
     }
   }
 #else
@@ -328,7 +327,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     const bool on2 = c0 + 128 < ce;     // lane 0 of the last region column: columns 126, 127
     const bool any2 = last_c && id.rx > 0;                // warp-uniform
     const size_t pitch8 = (size_t)pd.w*kRegWarps;
-    int *gr = gout + (ptrdiff_t)(Y0 - 2 + b0 + warp)*(ptrdiff_t)pd.w + X0 + c0;
+    int *gr = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2 + b0 + warp)*(ptrdiff_t)pd.w + X0 + c0;
     const int *arow = s.A + (b0 + warp)*kAP + 4 + c0;
     const int nb = b1 - b0 - warp;
 #pragma unroll

@@ -425,6 +425,14 @@ __device__ __forceinline__ void transpose4_if(int (&x)[4][4], bool t) {
 // g -> plane sample (Y0 - 2, X0 - 2), i.e. buffer row 0 / region column -2 (may lie
 // before the plane: such pieces are never stored).  Stored: buffer rows b0 .. b1-1,
 // region columns cs .. ce-1.
+// kRow: called by a whole warp for one block row (bi uniform, bj = lane).  The block of
+// lane j holds region columns 4j-2 .. 4j+1, which is 8 bytes off the 16-byte grid, so
+// every lane fetches the left half of its right neighbour's block by shuffle and the
+// row goes out as ONE run of 16-byte vectors (columns 4j .. 4j+3: whole 32-byte
+// sectors) plus one 8-byte piece at either end (lane 0: columns -2, -1; lane 31: 124,
+// 125).  !kRow: any lane, any block, only the left half (columns 4bj-2, 4bj-1) is
+// stored -- the blocks holding columns 126, 127 where the plane ends.
+template <bool kRow>
 __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned char *ub, int sb,
                                                   int bi, int bj, bool on, int *g, size_t pitch,
                                                   int b0, int b1, int cs, int ce) {
@@ -437,22 +445,41 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
     constexpr int S = kAP/2;
 #pragma unroll
     for (int r = 0; r < 4; r++) {
-      int2 l = p[r*S], h = p[r*S + 1];
-      x[r][0] = l.x; x[r][1] = l.y; x[r][2] = h.x; x[r][3] = h.y;
+      int2 l = p[r*S];
+      x[r][0] = l.x; x[r][1] = l.y;
+      if (kRow) {
+        int2 h = p[r*S + 1];
+        x[r][2] = h.x; x[r][3] = h.y;
+      }
     }
     if (!(TDLT_ABLATE & 1)) {
       const unsigned char *u = ub + ut(iu, ju);
       const int u0 = u[0];
       const int uc = ej ? u[-1] : u0;        // cell: the unit left of the crossing
-      const int ur = ei ? u[-kUS] : u0;      // cell: the unit above it
-      colR = ei && (u0 & kUbTop);
       colL = ei && (uc & kUbTop);
-      rowB = ej && (u0 & kUbLeft);
-      rowT = ej && (ur & kUbLeft);
-      // forward: the coarser line first, the horizontal edge on a tie; so the inverse
-      // starts along the rows iff the row line is at least as coarse as the column line
-      tr = ei && ej && lap_level8(iu, sb) >= lap_level8(ju, sb);
+      if (kRow) {
+        const int ur = ei ? u[-kUS] : u0;    // cell: the unit above it
+        colR = ei && (u0 & kUbTop);
+        rowB = ej && (u0 & kUbLeft);
+        rowT = ej && (ur & kUbLeft);
+        // forward: the coarser line first, the horizontal edge on a tie; so the inverse
+        // starts along the rows iff the row line is at least as coarse as the column line
+        tr = ei && ej && lap_level8(iu, sb) >= lap_level8(ju, sb);
+      }
     }
+  }
+  if (!kRow) {
+    // beyond the plane's last unit column nothing crosses the block along its rows
+    if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
+    if (on && !(TDLT_ABLATE & 128) && 4*bj - 2 < ce) {
+      int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        const int b = 4*bi + r;
+        if (b >= b0 && b < b1) *reinterpret_cast<int2 *>(gp + r*pitch) = make_int2(x[r][0], x[r][1]);
+      }
+    }
+    return;
   }
   if (tr) {
     bool t = colL; colL = rowT; rowT = t;
@@ -464,15 +491,25 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
   if (rowT) { post4(x[0][0], x[0][1], x[0][2], x[0][3]); post4(x[1][0], x[1][1], x[1][2], x[1][3]); }
   if (rowB) { post4(x[2][0], x[2][1], x[2][2], x[2][3]); post4(x[3][0], x[3][1], x[3][2], x[3][3]); }
   transpose4_if(x, tr);
-  if (on && !(TDLT_ABLATE & 128)) {
-    const bool lok = 4*bj - 2 >= cs && 4*bj - 2 < ce, hok = 4*bj < ce;
+  {
+    // columns 4bj .. 4bj+3 are all mine and the right half is in the warp (lane 31's is
+    // not: where the plane ends there, columns 126, 127 are the extra task's)
+    const bool full = 4*bj + 3 < ce && bj < 31;
+    // the 8-byte pieces: lane 0 its left half (if the region owns columns -2, -1), the
+    // lane whose right neighbour is beyond ce its right half
+    const bool pl = bj == 0 && cs < 0, ph = !full && 4*bj + 1 < ce;
     int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
 #pragma unroll
     for (int r = 0; r < 4; r++) {
+      const int n0 = __shfl_down_sync(0xffffffffu, x[r][0], 1);
+      const int n1 = __shfl_down_sync(0xffffffffu, x[r][1], 1);
       const int b = 4*bi + r;
-      if (b >= b0 && b < b1) {
-        if (lok) *reinterpret_cast<int2 *>(gp + r*pitch) = make_int2(x[r][0], x[r][1]);
-        if (hok) *reinterpret_cast<int2 *>(gp + r*pitch + 2) = make_int2(x[r][2], x[r][3]);
+      if (b >= b0 && b < b1 && !(TDLT_ABLATE & 128)) {
+        if (full) *reinterpret_cast<int4 *>(gp + r*pitch + 2) = make_int4(x[r][2], x[r][3], n0, n1);
+        if (pl | ph) {
+          *reinterpret_cast<int2 *>(gp + r*pitch + (pl ? 0 : 2)) =
+              pl ? make_int2(x[r][0], x[r][1]) : make_int2(x[r][2], x[r][3]);
+        }
       }
     }
   }
