@@ -24,10 +24,11 @@ __device__ __forceinline__ void pre4(int &x0, int &x1, int &x2, int &x3) {
   int t2 = x1 - x2;
   int t1 = x1 - (t2 >> 1);
   int t0 = x0 - (t3 >> 1);
-  t2 = (t2*85) >> 6;
-  t2 += (t2 > 0);
-  t3 = (t3*75) >> 6;
-  t3 += (t3 > 0);
+  // (t*85 >> 6) + (that > 0): the product keeps the sign of t and is >= 64 whenever
+  // t >= 1, so "> 0" is the sign bit of -85 t (one multiply-add pipe instruction and
+  // one shift-add instead of compare / add / select)
+  t2 = ((t2*85) >> 6) + (int)((unsigned)(t2*-85) >> 31);
+  t3 = ((t3*75) >> 6) + (int)((unsigned)(t3*-75) >> 31);
   t3 += (t2*-15 + 32) >> 6;
   t2 += (t3*33 + 32) >> 6;
   t0 += t3 >> 1;
@@ -45,8 +46,9 @@ __device__ __forceinline__ void post4(int &y0, int &y1, int &y2, int &y3) {
   int t2 = y1 - y2;
   int t1 = y1 - (t2 >> 1);
   int t0 = y0 - (t3 >> 1);
-  t2 -= (t3*33 + 32) >> 6;
-  t3 -= (t2*-15 + 32) >> 6;
+  // x -= (a + 32) >> 6  ==  x += (-a + 31) >> 6  (one shift-add instead of shift, subtract)
+  t2 += (t3*-33 + 31) >> 6;
+  t3 += (t2*15 + 31) >> 6;
   // (t*64)/75 and (t*64)/85, C division (truncating), as one multiply-high each:
   // trunc(t*64/d) = floor(t*M/2^32) + (t < 0) with M = ceil(2^38/d), exact for
   // |t| < 2^25, the range in which the reference's own t*64 does not overflow

@@ -161,9 +161,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
       }
       else if ((bd.flags & 1) && !(TDLT_ABLATE & 4)) {
         const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-        region_dc_level<false>(At, ls0, lane, 8);
-        region_dc_level<false>(At, ls0, lane, 16);
-        if (pd.dec == 0) region_dc_level<false>(At, ls0, lane, 32);
+        region_dc_merge_tile(At, ls0, lane, pd.dec == 0);
       }
       if (!(TDLT_ABLATE & 16)) {
         int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + TY + (lane >> 3))*pd.w + TX + 4*(lane & 7);

@@ -280,6 +280,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   // blocks holding columns 126, 127 make one more task.
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
 #ifndef TDLT_INV_PHASES
+  TDLT_MARK(t, 7);
   {
     const int b0 = (id.ry == 0) ? 2 : 0;
     const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
@@ -287,9 +288,12 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
     const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
     const int nbi = (b1 + 3) >> 2;
     int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
+    // even block rows carry filters of both directions, odd ones of one: warp w takes
+    // the rows w and 15 - w (one of each), then 16 + w
 #pragma unroll 1
-    for (int bi = warp; bi < nbi; bi += kRegWarps) {
-      unlap_block_store<true>(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
+    for (int k = 0; k < 3; k++) {
+      const int bi = k == 0 ? warp : (k == 1 ? 15 - warp : 16 + warp);
+      if (bi < nbi) unlap_block_store<true>(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
     }
     if (ce > kRegW - 2 && warp == kRegWarps - 1) {
       unlap_block_store<false>(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);

@@ -439,7 +439,10 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
   const bool ei = !(bi & 1), ej = !(bj & 1);
   const int iu = bi >> 1, ju = bj >> 1;
   int x[4][4];
-  bool colL = false, colR = false, rowT = false, rowB = false, tr = false;
+  // which filters cross the block: bit 0 down its left two columns, 1 its right two,
+  // 2 along its upper two rows, 3 its lower two
+  unsigned f = 0;
+  bool tr = false;
   if (on) {
     const int2 *p = reinterpret_cast<const int2 *>(A + 4*bi*kAP + 4*bj + 2);
     constexpr int S = kAP/2;
@@ -454,23 +457,24 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
     }
     if (!(TDLT_ABLATE & 1)) {
       const unsigned char *u = ub + ut(iu, ju);
-      const int u0 = u[0];
-      const int uc = ej ? u[-1] : u0;        // cell: the unit left of the crossing
-      colL = ei && (uc & kUbTop);
+      const unsigned u0 = u[0];
+      const unsigned uc = ej ? u[-1] : u0;        // cell: the unit left of the crossing
+      static_assert(kUbTop == 1 && kUbLeft == 2, "bit positions used below");
+      if (ei) f = uc & 1;
       if (kRow) {
-        const int ur = ei ? u[-kUS] : u0;    // cell: the unit above it
-        colR = ei && (u0 & kUbTop);
-        rowB = ej && (u0 & kUbLeft);
-        rowT = ej && (ur & kUbLeft);
+        const unsigned ur = ei ? u[-kUS] : u0;    // cell: the unit above it
+        if (ei) f |= (u0 & 1) << 1;
+        if (ej) f |= ((ur & 2) << 1) | ((u0 & 2) << 2);
         // forward: the coarser line first, the horizontal edge on a tie; so the inverse
         // starts along the rows iff the row line is at least as coarse as the column line
         tr = ei && ej && lap_level8(iu, sb) >= lap_level8(ju, sb);
       }
     }
   }
+  const bool colL0 = f & 1;
   if (!kRow) {
     // beyond the plane's last unit column nothing crosses the block along its rows
-    if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
+    if (colL0) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
     if (on && !(TDLT_ABLATE & 128) && 4*bj - 2 < ce) {
       int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
 #pragma unroll
@@ -481,11 +485,9 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
     }
     return;
   }
-  if (tr) {
-    bool t = colL; colL = rowT; rowT = t;
-    t = colR; colR = rowB; rowB = t;
-  }
+  if (tr) f = ((f & 3) << 2) | (f >> 2);       // on the transposed block rows and columns swap
   transpose4_if(x, tr);
+  const bool colL = f & 1, colR = f & 2, rowT = f & 4, rowB = f & 8;
   if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
   if (colR) { post4(x[0][2], x[1][2], x[2][2], x[3][2]); post4(x[0][3], x[1][3], x[2][3], x[3][3]); }
   if (rowT) { post4(x[0][0], x[0][1], x[0][2], x[0][3]); post4(x[1][0], x[1][1], x[1][2], x[1][3]); }
@@ -666,21 +668,47 @@ __device__ __forceinline__ void a_row32(int *a, int *v) {     // a -> (row lane,
 // ---- keyframe DC pyramid on one tile (reference src/encode.c:1328-1341,
 // src/decode.c:733).  At -> the tile's origin in A, ls0 -> unit table entry of the
 // tile's first unit.
-template <bool kInverse>
-__device__ __forceinline__ void region_dc_level(int *At, const unsigned char *ls0, int lane,
-                                                int n) {
-  int per = 32/n;
-  if (lane < per*per) {
-    int r0 = (lane/per)*n, c0 = (lane%per)*n;
-    int lsz = ls0[(r0 >> 3)*kUS + (c0 >> 3)];
-    if ((4 << lsz) < n) {
-      int hn = n >> 1;
-      int *p = At + r0*kAP + c0;
-      int x0 = p[0], x1 = p[hn], x2 = p[hn*kAP], x3 = p[hn*kAP + hn];
-      if (kInverse) haar2x2(x0, x1, x2, x3); else haar2x2(x0, x2, x1, x3);
-      p[0] = x0; p[hn] = x1; p[hn*kAP] = x2; p[hn*kAP + hn] = x3;
+// The forward direction (bottom-up merge) of a whole tile in ONE step: lane j < 16
+// takes unit j of the tile -- the DCs of its 4x4 blocks if it is split -- and the levels
+// above travel by shuffle: the four lanes of a 16x16 quadrant exchange their unit DCs,
+// the lanes 0, 2, 8, 10 the quadrant DCs (luma only: in 4:2:0 chroma the tile is four
+// superblocks).  Every lane of a group computes the group's butterfly redundantly and
+// keeps its own output.  Called by the whole warp.
+__device__ __forceinline__ void region_dc_merge_tile(int *At, const unsigned char *ls0, int lane,
+                                                     bool luma) {
+  const int uy = (lane >> 2) & 3, ux = lane & 3;
+  int *U = At + 8*uy*kAP + 8*ux;
+  const bool act = lane < 16;
+  int vu = 0, L = 3, Lq = 3;
+  if (act) {
+    L = ls0[uy*kUS + ux];
+    Lq = ls0[(uy & 2)*kUS + (ux & 2)];            // leaf size at the quadrant's origin
+    vu = U[0];
+    if (L == 0) {
+      int c1 = U[4], c2 = U[4*kAP], c3 = U[4*kAP + 4];
+      haar2x2(vu, c2, c1, c3);
+      U[4] = c1; U[4*kAP] = c2; U[4*kAP + 4] = c3;
     }
   }
+  {
+    const int base = lane & ~5;
+    int a0 = __shfl_sync(0xffffffffu, vu, base), a1 = __shfl_sync(0xffffffffu, vu, base + 1);
+    int a2 = __shfl_sync(0xffffffffu, vu, base + 4), a3 = __shfl_sync(0xffffffffu, vu, base + 5);
+    if (Lq < 2) {
+      haar2x2(a0, a2, a1, a3);
+      vu = (lane & 4) ? ((lane & 1) ? a3 : a2) : ((lane & 1) ? a1 : a0);
+    }
+  }
+  if (luma) {
+    const int L0 = __shfl_sync(0xffffffffu, L, 0);
+    int q0 = __shfl_sync(0xffffffffu, vu, 0), q1 = __shfl_sync(0xffffffffu, vu, 2);
+    int q2 = __shfl_sync(0xffffffffu, vu, 8), q3 = __shfl_sync(0xffffffffu, vu, 10);
+    if (L0 < 3 && !(lane & 5)) {
+      haar2x2(q0, q2, q1, q3);
+      vu = (lane & 8) ? ((lane & 2) ? q3 : q2) : ((lane & 2) ? q1 : q0);
+    }
+  }
+  if (act) U[0] = vu;
   __syncwarp();
 }
 
