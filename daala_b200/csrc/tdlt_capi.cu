@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <vector>
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include "../../include/daala_tdlt.h"
@@ -18,6 +20,10 @@ using namespace tdlt;
 static std::atomic<long long> g_launches{0};
 constexpr int kMaxChunks = 64;   // pipeline depth of one host-pointer call
 
+// Region orders of the inverse kernel: rows of regions in flight per frame, by batch size.
+constexpr int kOrderTables = 3;
+constexpr int kOrderBands[kOrderTables] = {3, 8, 24};
+
 struct od_tdlt_ctx {
   od_tdlt_geometry g;
   int device;
@@ -28,6 +34,7 @@ struct od_tdlt_ctx {
   // strip exchange of the inverse kernel
   int2 *strips;                 // (sample, epoch) pairs, kRegionStripInts per region
   int *ticket;
+  unsigned short *order;        // inverse kernel: kOrderTables orders of the region positions of a frame
   unsigned char *plan;          // kPlanBytes per region of the largest batch so far
   long long plan_regions;
   const unsigned char *plan_maps;   // what the records in `plan` were built from
@@ -170,6 +177,40 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
       if (!ok) { rc = OD_TDLT_EFAULT; break; }
     }
     if (cudaMalloc(&ctx->ticket, 256) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
+    {
+      // The order in which the inverse kernel's tickets walk the regions of a frame
+      // (tdlt_inv_region.cu): plane by plane, by rx + S*ry -- every region comes after
+      // the regions left of, above and above-left of it for any S >= 1.  S = nrx is
+      // raster order (one row of regions in flight per frame: the smallest working set
+      // of pages); S = nrx / b puts b rows in flight and the left neighbour b * nframes
+      // tickets back.  Measured (64 4K frames, ms per launch incl. plan): frame-major
+      // raster 2.23, b = 1: 2.12, 2: 2.09, 3: 2.08, 5: 2.08, 8: 2.09, diagonals: 2.14 /
+      // 2.25.  Three tables, the batch size picks one: about 200 tickets of distance.
+      // TDLT_INV_BANDS (experiments) overrides b of all three.
+      if (rb.regs_per_frame > 65535) { rc = OD_TDLT_EINVAL; break; }
+      const int nreg = rb.regs_per_frame;
+      std::vector<unsigned short> order((size_t)kOrderTables*nreg);
+      for (int tb = 0; tb < kOrderTables; tb++) {
+        int bands = kOrderBands[tb];
+        if (const char *e = getenv("TDLT_INV_BANDS")) bands = std::max(1, atoi(e));
+        std::vector<unsigned long long> key;
+        for (int p = 0; p < g->nplanes; p++) {
+          const RegionPlane &rp = rb.pl[p];
+          const int S = std::max(1, (rp.nrx + bands - 1)/bands);
+          for (int ry = 0; ry < rp.nry; ry++) {
+            for (int rx = 0; rx < rp.nrx; rx++) {
+              key.push_back(((unsigned long long)p << 48) | ((unsigned long long)(rx + S*ry) << 16) |
+                            (unsigned long long)(rp.reg0 + ry*rp.nrx + rx));
+            }
+          }
+        }
+        std::sort(key.begin(), key.end());
+        for (int i = 0; i < nreg; i++) order[(size_t)tb*nreg + i] = (unsigned short)(key[i] & 0xffff);
+      }
+      if (cudaMalloc(&ctx->order, order.size()*sizeof(unsigned short)) != cudaSuccess ||
+          cudaMemcpy(ctx->order, order.data(), order.size()*sizeof(unsigned short),
+                     cudaMemcpyHostToDevice) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
+    }
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
@@ -207,6 +248,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
+  cudaFree(ctx->order);
   cudaFree(ctx->plan);
   for (int k = 0; k < kMaxChunks; k++) {
     if (ctx->ev_in[k]) cudaEventDestroy(ctx->ev_in[k]);
@@ -276,6 +318,7 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   memset(&maps, 0, sizeof(maps));
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
+  rb.inv_nframes = 1.0f/(float)nframes;
   rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
   PlanePtrs out;
   memset(&out, 0, sizeof(out));
@@ -319,6 +362,7 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaSetDevice(ctx->device));
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
+  rb.inv_nframes = 1.0f/(float)nframes;
   rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
@@ -342,7 +386,8 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
   tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch);
+      maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch,
+      ctx->order + (size_t)(nframes >= 48 ? 0 : (nframes >= 16 ? 1 : 2))*rb.regs_per_frame);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

@@ -77,7 +77,8 @@ __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
-                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch) {
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
+                       const unsigned short *__restrict__ order) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
@@ -90,12 +91,22 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   __syncthreads();
   const int t = s.dyn[0];
   TDLT_MARK(t, 0);
-  // t / regs_per_frame by a float estimate and one correction step (exact: the
-  // estimate is within 1 of the quotient for every t < 2^31)
-  int frame = __float2int_rz(__int2float_rz(t)*bd.inv_rpf);
-  int rloc = t - frame*bd.regs_per_frame;
-  if (rloc < 0) { frame--; rloc += bd.regs_per_frame; }
-  else if (rloc >= bd.regs_per_frame) { frame++; rloc -= bd.regs_per_frame; }
+  // Ticket -> region.  Consecutive tickets go to the SAME region position of consecutive
+  // frames, and the positions of a frame are taken in the order of order[] (built by the
+  // host, tdlt_capi.cu: a few rows of regions at a time, skewed): the regions a region
+  // waits for -- left, above, above-left -- drew their tickets at least a few times
+  // nframes earlier, so their strips are there when it starts and nobody polls, while
+  // the regions in flight still touch only a few rows of every frame.  (With a small
+  // batch some may poll: the dependencies still have smaller tickets, which is all the
+  // protocol needs.)
+  // t / nframes by a float estimate and one correction step (exact: the estimate is
+  // within 1 of the quotient for every t < 2^31)
+  int k = __float2int_rz(__int2float_rz(t)*bd.inv_nframes);
+  int frame = t - k*bd.nframes;
+  if (frame < 0) { k--; frame += bd.nframes; }
+  else if (frame >= bd.nframes) { k++; frame -= bd.nframes; }
+  const int rloc = (TDLT_ABLATE & 512) ? k : (int)__ldg(order + k);
+  const int lin = frame*bd.regs_per_frame + rloc;     // index of the plan record / strip
   const RegionId id = decode_region(bd, frame, rloc);
   const RegionPlane &pd = bd.pl[id.pli];
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
@@ -108,20 +119,19 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   if (tid == 0) {
     mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
     tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
-    bulk_g2s(s.ls, plan + (size_t)t*kPlanBytes, kPlanBytes, s.bar);
+    bulk_g2s(s.ls, plan + (size_t)lin*kPlanBytes, kPlanBytes, s.bar);
   }
   // ---- the ring of raw samples from the regions above / left / above-left: one
-  // int2 per thread.  The regions above finished long ago as a rule: their part is
-  // read now and put into the halo of A once the box has landed; what is not there
-  // yet (the left neighbour, which started just before this region) is waited for
-  // after the transforms.
+  // int2 per thread.  With the ticket order above they finished long ago as a rule:
+  // the ring is read now and put into the halo of A once the box has landed; what is
+  // not there yet (small batches) is waited for after the transforms.
   bool ring_done;
   int2 ring_val = make_int2(0, 0);
-  RingSlot rs = ring_slot(s.A, strips, t, pd.nrx, id.rx > 0, id.ry > 0, tid);
+  RingSlot rs = ring_slot(s.A, strips, lin, pd.nrx, id.rx > 0, id.ry > 0, tid);
   bool ring_early = false;
   {
     ring_done = !rs.need || (TDLT_ABLATE & 32);
-    if (rs.need && (tid < 128 || tid >= 192)) {
+    if (rs.need) {
       int2 p0 = ld_pair(rs.src), p1 = ld_pair(rs.src + 1);
       ring_early = p0.y == epoch && p1.y == epoch;
       ring_val = make_int2(p0.x, p1.x);
@@ -244,7 +254,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
 
   // ---- publish my bottom rows / right columns (raw iDCT output) ---------------
   if (tid < 192) {
-    int2 *mine = strips + (size_t)t*kStripInts;
+    int2 *mine = strips + (size_t)lin*kStripInts;
     int2 val;
     int at;
     if (tid < 128) {          // rows 62, 63: 2 x 128 samples

@@ -28,7 +28,8 @@ __global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ plan,
                                        PlanePtrs out, int2 *__restrict__ strips,
-                                       int *__restrict__ ticket, int epoch);
+                                       int *__restrict__ ticket, int epoch,
+                                       const unsigned short *__restrict__ order);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;
 
 }  // namespace tdlt

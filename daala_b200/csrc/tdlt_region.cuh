@@ -45,7 +45,8 @@ extern __device__ long long *g_tdlt_trace;
 
 // Experiment switches (tools/variants.py builds libraries with them; the product
 // build leaves them at their defaults): minimum CTAs per SM the kernels are compiled
-// for, and phases to skip when measuring what a phase costs (results are then wrong).
+// for, and phases to skip when measuring what a phase costs (results are then wrong;
+// 512: inverse takes the regions of a frame in raster order -- still right).
 #ifndef TDLT_MINB
 #define TDLT_MINB 5
 #endif
@@ -102,6 +103,7 @@ struct RegionBatch {
   float inv_rpf;          // 1 / regs_per_frame
   int groups_per_frame;   // plan kernel grid
   int nframes;
+  float inv_nframes;      // 1 / nframes
   int pic_w, pic_h;      // LUMA picture size (gates the split filters)
   int bw, bh;            // block-size map: entries across / down (8x8 luma units)
   int flags;             // OD_TDLT_KEYFRAME | OD_TDLT_HAAR
