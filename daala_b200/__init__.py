@@ -52,6 +52,7 @@ def lib():
         L.od_tdlt_last_error.argtypes = [vp]
         L.od_tdlt_last_error.restype = C.c_char_p
         L.od_tdlt_launch_count.restype = ll
+        L.od_tdlt_region_order.argtypes = [C.POINTER(Geometry), ci, vp, ci]
         arr = C.POINTER(vp)
         L.od_tdlt_fwd_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_inv_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
@@ -207,6 +208,22 @@ class TdltContext:
             self._h, _ptr_array([a.ctypes.data for a in pix_planes]), ys, fs,
             _ptr_array([a.ctypes.data for a in d_planes]), bsize.ctypes.data, n, flags,
             xstride, bitdepth_mode, lossless), "od_tdlt_inv_frames_pix")
+
+
+def region_order(pic_width, pic_height, decs=(0, 1, 1), rows_in_flight=3):
+    """Host-only: the order in which the inverse kernel walks the regions of a frame
+    (od_tdlt_region_order).  Returns a numpy uint16 array of region indices."""
+    import numpy as np
+    g = Geometry()
+    g.pic_width, g.pic_height, g.nplanes = pic_width, pic_height, len(decs)
+    for i, d in enumerate(decs):
+        g.xdec[i] = d
+        g.ydec[i] = d
+    out = np.zeros(65536, np.uint16)
+    n = lib().od_tdlt_region_order(C.byref(g), rows_in_flight, out.ctypes.data, out.size)
+    if n < 0:
+        raise TdltError("od_tdlt_region_order failed: %d" % n)
+    return out[:n].copy()
 
 
 def launch_count():

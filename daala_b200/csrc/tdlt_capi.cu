@@ -109,7 +109,55 @@ static int make_tmap(od_tdlt_ctx *ctx, CUtensorMap *m, const void *base, int w, 
   return OD_TDLT_SUCCESS;
 }
 
+// The order in which the inverse kernel's tickets walk the region positions of a frame
+// (tdlt_inv_region.cu): plane by plane, by rx + S*ry -- every region comes after the
+// regions left of, above and above-left of it for any S >= 1.  S = nrx is raster order
+// (one row of regions in flight per frame: the smallest working set of pages); S =
+// nrx / b puts b rows in flight and the left neighbour b * nframes tickets back.
+// Host only; order[] gets regs_per_frame region indices (reg0 + ry*nrx + rx).
+struct OrderPlane { int nrx, nry, reg0; };
+static void build_region_order(const OrderPlane *pl, int nplanes, int bands,
+                               std::vector<unsigned short> &order) {
+  std::vector<unsigned long long> key;
+  for (int p = 0; p < nplanes; p++) {
+    const int S = std::max(1, (pl[p].nrx + bands - 1)/bands);
+    for (int ry = 0; ry < pl[p].nry; ry++) {
+      for (int rx = 0; rx < pl[p].nrx; rx++) {
+        key.push_back(((unsigned long long)p << 48) | ((unsigned long long)(rx + S*ry) << 16) |
+                      (unsigned long long)(pl[p].reg0 + ry*pl[p].nrx + rx));
+      }
+    }
+  }
+  std::sort(key.begin(), key.end());
+  order.resize(key.size());
+  for (size_t i = 0; i < key.size(); i++) order[i] = (unsigned short)(key[i] & 0xffff);
+}
+
 extern "C" {
+
+int od_tdlt_region_order(const od_tdlt_geometry *g, int rows_in_flight, unsigned short *order,
+                         int capacity) {
+  if (!g || !order) return OD_TDLT_EFAULT;
+  if (g->nplanes < 1 || g->nplanes > kMaxPlanes || g->pic_width < 1 || g->pic_height < 1 ||
+      rows_in_flight < 1) {
+    return OD_TDLT_EINVAL;
+  }
+  OrderPlane pl[kMaxPlanes];
+  int reg0 = 0;
+  for (int p = 0; p < g->nplanes; p++) {
+    if (g->xdec[p] != g->ydec[p] || g->xdec[p] < 0 || g->xdec[p] > 1) return OD_TDLT_EINVAL;
+    const int w = ((g->pic_width + 63) & ~63) >> g->xdec[p], h = ((g->pic_height + 63) & ~63) >> g->xdec[p];
+    pl[p].nrx = (w + kRegW - 1)/kRegW;
+    pl[p].nry = (h + kRegH - 1)/kRegH;
+    pl[p].reg0 = reg0;
+    reg0 += pl[p].nrx*pl[p].nry;
+  }
+  if (reg0 > 65535 || reg0 > capacity) return OD_TDLT_EINVAL;
+  std::vector<unsigned short> v;
+  build_region_order(pl, g->nplanes, rows_in_flight, v);
+  memcpy(order, v.data(), v.size()*sizeof(unsigned short));
+  return reg0;
+}
 
 int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
                        int max_frames) {
@@ -178,34 +226,22 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     }
     if (cudaMalloc(&ctx->ticket, 256) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
     {
-      // The order in which the inverse kernel's tickets walk the regions of a frame
-      // (tdlt_inv_region.cu): plane by plane, by rx + S*ry -- every region comes after
-      // the regions left of, above and above-left of it for any S >= 1.  S = nrx is
-      // raster order (one row of regions in flight per frame: the smallest working set
-      // of pages); S = nrx / b puts b rows in flight and the left neighbour b * nframes
-      // tickets back.  Measured (64 4K frames, ms per launch incl. plan): frame-major
-      // raster 2.23, b = 1: 2.12, 2: 2.09, 3: 2.08, 5: 2.08, 8: 2.09, diagonals: 2.14 /
-      // 2.25.  Three tables, the batch size picks one: about 200 tickets of distance.
-      // TDLT_INV_BANDS (experiments) overrides b of all three.
+      // Region orders of the inverse kernel (build_region_order above).  Measured (64 4K
+      // frames, ms per launch incl. plan): frame-major raster 2.23; frame-interleaved with
+      // b = 1 / 2 / 3 / 5 / 8 rows of regions in flight 2.12 / 2.09 / 2.08 / 2.08 / 2.09;
+      // whole diagonals 2.14 - 2.25.  Three tables, the batch size picks one: about 200
+      // tickets between a region and its left neighbour.  TDLT_INV_BANDS (experiments)
+      // overrides b of all three.
       if (rb.regs_per_frame > 65535) { rc = OD_TDLT_EINVAL; break; }
       const int nreg = rb.regs_per_frame;
-      std::vector<unsigned short> order((size_t)kOrderTables*nreg);
+      std::vector<unsigned short> order((size_t)kOrderTables*nreg), one;
+      OrderPlane opl[kMaxPlanes];
+      for (int p = 0; p < g->nplanes; p++) opl[p] = OrderPlane{rb.pl[p].nrx, rb.pl[p].nry, rb.pl[p].reg0};
       for (int tb = 0; tb < kOrderTables; tb++) {
         int bands = kOrderBands[tb];
         if (const char *e = getenv("TDLT_INV_BANDS")) bands = std::max(1, atoi(e));
-        std::vector<unsigned long long> key;
-        for (int p = 0; p < g->nplanes; p++) {
-          const RegionPlane &rp = rb.pl[p];
-          const int S = std::max(1, (rp.nrx + bands - 1)/bands);
-          for (int ry = 0; ry < rp.nry; ry++) {
-            for (int rx = 0; rx < rp.nrx; rx++) {
-              key.push_back(((unsigned long long)p << 48) | ((unsigned long long)(rx + S*ry) << 16) |
-                            (unsigned long long)(rp.reg0 + ry*rp.nrx + rx));
-            }
-          }
-        }
-        std::sort(key.begin(), key.end());
-        for (int i = 0; i < nreg; i++) order[(size_t)tb*nreg + i] = (unsigned short)(key[i] & 0xffff);
+        build_region_order(opl, g->nplanes, bands, one);
+        memcpy(&order[(size_t)tb*nreg], one.data(), (size_t)nreg*sizeof(unsigned short));
       }
       if (cudaMalloc(&ctx->order, order.size()*sizeof(unsigned short)) != cudaSuccess ||
           cudaMemcpy(ctx->order, order.data(), order.size()*sizeof(unsigned short),

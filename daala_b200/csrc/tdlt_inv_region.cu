@@ -13,10 +13,16 @@
 // neighbours.  Every region publishes those strips to global memory as 8-byte
 // (sample, epoch) pairs -- an aligned 8-byte store is indivisible, so a reader
 // that sees the epoch of this launch has the sample too: no flag, no fence --
-// and consumers poll the pairs of regions that precede them in a TICKET order
+// and consumers take the pairs of regions that precede them in a TICKET order
 // (CTAs draw tickets in the order they start running, so a region only ever
-// waits on work that is already resident: no deadlock, and on average the
-// producer is ahead because it started first).
+// waits on work that is already resident: no deadlock).  The tickets walk the
+// batch frame-interleaved, a few skewed rows of regions of every frame at a
+// time, so that a region's producers are hundreds of tickets ahead and their
+// strips are there when it starts (see the ticket -> region mapping below).
+//
+// Phases: ticket, TMA box + plan record, ring fetch | DC pyramid top-down |
+// inverse transforms in place (class-sorted warp tasks) | publish | un-lapping of
+// the levels 8 .. superblock fused with the store (unlap_block_store).
 #include "tdlt_tasks.cuh"
 #include "tdlt_region.cuh"
 #include "tdlt_kernels.h"
@@ -289,7 +295,6 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   // (unlap_block_store, tdlt_region.cuh); where the plane ends in this region the
   // blocks holding columns 126, 127 make one more task.
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
-#ifndef TDLT_INV_PHASES
   TDLT_MARK(t, 7);
   {
     const int b0 = (id.ry == 0) ? 2 : 0;
@@ -309,56 +314,6 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
       unlap_block_store<false>(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);
     }
   }
-#else
-  // ---- un-lap, fine to coarse: the forward sequence backwards ------------------
-#ifndef TDLT_LAP_BLOCKS
-#pragma unroll 1
-  for (int lv = (TDLT_ABLATE & 1) ? 64 : 8; lv <= sb; lv <<= 1) {
-    region_lap_rows<true>(s.A, s.msk, lv, sb, warp, lane, last_r);
-    __syncthreads();
-    region_lap_cols<true>(s.A, s.msk, lv, sb, warp, lane);
-    __syncthreads();
-  }
-#else
-  if (!(TDLT_ABLATE & 1)) {
-    region_lap_blocks<true>(s.A, s.ub, sb, warp, lane, last_r ? 9 : 8, last_c ? 17 : 16, 8, 16);
-  }
-  __syncthreads();
-#endif
-  TDLT_MARK(t, 7);
-  // ---- store the owned rectangle: buffer row b <-> plane row Y0 - 2 + b ---------
-  // The owned columns cs .. ce-1 (cs = -2, or 0 in the first region column; ce = 126,
-  // or where the plane ends) are at most 128 and start on an 8-byte boundary: every
-  // row goes out as two warp-wide runs of 8-byte vectors, lane = column pair (plus
-  // one more pair in the last region column of a plane wider than one region).
-  {
-    const int b0 = (id.ry == 0) ? 2 : 0;
-    const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
-    const int cs = (id.rx > 0) ? -2 : 0;
-    const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
-    const int c0 = cs + 2*lane, c1 = c0 + 64;
-    const bool on0 = c0 < ce, on1 = c1 < ce;
-    const bool on2 = c0 + 128 < ce;     // lane 0 of the last region column: columns 126, 127
-    const bool any2 = last_c && id.rx > 0;                // warp-uniform
-    const size_t pitch8 = (size_t)pd.w*kRegWarps;
-    int *gr = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2 + b0 + warp)*(ptrdiff_t)pd.w + X0 + c0;
-    const int *arow = s.A + (b0 + warp)*kAP + 4 + c0;
-    const int nb = b1 - b0 - warp;
-#pragma unroll
-    for (int k = 0; k < 9; k++) {
-      if (kRegWarps*k < nb) {
-        const int *ar = arow + k*kRegWarps*kAP;
-        if (TDLT_ABLATE & 128) continue;
-        if (on0) *reinterpret_cast<int2 *>(gr) = *reinterpret_cast<const int2 *>(ar);
-        if (on1) *reinterpret_cast<int2 *>(gr + 64) = *reinterpret_cast<const int2 *>(ar + 64);
-        if (any2 && on2) {
-          *reinterpret_cast<int2 *>(gr + 128) = *reinterpret_cast<const int2 *>(ar + 128);
-        }
-        gr += pitch8;
-      }
-    }
-  }
-#endif
   TDLT_MARK(t, 8);
 }
 

@@ -194,6 +194,16 @@ void od_apply_prefilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nv
 void od_apply_postfilter_frame_sbs_cuda(od_coeff *c, int stride, int nhsb, int nvsb,
  int xdec, int ydec, int q, unsigned char *skip, int skip_stride);
 
+/* Introspection (host only, no device needed): the order in which the inverse
+   kernel walks the 128x64 regions of one frame when `rows_in_flight` rows of
+   regions are in flight per frame -- region indices plane by plane, row-major
+   within a plane.  A region's strip exchange (tdlt_inv_region.cu) only needs its
+   left / upper / upper-left neighbours to come earlier in this order; the tests
+   check exactly that.  Returns the number of regions of a frame (<= capacity), or
+   a negative OD_TDLT_* code. */
+int od_tdlt_region_order(const od_tdlt_geometry *g, int rows_in_flight, unsigned short *order,
+                         int capacity);
+
 /* Number of kernel launches issued by this library since load (bench.py's
    gpu_launches claim is read from here). */
 long long od_tdlt_launch_count(void);

@@ -136,3 +136,37 @@ def test_post_filter_division_is_exact(hostlib):
     multiply-high each: exact over the whole range in which t*64 fits an int."""
     hostlib.post_div_mismatches.restype = C.c_longlong
     assert hostlib.post_div_mismatches(1 << 25) == 0
+
+
+@pytest.mark.parametrize("size", [(3840, 2160), (1920, 1080), (352, 288), (100, 60), (33, 17)])
+@pytest.mark.parametrize("rows", [1, 3, 8, 24, 1000])
+def test_inverse_region_order_keeps_every_dependency_ahead(size, rows):
+    """The inverse kernel's regions wait for the strips of their left / upper / upper-left
+    neighbours and draw tickets in the order of this table (frame-interleaved), so the
+    table must be a permutation of a frame's regions in which every region comes after
+    those three -- whatever the skew (rows of regions in flight)."""
+    import daala_b200
+    pic_w, pic_h = size
+    decs = (0, 1, 1)
+    order = daala_b200.region_order(pic_w, pic_h, decs, rows)
+    fw, fh = (pic_w + 63) & ~63, (pic_h + 63) & ~63
+    planes, reg0 = [], 0
+    for d in decs:
+        nrx, nry = ((fw >> d) + 127)//128, ((fh >> d) + 63)//64
+        planes.append((reg0, nrx, nry))
+        reg0 += nrx*nry
+    assert sorted(order.tolist()) == list(range(reg0))
+    pos = np.empty(reg0, np.int64)
+    pos[order] = np.arange(reg0)
+    for r0, nrx, nry in planes:
+        for ry in range(nry):
+            for rx in range(nrx):
+                me = pos[r0 + ry*nrx + rx]
+                if rx > 0:
+                    assert pos[r0 + ry*nrx + rx - 1] < me
+                if ry > 0:
+                    assert pos[r0 + (ry - 1)*nrx + rx] < me
+                if rx > 0 and ry > 0:
+                    assert pos[r0 + (ry - 1)*nrx + rx - 1] < me
+    if rows == 1:         # raster order within each plane
+        assert order.tolist() == list(range(reg0))
