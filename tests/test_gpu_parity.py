@@ -60,6 +60,27 @@ def test_frames_match_checker(pic_w, pic_h, kind, key):
     chk.close()
 
 
+@pytest.mark.parametrize("nframes", [5, 20, 50])
+def test_inverse_batch_sizes_pick_every_region_order(nframes):
+    """The inverse kernel walks the batch frame-interleaved and picks one of three region
+    orders by batch size (< 16, < 48, >= 48 frames): each of them, on a plane that is several
+    regions wide and high, must give the checker's samples for arbitrary coefficients."""
+    import daala_b200
+    rng = np.random.default_rng(900 + nframes)
+    pic_w, pic_h = 400, 250            # 448 x 256 padded: luma 4 x 4 regions, chroma 2 x 2
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        bsize = make_maps("quad", nframes, ctx.nhsb, ctx.nvsb, rng)
+        dq = _rand_planes(ctx.plane_shapes, nframes, rng, -20000, 20000)
+        c2 = [np.zeros_like(a) for a in dq]
+        for rep in range(2):           # twice: the strip buffer is reused with a new epoch
+            ctx.inv_frames(c2, dq, bsize, daala_b200.OD_TDLT_KEYFRAME)
+            c_ref = chk.inv_frames(dq, bsize, DECS, 1)
+            for p in range(3):
+                assert np.array_equal(c2[p], c_ref[p]), "inverse plane %d" % p
+    chk.close()
+
+
 @pytest.mark.parametrize("decs", [(0,), (0, 0, 0), (0, 1, 1, 0)])
 def test_other_plane_layouts(decs):
     import daala_b200
