@@ -165,9 +165,13 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   }
 
   // ---- keyframe: undo the DC pyramid, top-down --------------------------------
-  if ((bd.flags & 1) && tile_on && !(TDLT_ABLATE & 4)) {
-    const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-    region_dc_split_tile(At, ls0, lane, pd.dec == 0);
+  // (16 lanes per tile: the warps 0..3 take two tiles each, half the instructions of one
+  // tile per warp)
+  if ((bd.flags & 1) && warp < kRegTiles/2 && !(TDLT_ABLATE & 4)) {
+    const int tl = 2*warp + (lane >> 4), ttx = tl & 3, tty = tl >> 2;
+    const bool on = X0 + 32*ttx < pd.w && Y0 + 32*tty < pd.h;
+    region_dc_split_tile(s.A + (32*tty + 2)*kAP + 32*ttx + 4, s.ls + ut(4*tty, 4*ttx), lane & 15,
+                         on, pd.dec == 0);
   }
   __syncthreads();
   TDLT_MARK(t, 3);

@@ -488,13 +488,13 @@ __device__ __forceinline__ void unlap_block_store(const int *A, const unsigned c
     return;
   }
   if (tr) f = ((f & 3) << 2) | (f >> 2);       // on the transposed block rows and columns swap
-  transpose4_if(x, tr);
+  if (ei) transpose4_if(x, tr);                // (bi is warp-uniform here: odd rows skip it)
   const bool colL = f & 1, colR = f & 2, rowT = f & 4, rowB = f & 8;
   if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
   if (colR) { post4(x[0][2], x[1][2], x[2][2], x[3][2]); post4(x[0][3], x[1][3], x[2][3], x[3][3]); }
   if (rowT) { post4(x[0][0], x[0][1], x[0][2], x[0][3]); post4(x[1][0], x[1][1], x[1][2], x[1][3]); }
   if (rowB) { post4(x[2][0], x[2][1], x[2][2], x[2][3]); post4(x[3][0], x[3][1], x[3][2], x[3][3]); }
-  transpose4_if(x, tr);
+  if (ei) transpose4_if(x, tr);
   {
     // columns 4bj .. 4bj+3 are all mine and the right half is in the warp (lane 31's is
     // not: where the plane ends there, columns 126, 127 are the extra task's)
@@ -720,14 +720,15 @@ __device__ __forceinline__ void region_dc_merge_tile(int *At, const unsigned cha
 // before any split; lanes that share ancestors compute them redundantly.  Every lane
 // reads first, then writes the DC(s) at positions inside its own unit: no ordering
 // between levels through shared memory.  luma: the tile is one 32x32 superblock;
-// chroma (4:2:0): four 16x16 superblocks.
+// chroma (4:2:0): four 16x16 superblocks.  lane = 0..15 (the unit), act = the tile is
+// inside the plane; At / ls0 may differ between the two halves of a warp (two tiles per
+// warp).  Called by the whole warp.
 __device__ __forceinline__ void region_dc_split_tile(int *At, const unsigned char *ls0, int lane,
-                                                     bool luma) {
+                                                     bool act, bool luma) {
   const int uy = (lane >> 2) & 3, ux = lane & 3, qy = uy >> 1, qx = ux >> 1;
   int *Q = At + 16*qy*kAP + 16*qx;            // my quadrant
   int *U = At + 8*uy*kAP + 8*ux;              // my unit
   int vq, b1, b2, b3, c1 = 0, c2 = 0, c3 = 0;
-  const bool act = lane < 16;
   const int L = act ? ls0[uy*kUS + ux] : 3;
   if (act) {
     vq = Q[0];
