@@ -41,6 +41,9 @@ WORKLOADS = {
 DECS = (0, 1, 1)
 
 
+_REAL_STDOUT = None
+
+
 def make_maps_np(kind, nframes, nhsb, nvsb, seed):
     """Vectorised random quadtree (split 32 w.p. .8, 16 w.p. .6, 8 w.p. .5)."""
     rng = np.random.default_rng(seed)
@@ -237,9 +240,14 @@ def main():
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
-        # stdout carries exactly one JSON line: keep NCCL's version banner (printed to stdout
-        # at NCCL_DEBUG=VERSION / INFO) out of it
-        os.environ["NCCL_DEBUG"] = "WARN"
+        # stdout carries exactly one JSON line: NCCL writes its version banner to fd 1 from
+        # C (at WARN level too), so fd 1 points at stderr while the job runs and the line is
+        # written to the saved descriptor at the end
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
+        sys.stdout.flush()
+        global _REAL_STDOUT
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
@@ -448,7 +456,11 @@ def main():
                 "data": "synthetic", "config": config, "clocks": clocks, "roofline": roof,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "round_trip_exact": True}
-        print(json.dumps(line))
+        if _REAL_STDOUT is not None:
+            sys.stdout.flush()
+            os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+        else:
+            print(json.dumps(line))
     ctx.close()
     if dist:
         dist.destroy_process_group()
