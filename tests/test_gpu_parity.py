@@ -316,6 +316,35 @@ def test_full_size_properties():
     chk.close()
 
 
+def test_8k_frame_matches_checker():
+    """The largest frame the region index allows comfortably (7680x4320 4:2:0: 60 x 68 luma
+    regions, 6120 regions per frame): forward against the checker, inverse of arbitrary
+    coefficients against the checker, exact round trip -- non-keyframe and keyframe."""
+    import daala_b200
+    rng = np.random.default_rng(8000)
+    pic_w, pic_h = 7680, 4320
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, 1) as ctx:
+        bsize = make_maps("quad", 1, ctx.nhsb, ctx.nvsb, rng)
+        c = _rand_planes(ctx.plane_shapes, 1, rng)
+        for key in (0, 1):
+            flags = daala_b200.OD_TDLT_KEYFRAME if key else 0
+            d = [np.zeros_like(a) for a in c]
+            ctx.fwd_frames(d, c, bsize, flags)
+            d_ref = chk.fwd_frames(c, bsize, DECS, key)
+            c2 = [np.zeros_like(a) for a in c]
+            ctx.inv_frames(c2, d, bsize, flags)
+            for p in range(3):
+                assert np.array_equal(d[p], d_ref[p]), "forward plane %d key %d" % (p, key)
+                assert np.array_equal(c2[p], c[p]), "round trip plane %d key %d" % (p, key)
+        dq = _rand_planes(ctx.plane_shapes, 1, rng, -30000, 30000)
+        ctx.inv_frames(c2, dq, bsize, daala_b200.OD_TDLT_KEYFRAME)
+        c_ref = chk.inv_frames(dq, bsize, DECS, 1)
+        for p in range(3):
+            assert np.array_equal(c2[p], c_ref[p]), "inverse plane %d" % p
+    chk.close()
+
+
 def test_device_batches_plan_reuse_and_stress():
     """Device-pointer batch calls on a 16-frame 1080p batch, run three times on the same
     buffers (the inverse kernel's strip exchange reuses its buffer with a new epoch each
