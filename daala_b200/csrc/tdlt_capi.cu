@@ -249,8 +249,12 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     }
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+    cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+    cudaFuncSetAttribute(tdlt_inv_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(tdlt_inv_haar_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (max_frames > 0) {
       bool ok = true;
       for (int p = 0; p < g->nplanes && ok; p++) {
@@ -370,8 +374,14 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   int prc = launch_plan(ctx, rb, bsize, nframes, flags, (cudaStream_t)stream);
   if (prc) return prc;
   dim3 grid((unsigned)rb.regs_per_frame, (unsigned)nframes);
-  tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
-      maps, rb, ctx->plan, out);
+  if (rb.flags & OD_TDLT_HAAR) {
+    tdlt_fwd_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
+        maps, rb, ctx->plan, out);
+  }
+  else {
+    tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
+        maps, rb, ctx->plan, out);
+  }
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
@@ -421,9 +431,16 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   if (rc) return rc;
   CK(ctx, cudaMemsetAsync(ctx->ticket, 0, sizeof(int), st));
   ctx->epoch++;
-  tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
-      maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch,
-      ctx->order + (size_t)(nframes >= 48 ? 0 : (nframes >= 16 ? 1 : 2))*rb.regs_per_frame);
+  const unsigned short *order =
+      ctx->order + (size_t)(nframes >= 48 ? 0 : (nframes >= 16 ? 1 : 2))*rb.regs_per_frame;
+  if (rb.flags & OD_TDLT_HAAR) {
+    tdlt_inv_haar_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+  }
+  else {
+    tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+  }
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;

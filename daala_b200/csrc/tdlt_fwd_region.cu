@@ -18,9 +18,9 @@ namespace tdlt {
 __device__ long long *g_tdlt_trace = nullptr;
 #endif
 
-__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
-tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
-                       const __grid_constant__ RegionBatch bd,
+template <bool kHaar>
+__device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
+                       const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -29,7 +29,7 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   const RegionId id = decode_region(bd, blockIdx.y, blockIdx.x);
   const RegionPlane &pd = bd.pl[id.pli];
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
-  const bool haar = (bd.flags & 2) != 0;
+  constexpr bool haar = kHaar;      // lossless mode is a kernel of its own (less code in either)
 
   // One thread starts both loads: the samples (TMA box with the halo) and the region's
   // plan record (tdlt_plan.cu), on one mbarrier.
@@ -176,5 +176,21 @@ tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
   }
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 6);
 }
+
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out) {
+  tdlt_fwd_region_body<false>(maps, bd, plan, out);
+}
+
+// Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_fwd_haar_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out) {
+  tdlt_fwd_region_body<true>(maps, bd, plan, out);
+}
+
 
 }  // namespace tdlt

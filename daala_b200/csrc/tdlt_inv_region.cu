@@ -79,9 +79,9 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
-__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
-tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
-                       const __grid_constant__ RegionBatch bd,
+template <bool kHaar>
+__device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
+                       const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order) {
@@ -116,7 +116,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   const RegionId id = decode_region(bd, frame, rloc);
   const RegionPlane &pd = bd.pl[id.pli];
   const int X0 = id.rx*kRegW, Y0 = id.ry*kRegH;
-  const bool haar = (bd.flags & 2) != 0;
+  constexpr bool haar = kHaar;      // lossless mode is a kernel of its own (less code in either)
   const int sb = 32 >> pd.dec;
 
   // ---- the region's coefficients: the same TMA box as the forward kernel's (the halo
@@ -320,5 +320,25 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
   }
   TDLT_MARK(t, 8);
 }
+
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out,
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
+                       const unsigned short *__restrict__ order) {
+  tdlt_inv_region_body<false>(maps, bd, plan, out, strips, ticket, epoch, order);
+}
+
+// Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out,
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
+                       const unsigned short *__restrict__ order) {
+  tdlt_inv_region_body<true>(maps, bd, plan, out, strips, ticket, epoch, order);
+}
+
 
 }  // namespace tdlt
