@@ -51,7 +51,6 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
     // ---- lapping, level by level, coarse to fine (level 4 is done in registers
     // by the transform tasks of the units it concerns) ---------------------------
     if (!(TDLT_ABLATE & 1)) {
-#ifndef TDLT_LAP_BLOCKS
       const int sb = 32 >> pd.dec;
 #pragma unroll 1
       for (int lv = sb; lv >= 8; lv >>= 1) {
@@ -60,10 +59,6 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
         region_lap_rows<false>(s.A, s.msk, lv, sb, warp, lane, false);
         __syncthreads();
       }
-#else
-      region_lap_blocks<false>(s.A, s.ub, 32 >> pd.dec, warp, lane, 9, 17, 9, 17);
-      __syncthreads();
-#endif
     }
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 4);
     // ---- transforms, in place: columns first, then rows (src/dct.c:137-142) ----

@@ -236,17 +236,23 @@ __device__ __forceinline__ void region_lap_cols(int *A, const unsigned *msk, int
   const int nlines = top ? (kRegH >> lg) + (kInverse ? 0 : 1) : (kRegH/2) >> lg;
   const int first = top ? 0 : lv, step = top ? sb : 2*lv;
   const int nextra = kInverse ? 1 : (top ? 2 : 0);         // extra chunks per line
+  // one call site for both kinds of task (the filter code is inlined once)
+  int yl = 0, m = 0;
+  bool on = false;
   if (warp < nlines) {
-    int yl = first + warp*step;
+    yl = first + warp*step;
+    m = lane + 1;
     // chunk m = lane + 1 lies in unit column lane >> 1, mask bit (lane >> 1) + 1
-    if ((msk[(yl >> 3) + 1] >> ((lane >> 1) + 1)) & 1) lap_chunk<kInverse>(A, yl, lane + 1);
+    on = (msk[(yl >> 3) + 1] >> ((lane >> 1) + 1)) & 1;
   }
   else if (warp == nlines && nextra) {
-    int line = lane >> 1, m = (lane & 1) ? 33 : 0;
-    int yl = first + line*step;
-    bool on = lane < 2*nlines && (lane & 1) < nextra;
-    if (on && ((msk[(yl >> 3) + 1] >> ((lane & 1) ? 17 : 0)) & 1)) lap_chunk<kInverse>(A, yl, m);
+    const int line = lane >> 1;
+    m = (lane & 1) ? 33 : 0;
+    yl = first + line*step;
+    on = lane < 2*nlines && (lane & 1) < nextra &&
+         ((msk[(yl >> 3) + 1] >> ((lane & 1) ? 17 : 0)) & 1);
   }
+  if (on) lap_chunk<kInverse>(A, yl, m);
 }
 
 // Rows: warp w takes the rows 32*(w & 1) .. +31 and the line pairs w >> 1, +4,
@@ -298,108 +304,17 @@ __device__ __forceinline__ void region_lap_rows(int *A, const unsigned *msk, int
   }
 }
 
-// ---------------------------------------------------------------------------
-// Alternative, compiled with -DTDLT_LAP_BLOCKS only (measured: bit-exact, one barrier
-// instead of six, but no faster forward and 5 % slower inverse than the level phases
-// above -- more shared-memory bank conflicts and longer per-lane chains; kept for the
-// next round's experiments).
-// The same lapping (levels 8 .. superblock) as ONE phase of independent 4x4 blocks.
-// Tile the region buffer with 4x4 blocks on the grid offset by 2 columns: block
-// (bi, bj) = buffer rows 4bi .. 4bi+3, region columns 4bj-2 .. 4bj+1.  Every filter
-// of level >= 8 lies inside exactly one block, and by the parity of (bi, bj) a block is
-//   a CELL (even, even): the crossing of the horizontal edge at row 8i with the
-//        vertical edge at column 8j -- up to four filters down its columns (the left
-//        two if unit (i, j-1) has its top edge filtered, the right two if unit (i, j)
-//        has) and four along its rows (the upper two: left edge of unit (i-1, j), the
-//        lower two: of unit (i, j)).  The coarser line goes first, the horizontal edge
-//        on a tie (the reference's order: level by level, and inside a level across the
-//        horizontal edges first); the inverse undoes them in the opposite order;
-//   HF  (even, odd): columns 2..5 of unit (i, j) across its top edge: four filters down
-//        the columns, crossed by nothing of level >= 8;
-//   VF  (odd, even): rows 2..5 of unit (i, j) across its left edge: four along the rows;
-//   (odd, odd): the inside of a unit, untouched here.
-// Blocks share no sample, so there is no order between them and no barrier inside the
-// phase.  One lane per block; a warp task is 32 blocks of one kind.
-// ---------------------------------------------------------------------------
-template <bool kInverse>
-__device__ __forceinline__ void lap_f4(int &a, int &b, int &c, int &d) {
-  if (kInverse) post4(a, b, c, d); else pre4(a, b, c, d);
-}
-// cols_first: the column filters run before the row filters (as seen by this kernel).
-template <bool kInverse>
-__device__ __forceinline__ void lap_block(int *A, int bi, int bj, bool colL, bool colR, bool rowT,
-                                          bool rowB, bool cols_first) {
-  int2 *p = reinterpret_cast<int2 *>(A + 4*bi*kAP + 4*bj + 2);
-  constexpr int S = kAP/2;
-  int2 l0 = p[0], h0 = p[1], l1 = p[S], h1 = p[S + 1];
-  int2 l2 = p[2*S], h2 = p[2*S + 1], l3 = p[3*S], h3 = p[3*S + 1];
-  if (cols_first) {
-    if (colL) { lap_f4<kInverse>(l0.x, l1.x, l2.x, l3.x); lap_f4<kInverse>(l0.y, l1.y, l2.y, l3.y); }
-    if (colR) { lap_f4<kInverse>(h0.x, h1.x, h2.x, h3.x); lap_f4<kInverse>(h0.y, h1.y, h2.y, h3.y); }
-  }
-  if (rowT) { lap_f4<kInverse>(l0.x, l0.y, h0.x, h0.y); lap_f4<kInverse>(l1.x, l1.y, h1.x, h1.y); }
-  if (rowB) { lap_f4<kInverse>(l2.x, l2.y, h2.x, h2.y); lap_f4<kInverse>(l3.x, l3.y, h3.x, h3.y); }
-  if (!cols_first) {
-    if (colL) { lap_f4<kInverse>(l0.x, l1.x, l2.x, l3.x); lap_f4<kInverse>(l0.y, l1.y, l2.y, l3.y); }
-    if (colR) { lap_f4<kInverse>(h0.x, h1.x, h2.x, h3.x); lap_f4<kInverse>(h0.y, h1.y, h2.y, h3.y); }
-  }
-  p[0] = l0; p[1] = h0; p[S] = l1; p[S + 1] = h1;
-  p[2*S] = l2; p[2*S + 1] = h2; p[3*S] = l3; p[3*S + 1] = h3;
-}
 // Level of the line at coordinate 8k: the largest power of two dividing it, capped at
 // the superblock size.
 __device__ __forceinline__ int lap_level8(int k, int sb) {
   int c = 8*k;
   return (c & (sb - 1)) == 0 ? sb : (c & -c);
 }
-// ni, nj: cells (i, j) with i < ni, j < nj are this region's (forward: 9 x 17; inverse:
-// 8 x 16, one more row / column where the plane ends); HF covers i < nih, j < 16 and VF
-// i < 8, j < njv.
-template <bool kInverse>
-__device__ __forceinline__ void region_lap_blocks(int *A, const unsigned char *ub, int sb, int warp,
-                                                  int lane, int ni, int nj, int nih, int njv) {
-  // warp tasks: [0, 5) cells, [5, 10) HF, [10, 15) VF
-#pragma unroll 1
-  for (int wt = warp; wt < 15; wt += kRegWarps) {
-    const int kind = wt >= 10 ? 2 : (wt >= 5 ? 1 : 0);
-    const int e = (wt - 5*kind)*32 + lane;
-    if (kind == 0) {
-      const int i = e/17, j = e - 17*i;
-      bool on = i < ni && j < nj;
-      int t = 0, l0 = 0, l1 = 0, tl = 0;
-      if (on) {
-        t = ub[ut(i, j)];
-        tl = ub[ut(i, j - 1)] & kUbTop;
-        l0 = ub[ut(i - 1, j)] & kUbLeft;
-        l1 = t & kUbLeft;
-        t &= kUbTop;
-      }
-      on = on && (t | tl | l0 | l1);
-      if (on) {
-        bool cf = lap_level8(i, sb) >= lap_level8(j, sb);
-        lap_block<kInverse>(A, 2*i, 2*j, tl != 0, t != 0, l0 != 0, l1 != 0, kInverse ? !cf : cf);
-      }
-    }
-    else if (kind == 1) {
-      const int i = e >> 4, j = e & 15;
-      if (i < nih && (ub[ut(i, j)] & kUbTop)) {
-        lap_block<kInverse>(A, 2*i, 2*j + 1, true, true, false, false, true);
-      }
-    }
-    else {
-      const int i = e/17, j = e - 17*i;
-      if (i < 8 && j < njv && (ub[ut(i, j)] & kUbLeft)) {
-        lap_block<kInverse>(A, 2*i + 1, 2*j, false, false, true, true, true);
-      }
-    }
-  }
-}
-
 // ---------------------------------------------------------------------------
 // Inverse tail: the un-lapping of the levels 8 .. superblock AND the store of the
 // region's owned rectangle as one barrier-free phase.  The owned rectangle (region rows
-// -2 .. 61, columns -2 .. 125) is tiled exactly by the 4x4 blocks of the offset grid
-// above -- block (bi, bj) = buffer rows 4bi .. 4bi+3, region columns 4bj-2 .. 4bj+1 --
+// -2 .. 61, columns -2 .. 125) is tiled exactly by the 4x4 blocks of the grid offset by
+// (2, 2) -- block (bi, bj) = buffer rows 4bi .. 4bi+3, region columns 4bj-2 .. 4bj+1 --
 // and every filter lies inside one block, so a lane takes one block from shared memory
 // into registers, undoes the filters that cross it (a CELL up to four along its rows
 // and four down its columns, HF / VF blocks four of one direction, the inside of a unit
