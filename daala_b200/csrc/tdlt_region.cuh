@@ -80,7 +80,10 @@ constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints, [4..7] = cla
 constexpr int kOffMsk = kOffCnt + 32;                    // 2 x 10 edge masks, right after cnt
 constexpr int kOffBar = kOffMsk + 80;
 constexpr int kPlanBytes = kOffBar - kOffLs;
-constexpr int kPlanPerCta = 4;                           // regions per CTA of tdlt_plan_kernel
+#ifndef TDLT_PLAN_PER_CTA
+#define TDLT_PLAN_PER_CTA 8
+#endif
+constexpr int kPlanPerCta = TDLT_PLAN_PER_CTA;           // regions per CTA of tdlt_plan_kernel
 constexpr int kOffDyn = kOffBar + 16;                    // [0] ticket, [1] task draw counter
 constexpr int kRegSmemBytes = kOffDyn + 16;
 static_assert(kOffCnt % 4 == 0 && kOffBar % 8 == 0 && kOffLs % 16 == 0, "alignment");
