@@ -637,6 +637,71 @@ void oc_tdlt_inv_plane(oc_coeff *c, oc_coeff *d, int nhsb, int nvsb, int dec,
   if (!use_haar) oc_apply_postfilter_frame_sbs(c, k.w, nhsb, nvsb, dec, dec);
 }
 
+/* ---------------------------------------------- chroma-from-luma predictor -- */
+
+/* reference src/intra.c:65-70 (a table of trained constants; the only data of this step) */
+static const int OC_CFL_SCALING4[4][4] = {
+  {128, 128, 100, 36},
+  {128, 80, 71, 35},
+  {100, 71, 35, 31},
+  {36, 35, 31, 18},
+};
+
+/* reference src/intra.c:72-109.  bs: chroma transform size (n = 4 << bs samples);
+   chroma_bs: the LUMA block size at this position (the call sites pass obs,
+   src/encode.c:1514-1516, src/decode.c:818-820).  4:2:0 and 4:4:4 only, as the
+   callers assert (src/encode.c:1499). */
+void oc_resample_luma_coeffs(oc_coeff *chroma_pred, int cpstride, const oc_coeff *decoded_luma,
+ int dlstride, int xdec, int ydec, int bs, int chroma_bs) {
+  int n = 4 << bs;
+  int x;
+  int y;
+  if (chroma_bs == 0 && xdec && ydec) {
+    /* four 4x4 luma transforms merged into one 4x4: their low 2x2 corners */
+    oc_tf_up_hv_lp(chroma_pred, cpstride, decoded_luma, dlstride, n, n, n);
+    for (y = 0; y < 4; y++) {
+      for (x = 0; x < 4; x++) {
+        chroma_pred[y*cpstride + x] = (OC_CFL_SCALING4[x][y]*chroma_pred[y*cpstride + x] + 64) >> 7;
+      }
+    }
+    return;
+  }
+  if (chroma_bs == 0 && xdec) {
+    oc_tf_up_h_lp(chroma_pred, cpstride, decoded_luma, dlstride, n, n);
+    return;
+  }
+  if (chroma_bs == 0 && ydec) {
+    oc_tf_up_v_lp(chroma_pred, cpstride, decoded_luma, dlstride, n, n);
+    return;
+  }
+  /* the luma transform is at least as large: its upper-left n x n coefficients */
+  for (y = 0; y < n; y++) {
+    for (x = 0; x < n; x++) chroma_pred[y*cpstride + x] = decoded_luma[y*dlstride + x];
+  }
+}
+
+/* The predictor of every 4:2:0 chroma leaf block of one frame, each written at the
+   block's own position of a half-resolution plane `l` (stride nhsb*16): what the
+   recursion of src/encode.c:1491-1517 / src/decode.c:780-821 hands od_resample_luma_coeffs,
+   leaf by leaf, with ctx->l repointed into a plane. */
+void oc_cfl_pred_plane(oc_coeff *l, const oc_coeff *d_luma, int nhsb, int nvsb,
+ const unsigned char *bsize, int bstride) {
+  int fw = nhsb*32;
+  int cw = fw >> 1;
+  int ux;
+  int uy;
+  for (uy = 0; uy < nvsb*4; uy++) {
+    for (ux = 0; ux < nhsb*4; ux++) {
+      int obs = bsize[uy*bstride + ux];
+      int bsi = obs > 1 ? obs : 1;
+      int m = 1 << (bsi - 1);
+      if ((ux & (m - 1)) || (uy & (m - 1))) continue;   /* not the block's first unit */
+      oc_resample_luma_coeffs(l + (uy*4)*cw + ux*4, cw, d_luma + (uy*8)*fw + ux*8, fw,
+       1, 1, bsi - 1, obs);
+    }
+  }
+}
+
 /* ------------------------------------------------- pixel <-> coefficient -- */
 
 /* reference src/state.c:1209-1248.  bitdepth_mode: 1/2/3 for 8/10/12 bits

@@ -34,6 +34,11 @@ class Checker:
             return self.rc.inv_plane(d, bsize, dec, dc_split, use_haar=haar, impl=1)
         return ol.port_inv_plane(d, bsize, dec, self.pic_w, self.pic_h, dc_split, use_haar=haar)
 
+    def cfl_pred_frames(self, d_luma, bsize):
+        """d_luma: (nframes, fh, fw) -> (nframes, fh/2, fw/2) chroma-from-luma predictor planes."""
+        f = ol.ref_cfl_pred_plane if self.rc else ol.port_cfl_pred_plane
+        return np.stack([f(d_luma[i], bsize[i]) for i in range(d_luma.shape[0])])
+
     def fwd_frames(self, c_planes, bsize, decs, keyframe, haar=0):
         """c_planes[p]: (nframes, h, w) -> list of d planes of the same shape."""
         out = []

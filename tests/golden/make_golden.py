@@ -189,6 +189,9 @@ def main():
             cl = np.ascontiguousarray(lcg_ints(80 + pli, H * W, -128, 128).reshape(H, W))
             G["plane_%d_cl" % pli] = cl
             G["plane_%d_d_haar" % pli] = rc.fwd_plane(cl, hb, dec, 1, use_haar=1, impl=0)[0]
+        # chroma-from-luma predictor plane of the decoded luma coefficients above
+        # (od_resample_luma_coeffs, src/intra.c:72, called per chroma leaf block)
+        G["plane_cfl"] = ol.ref_cfl_pred_plane(G["plane_0_dq"], bsize)
 
     # ---- C1: CIF keyframe, block sizes chosen by the reference encoder's RDO ------
     with ol.RefCtx(352, 288) as rc:

@@ -101,6 +101,42 @@ def port_inv_plane(d, bsize, dec, pic_w, pic_h, dc_split, use_haar=0):
     return c
 
 
+def port_cfl_pred_plane(d_luma, bsize):
+    """Chroma-from-luma predictor plane of one frame (restatement)."""
+    lib = port()
+    d_luma = np.ascontiguousarray(d_luma, dtype=np.int32)
+    H, W = d_luma.shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    l = np.zeros((H // 2, W // 2), np.int32)
+    lib.oc_cfl_pred_plane(ptr(l), ptr(d_luma), W // 32, H // 32, ptr(bsize), bsize.shape[1])
+    return l
+
+
+def ref_cfl_pred_plane(d_luma, bsize):
+    """The same plane from the REFERENCE's od_resample_luma_coeffs (src/intra.c:72), called
+    once per chroma leaf block with the arguments of its call sites (src/encode.c:1512-1517):
+    luma origin (bx << (2 + bsi), by << (2 + bsi)), xdec = ydec = 1, bs = max(obs, 1) - 1,
+    chroma_bs = obs."""
+    lib = ref()
+    d_luma = np.ascontiguousarray(d_luma, dtype=np.int32)
+    H, W = d_luma.shape
+    cw = W // 2
+    l = np.zeros((H // 2, cw), np.int32)
+    f = lib.od_resample_luma_coeffs
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    for uy in range(H // 8):
+        for ux in range(W // 8):
+            obs = int(bsize[uy, ux])
+            bsi = max(obs, 1)
+            m = 1 << (bsi - 1)
+            if (ux & (m - 1)) or (uy & (m - 1)):
+                continue
+            f(l.ctypes.data + 4 * ((uy * 4) * cw + ux * 4), cw,
+              d_luma.ctypes.data + 4 * ((uy * 8) * W + ux * 8), W, 1, 1, bsi - 1, obs)
+    return l
+
+
 # ----------------------------------------------------------------- ref API --
 class RefCtx:
     """An instance of the reference encoder state for one picture size."""

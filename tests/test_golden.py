@@ -115,6 +115,10 @@ def test_port_planes(G):
         assert np.array_equal(d, G["plane_%d_d_haar" % pli])
 
 
+def test_port_cfl_pred_plane(G):
+    assert np.array_equal(ol.port_cfl_pred_plane(G["plane_0_dq"], G["plane_bsize"]), G["plane_cfl"])
+
+
 def test_port_cif_keyframe(G):
     """BASELINE config 1: CIF keyframe with the block sizes the reference encoder's
     RDO chose; the coefficient planes are pinned by SHA-256."""
@@ -238,6 +242,9 @@ def test_cuda_planes(G):
         ctx.fwd_frames(d, cl, hb, daala_b200.OD_TDLT_KEYFRAME | daala_b200.OD_TDLT_HAAR)
         for p in range(3):
             assert np.array_equal(d[p][0], G["plane_%d_d_haar" % p])
+        l = np.zeros((1,) + G["plane_cfl"].shape, np.int32)
+        ctx.cfl_pred_frames(l, dq[0], bsize)
+        assert np.array_equal(l[0], G["plane_cfl"])
 
 
 @pytest.mark.gpu

@@ -257,3 +257,41 @@ def test_pixel_conversion_matches_reference(reflib, mode, lossless, xstride):
     port.oc_coeff_to_buf(mode, ptr(pa), xstride, ystride, ptr(co), w, lossless, w, h)
     reflib.ref_coeff_to_buf(mode, ptr(pb), xstride, ystride, ptr(co), w, lossless, w, h)
     assert np.array_equal(pa, pb)
+
+
+@pytest.mark.parametrize("chroma_bs,dec", [(0, 1), (1, 1), (2, 1), (3, 1), (0, 0), (1, 0), (2, 0), (3, 0)])
+def test_resample_luma_block_matches_reference(reflib, chroma_bs, dec):
+    """od_resample_luma_coeffs (src/intra.c:72-109), one block: the 4:2:0 branches (4x4 chroma
+    from four 4x4 luma blocks; upper-left quarter otherwise) and the 4:4:4 copy."""
+    rng = np.random.default_rng(1000 + chroma_bs * 2 + dec)
+    port = ol.port()
+    # the call sites' arguments (src/encode.c:1512-1517): chroma_bs is the LUMA block size,
+    # bs the chroma transform size
+    bs = max(chroma_bs, 1) - 1 if dec else chroma_bs
+    n = 4 << bs
+    ln = n << dec
+    f = reflib.od_resample_luma_coeffs
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    for trial in range(4):
+        luma = rng.integers(-30000, 30000, size=(ln, ln + 5)).astype(np.int32)
+        a = np.full((n, n + 3), 77, np.int32)
+        b = a.copy()
+        f(ptr(a), n + 3, ptr(luma), ln + 5, dec, dec, bs, chroma_bs)
+        port.oc_resample_luma_coeffs(ptr(b), n + 3, ptr(luma), ln + 5, dec, dec, bs, chroma_bs)
+        assert np.array_equal(a, b)
+        assert np.all(a[:, n:] == 77)
+
+
+@pytest.mark.parametrize("w,h", [(64, 64), (352, 288), (200, 136)])
+def test_cfl_pred_plane_matches_reference(reflib, w, h):
+    """Whole-frame driver of the restatement against the reference called per chroma leaf."""
+    rng = np.random.default_rng(1100 + w)
+    fw, fh = ol.padded_dims(w, h)
+    nhsb, nvsb = fw // 32, fh // 32
+    maps = [ol.random_quadtree_bsize(nhsb, nvsb, rng),
+            ol.random_quadtree_bsize(nhsb, nvsb, rng, 1.0, 0.9, 0.5)]
+    maps += [np.full((nvsb * 4, nhsb * 4), k, np.uint8) for k in range(4)]
+    for bsize in maps:
+        d = rng.integers(-30000, 30000, size=(fh, fw)).astype(np.int32)
+        assert np.array_equal(ol.port_cfl_pred_plane(d, bsize), ol.ref_cfl_pred_plane(d, bsize))
