@@ -58,6 +58,10 @@ def lib():
         L.od_tdlt_inv_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_pix_to_coeff_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_coeff_to_pix_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
+        L.od_tdlt_cfl_pred_batch.argtypes = [vp, vp, vp, vp, ci, vp]
+        L.od_tdlt_cfl_pred_frames.argtypes = [vp, vp, vp, vp, ci]
+        L.od_resample_luma_coeffs_cuda.argtypes = [vp, ci, vp, ci, ci, ci, ci, ci]
+        L.od_resample_luma_coeffs_cuda.restype = None
         L.od_tdlt_fwd_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_inv_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         iarr, larr = C.POINTER(ci), C.POINTER(ll)
@@ -154,6 +158,11 @@ class TdltContext:
         self._check(self.L.od_tdlt_inv_batch(self._h, _ptr_array(c_ptrs), _ptr_array(d_ptrs),
                                              bsize_ptr, nframes, flags, stream), "od_tdlt_inv_batch")
 
+    def cfl_pred_batch(self, l_ptr, d_luma_ptr, bsize_ptr, nframes, stream=0):
+        """Device pointers: chroma-from-luma predictor planes (od_tdlt_cfl_pred_batch)."""
+        self._check(self.L.od_tdlt_cfl_pred_batch(self._h, l_ptr, d_luma_ptr, bsize_ptr, nframes,
+                                                  stream), "od_tdlt_cfl_pred_batch")
+
     def pix_to_coeff_batch(self, c_ptr, pix_ptr, pli, nframes, xstride=1, bitdepth_mode=1,
                            lossless=0, stream=0):
         self._check(self.L.od_tdlt_pix_to_coeff_batch(self._h, c_ptr, pix_ptr, pli, nframes, xstride,
@@ -180,6 +189,12 @@ class TdltContext:
             self._h, _ptr_array([a.ctypes.data for a in c_planes]),
             _ptr_array([a.ctypes.data for a in d_planes]), bsize.ctypes.data, n, flags),
             "od_tdlt_inv_frames")
+
+    def cfl_pred_frames(self, l, d_luma, bsize):
+        """Host arrays: l (nframes, fh/2, fw/2) <- d_luma (nframes, fh, fw), bsize maps."""
+        n = bsize.shape[0]
+        self._check(self.L.od_tdlt_cfl_pred_frames(self._h, l.ctypes.data, d_luma.ctypes.data,
+                                                   bsize.ctypes.data, n), "od_tdlt_cfl_pred_frames")
 
     def _pix_args(self, pix_planes, xstride):
         ys = (C.c_int * NPLANES_MAX)()

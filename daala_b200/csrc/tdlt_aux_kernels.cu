@@ -489,4 +489,86 @@ void launch_coeff_to_pix(void *pix, const int *c, long long nsamples, int xstrid
       pix, reinterpret_cast<const int4 *>(c), n4, xstride, shift);
 }
 
+
+// ---------------------------------------------------------------------------
+// Chroma-from-luma predictor planes (reference od_resample_luma_coeffs,
+// src/intra.c:72-109, as the leaf visits of src/encode.c:1491-1517 call it for
+// 4:2:0): for every chroma leaf block the low-frequency coefficients of the luma
+// transform covering it.  One thread per 8x8 luma unit = 4x4 samples of the
+// half-resolution plane `l`:
+//   unit size 0 (four 4x4 luma transforms over one 4x4 chroma block): the 2x2 low
+//   corners of the four blocks merged by one Haar level, then the trained 4x4 scaling;
+//   otherwise: the 4x4 patch of the luma block's upper-left quarter this unit covers.
+// Memory bound: per `l` sample 4 bytes read + 4 written (+ 1/16 byte of map).
+// Threads of a warp cover 32 consecutive units of a unit row: their four 16-byte
+// stores per thread tile four full 512-byte row segments.
+// ---------------------------------------------------------------------------
+__constant__ int kCflScaling4[16] = {   // reference src/intra.c:65-70, [x][y] flattened
+    128, 128, 100, 36, 128, 80, 71, 35, 100, 71, 35, 31, 36, 35, 31, 18};
+
+__global__ void __launch_bounds__(256) cfl_pred_kernel(
+    int *__restrict__ l, int lstride, long long lframe, const int *__restrict__ d_luma,
+    int dstride, long long dframe, const unsigned char *__restrict__ bsize, int bw, int bh,
+    long long nunits) {
+  long long i = (long long)blockIdx.x*blockDim.x + threadIdx.x;
+  if (i >= nunits) return;
+  int per = bw*bh;
+  int frame = (int)(i/per);
+  int u = (int)(i - (long long)frame*per);
+  int uy = u/bw, ux = u - uy*bw;
+  int obs = __ldg(bsize + (long long)frame*per + u);
+  const int *src = d_luma + frame*dframe;
+  int *dst = l + frame*lframe + (long long)(4*uy)*lstride + 4*ux;
+  if (obs == 0) {
+    const int *s = src + (long long)(8*uy)*dstride + 8*ux;
+    int o[4][4];
+#pragma unroll
+    for (int y = 0; y < 2; y++) {
+      int2 a = *reinterpret_cast<const int2 *>(s + y*dstride);
+      int2 b = *reinterpret_cast<const int2 *>(s + y*dstride + 4);
+      int2 c = *reinterpret_cast<const int2 *>(s + (y + 4)*dstride);
+      int2 e = *reinterpret_cast<const int2 *>(s + (y + 4)*dstride + 4);
+      int ll[2] = {a.x, a.y}, lh[2] = {b.x, b.y}, hl[2] = {c.x, c.y}, hh[2] = {e.x, e.y};
+#pragma unroll
+      for (int x = 0; x < 2; x++) {
+        haar2x2(ll[x], hl[x], lh[x], hh[x]);
+        // low band at the position of its parity, as the reference's merge interleaves them
+        int hs = x, vs = y;
+        o[2*y + vs][2*x + hs] = ll[x];
+        o[2*y + vs][2*x + 1 - hs] = lh[x];
+        o[2*y + 1 - vs][2*x + hs] = hl[x];
+        o[2*y + 1 - vs][2*x + 1 - hs] = hh[x];
+      }
+    }
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      int4 v;
+      v.x = (kCflScaling4[0 + y]*o[y][0] + 64) >> 7;
+      v.y = (kCflScaling4[4 + y]*o[y][1] + 64) >> 7;
+      v.z = (kCflScaling4[8 + y]*o[y][2] + 64) >> 7;
+      v.w = (kCflScaling4[12 + y]*o[y][3] + 64) >> 7;
+      *reinterpret_cast<int4 *>(dst + (long long)y*lstride) = v;
+    }
+    return;
+  }
+  // The luma block of 2^(obs-1) x 2^(obs-1) units this unit belongs to; the chroma block
+  // has the same origin at half scale and reads the block's first rows / columns.
+  int m = (1 << (obs - 1)) - 1;
+  int bx = ux & ~m, by = uy & ~m;
+  const int *s = src + (long long)(8*by + 4*(uy - by))*dstride + 8*bx + 4*(ux - bx);
+  int4 v[4];
+#pragma unroll
+  for (int y = 0; y < 4; y++) v[y] = __ldg(reinterpret_cast<const int4 *>(s + (long long)y*dstride));
+#pragma unroll
+  for (int y = 0; y < 4; y++) *reinterpret_cast<int4 *>(dst + (long long)y*lstride) = v[y];
+}
+
+void launch_cfl_pred(int *l, int lstride, long long lframe, const int *d_luma, int dstride,
+                     long long dframe, const unsigned char *bsize, int bw, int bh, int nframes,
+                     cudaStream_t st) {
+  long long nunits = (long long)bw*bh*nframes;
+  cfl_pred_kernel<<<(unsigned)((nunits + 255)/256), 256, 0, st>>>(
+      l, lstride, lframe, d_luma, dstride, dframe, bsize, bw, bh, nunits);
+}
+
 }  // namespace tdlt

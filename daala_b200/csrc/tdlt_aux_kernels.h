@@ -23,4 +23,10 @@ void launch_tf_hv(bool down, int *dst, int dstride, const int *src, int sstride,
 void launch_tf_op(int op, int *dst, int dstride, const int *src, int sstride, int n, int p0,
                   int p1, int p2, cudaStream_t st);
 
+// Chroma-from-luma predictor planes: bw x bh 8x8 luma units per frame, planes with row
+// strides lstride / dstride (words, multiples of 4) and frame strides lframe / dframe.
+void launch_cfl_pred(int *l, int lstride, long long lframe, const int *d_luma, int dstride,
+                     long long dframe, const unsigned char *bsize, int bw, int bh, int nframes,
+                     cudaStream_t st);
+
 }  // namespace tdlt

@@ -484,6 +484,25 @@ int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c, i
   return OD_TDLT_SUCCESS;
 }
 
+// Chroma-from-luma predictor planes (reference src/intra.c:72-109 over the leaf visits of
+// src/encode.c:1491-1517 / src/decode.c:780-821): l is a plane of the size of plane 1.
+int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
+                           const unsigned char *bsize, int nframes, void *stream) {
+  if (!ctx || !l || !d_luma || !bsize) return OD_TDLT_EFAULT;
+  if (ctx->g.nplanes < 2 || ctx->g.xdec[0] || ctx->g.ydec[0] || ctx->g.xdec[1] != 1 ||
+      ctx->g.ydec[1] != 1) {
+    return fail(ctx, OD_TDLT_EINVAL, "chroma-from-luma planes need 4:2:0 (plane 0 full size, "
+                "plane 1 halved both ways); with 4:4:4 the predictor is the luma plane itself");
+  }
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_cfl_pred(l, ctx->fw >> 1, ctx->plane_size[1], d_luma, ctx->fw, ctx->plane_size[0], bsize,
+                  ctx->nhsb*4, ctx->nvsb*4, nframes, (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------- whole-frame host calls --
@@ -631,6 +650,28 @@ int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *co
   j.inverse = true;
   j.coef_out = c; j.coef_in = d; j.bsize = bsize; j.nframes = nframes; j.flags = flags;
   return run_frames(ctx, j);
+}
+
+int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
+                            const unsigned char *bsize, int nframes) {
+  if (!ctx || !l || !d_luma || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  if (ctx->g.nplanes < 2) return fail(ctx, OD_TDLT_EINVAL, "no chroma plane");
+  CK(ctx, cudaSetDevice(ctx->device));
+  // staging: the luma coefficient plane and the predictor plane in the slots the
+  // transform calls use for them (plane 0 coefficients, plane 1 samples)
+  cudaStream_t st = ctx->stream;
+  CK(ctx, cudaMemcpyAsync(ctx->dev_d[0], d_luma, (size_t)ctx->plane_size[0]*nframes*sizeof(od_coeff),
+                          cudaMemcpyHostToDevice, st));
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, (size_t)od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_cfl_pred_batch(ctx, ctx->dev_c[1], ctx->dev_d[0], ctx->dev_bsize, nframes, st);
+  if (rc) return rc;
+  CK(ctx, cudaMemcpyAsync(l, ctx->dev_c[1], (size_t)ctx->plane_size[1]*nframes*sizeof(od_coeff),
+                          cudaMemcpyDeviceToHost, st));
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
 }
 
 int od_tdlt_fwd_frames_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
@@ -805,6 +846,30 @@ void od_tf_up_v_lp_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int 
 void od_tf_up_hv_lp_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int dx, int dy,
                          int n) {
   tf_op(2, dst, ds, src, ss, n, (n >> 1) + dx, (n >> 1) + dy, dx, dy, 0);
+}
+// reference src/intra.c:72-109, one block.  The block goes through the frame kernel as a
+// frame of its own: n/4 x n/4 units whose map entries make the kernel take the same branch.
+void od_resample_luma_coeffs_cuda(od_coeff *chroma_pred, int cpstride, const od_coeff *decoded_luma,
+                                  int dlstride, int xdec, int ydec, int bs, int chroma_bs) {
+  if (xdec != ydec || bs < 0 || bs > 3) {
+    die("od_resample_luma_coeffs: 4:2:0 / 4:4:4 and bs 0..3 only (the reference's callers "
+        "assert the same, src/encode.c:1499)", cudaErrorInvalidValue);
+  }
+  int n = 4 << bs;
+  bool merge = chroma_bs == 0 && xdec;
+  if (merge && bs != 0) die("od_resample_luma_coeffs: merged block larger than 4x4", cudaErrorInvalidValue);
+  int units = merge ? 1 : n >> 2;
+  int ln = merge ? 8 : n;                     // luma samples read per row / column
+  int *din = g_scratch.A((size_t)ln*ln + 16), *dout = g_scratch.B((size_t)n*n);
+  unsigned char map[64];
+  memset(map, merge ? 0 : bs + 1, sizeof(map));
+  unsigned char *dmap = reinterpret_cast<unsigned char *>(din + (size_t)ln*ln);
+  h2d_rect(din, decoded_luma, dlstride, ln, ln);
+  CKF(cudaMemcpy(dmap, map, (size_t)units*units, cudaMemcpyHostToDevice));
+  launch_cfl_pred(dout, n, 0, din, ln, 0, dmap, units, units, 1, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(chroma_pred, cpstride, dout, n, n);
 }
 void od_tf_filter_2d_cuda(od_coeff *dst, int ds, const od_coeff *src, int ss, int n) {
   tf_op(3, dst, ds, src, ss, n, n, n, 0, 0, 0);

@@ -115,6 +115,15 @@ int od_tdlt_pix_to_coeff_batch(od_tdlt_ctx *ctx, od_coeff *c, const void *pix,
 int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c,
  int pli, int nframes, int xstride, int bitdepth_mode, int lossless_p, void *stream);
 
+/* Chroma-from-luma predictor planes for 4:2:0 (reference od_resample_luma_coeffs,
+   src/intra.c:72-109, as called for every chroma leaf block at src/encode.c:1512-1517 and
+   src/decode.c:816-821).  d_luma: the decoded luma coefficient planes (plane 0 layout);
+   l: planes of the size of plane 1, every chroma leaf block's predictor at the block's own
+   position (the reference's ctx->l, one block at a time, laid out as a plane).  DEVICE
+   pointers, asynchronous on `stream`; nframes is not limited by max_frames. */
+int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
+ const unsigned char *bsize, int nframes, void *stream);
+
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
    out as above but in host memory (pinned or pageable).
@@ -124,6 +133,9 @@ int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *co
  const unsigned char *bsize, int nframes, int flags);
 int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
  const unsigned char *bsize, int nframes, int flags);
+/* Host-pointer form of od_tdlt_cfl_pred_batch (synchronous, nframes <= max_frames). */
+int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
+ const unsigned char *bsize, int nframes);
 /* Same with the pixel conversion done on the device: the host ships 8/16-bit
    reference-buffer samples instead of od_coeff (od_ref_plane_to_coeff,
    src/state.c:1252; od_coeff_to_ref_plane, :1320).  pix[pli] points at the
@@ -178,6 +190,10 @@ void od_tf_up_v_lp_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sst
  int n);
 void od_tf_up_hv_lp_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int dx,
  int dy, int n);
+/* reference src/intra.h / src/intra.c:72-109, one block (host pointers, synchronous; the
+   4:2:0 and 4:4:4 branches: xdec == ydec) */
+void od_resample_luma_coeffs_cuda(od_coeff *chroma_pred, int cpstride,
+ const od_coeff *decoded_luma, int dlstride, int xdec, int ydec, int bs, int chroma_bs);
 /* reference src/tf.h:60-66, src/tf.c:171-277 */
 void od_tf_filter_2d_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride, int n);
 void od_tf_filter_inv_2d_cuda(od_coeff *dst, int dstride, const od_coeff *src, int sstride,

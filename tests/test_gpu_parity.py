@@ -282,6 +282,54 @@ def test_split_and_sb_edge_filters():
         assert np.array_equal(a, b)
 
 
+CFL_CASES = [(352, 288, "quad"), (352, 288, "deep"), (200, 136, "quad"), (33, 17, "deep"),
+             (64, 64, "uniform0"), (352, 288, "uniform1"), (352, 288, "uniform2"),
+             (352, 288, "uniform3"), (1920, 1080, "quad")]
+
+
+@pytest.mark.parametrize("pic_w,pic_h,kind", CFL_CASES)
+def test_cfl_predictor_planes_match_checker(pic_w, pic_h, kind):
+    """Chroma-from-luma predictor planes (od_resample_luma_coeffs over every chroma leaf
+    block) against the reference called leaf by leaf."""
+    rng = np.random.default_rng(pic_w + 5 * pic_h + sum(map(ord, kind)))
+    nframes = 3 if pic_w < 1000 else 1
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+        d_luma = rng.integers(-30000, 30000, size=(nframes, chk.fh, chk.fw)).astype(np.int32)
+        l = np.full((nframes, chk.fh // 2, chk.fw // 2), 12345, np.int32)
+        ctx.cfl_pred_frames(l, d_luma, bsize)
+        assert np.array_equal(l, chk.cfl_pred_frames(d_luma, bsize))
+    chk.close()
+
+
+def test_cfl_predictor_needs_420():
+    import daala_b200
+    with _ctx(64, 64, 1, decs=(0, 0, 0)) as ctx:
+        l = np.zeros((1, 64, 64), np.int32)
+        with pytest.raises(daala_b200.TdltError):
+            ctx.cfl_pred_frames(l, l.copy(), np.zeros((1, 8, 8), np.uint8))
+
+
+@pytest.mark.parametrize("obs,dec", [(0, 1), (1, 1), (2, 1), (3, 1), (0, 0), (1, 0), (2, 0), (3, 0)])
+def test_resample_luma_block(obs, dec):
+    """od_resample_luma_coeffs with the reference's signature, one block, the arguments of
+    its call sites: the 4:2:0 merge, the 4:2:0 upper-left quarter and the 4:4:4 copy."""
+    import daala_b200
+    L, port = daala_b200.lib(), ol.port()
+    rng = np.random.default_rng(1300 + 2 * obs + dec)
+    bs = max(obs, 1) - 1 if dec else obs
+    n = 4 << bs
+    ln = n << dec
+    for trial in range(3):
+        luma = rng.integers(-30000, 30000, size=(ln, ln + 7)).astype(np.int32)
+        a = np.full((n, n + 5), 99, np.int32)
+        b = a.copy()
+        L.od_resample_luma_coeffs_cuda(a.ctypes.data, n + 5, luma.ctypes.data, ln + 7, dec, dec, bs, obs)
+        port.oc_resample_luma_coeffs(ol.ptr(b), n + 5, ol.ptr(luma), ln + 7, dec, dec, bs, obs)
+        assert np.array_equal(a, b)
+
+
 def test_full_size_properties():
     """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
     size, where the CPU checker is too slow to be run on every frame: (1) the round
