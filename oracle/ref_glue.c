@@ -291,3 +291,42 @@ int ref_encode_keyframe_bsize(void *h, const unsigned char *y,
   }
   return 0;
 }
+
+/* ---- deringing (src/filter.c:1835, the step after the post-filter) ---------------- */
+
+/* od_dering as the decoder calls it (src/decode.c:1104-1110), on caller-provided planes.
+   impl: 0 = the C filters, 1 = whatever the runtime dispatch installed (SSE2 twins). */
+void ref_dering(void *h, int16_t *y, int ystride, int16_t *x, int xstride, int ln, int sbx,
+ int sby, int nhsb, int nvsb, int q, int xdec, int *dir, int pli, unsigned char *bskip,
+ int skip_stride, int impl) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *state = &r->enc->state;
+  if (impl == 0) {
+    state->opt_vtbl.filter_dering_direction[0] = od_filter_dering_direction_4x4_c;
+    state->opt_vtbl.filter_dering_direction[1] = od_filter_dering_direction_8x8_c;
+    state->opt_vtbl.filter_dering_orthogonal[0] = od_filter_dering_orthogonal_4x4_c;
+    state->opt_vtbl.filter_dering_orthogonal[1] = od_filter_dering_orthogonal_8x8_c;
+  }
+  else {
+#if defined(OD_X86ASM)
+    od_state_opt_vtbl_init_x86(state);
+#endif
+  }
+  od_dering(state, y, ystride, x, xstride, ln, sbx, sby, nhsb, nvsb, q, xdec,
+   (int (*)[OD_DERING_NBLOCKS])dir, pli, bskip, skip_stride);
+}
+
+/* The two filters through the dispatch table, one block: bsi 0 = 4x4, 1 = 8x8; `in` has the
+   reference's row pitch OD_FILT_BSTRIDE. */
+void ref_dering_direction(void *h, int bsi, int16_t *y, int ystride, int16_t *in, int threshold,
+ int dir) {
+  ref_ctx *r = (ref_ctx *)h;
+  (*r->enc->state.opt_vtbl.filter_dering_direction[bsi])(y, ystride, in, threshold, dir);
+}
+
+void ref_dering_orthogonal(void *h, int bsi, int16_t *y, int ystride, int16_t *in, int16_t *x,
+ int xstride, int threshold, int dir) {
+  ref_ctx *r = (ref_ctx *)h;
+  (*r->enc->state.opt_vtbl.filter_dering_orthogonal[bsi])(y, ystride, in, x, xstride, threshold,
+   dir);
+}

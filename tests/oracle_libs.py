@@ -137,6 +137,87 @@ def ref_cfl_pred_plane(d_luma, bsize):
     return l
 
 
+def dering_args(planes, decs, bskip):
+    """ctypes arrays for the frame-level deringing calls."""
+    n = len(planes)
+    pa = (C.c_void_p * 4)(*[p.ctypes.data for p in planes])
+    da = (C.c_int * 4)(*decs)
+    ba = (C.c_void_p * 4)(*[b.ctypes.data for b in bskip])
+    return n, pa, da, ba
+
+
+def port_dering_frame(planes, decs, flags, bskip, q):
+    """planes[p]: (H >> dec, W >> dec) int32 reconstructions; flags: (nvsb, nhsb) uint8, one per
+    32x32 luma superblock; bskip[p]: (nvsb*8, nhsb*8) uint8 skip flags of plane p (one per 4x4
+    samples; chroma planes use the upper-left quarter); q[p]: quantizers.  Returns filtered planes."""
+    lib = port()
+    planes = [np.ascontiguousarray(p, dtype=np.int32) for p in planes]
+    out = [np.zeros_like(p) for p in planes]
+    H, W = planes[0].shape
+    nhsb, nvsb = W // 32, H // 32
+    flags = np.ascontiguousarray(flags, dtype=np.uint8)
+    bskip = [np.ascontiguousarray(b, dtype=np.uint8) for b in bskip]
+    n, pa, da, ba = dering_args(planes, decs, bskip)
+    oa = (C.c_void_p * 4)(*[o.ctypes.data for o in out])
+    qa = (C.c_int * 4)(*q)
+    lib.oc_dering_frame(oa, pa, n, da, nhsb, nvsb, ptr(flags), ba, bskip[0].shape[1], qa)
+    return out
+
+
+def ref_dering_frame(rc, planes, decs, flags, bskip, q, impl=1):
+    """The same frame through the REFERENCE's od_dering, one superblock and plane at a time, in
+    the decoder's loop order (src/decode.c:1055-1122): etmp = int16 copy, output into ctmp."""
+    lib = rc.lib
+    planes = [np.ascontiguousarray(p, dtype=np.int32) for p in planes]
+    e = [p.astype(np.int16) for p in planes]
+    out = [p.copy() for p in planes]
+    H, W = planes[0].shape
+    nhsb, nvsb = W // 32, H // 32
+    bskip = [np.ascontiguousarray(b, dtype=np.uint8) for b in bskip]
+    ss = bskip[0].shape[1]
+    for sby in range(nvsb):
+        for sbx in range(nhsb):
+            if not flags[sby, sbx]:
+                continue
+            dirs = np.zeros((4, 4), np.int32)
+            for p, dec in enumerate(decs):
+                ln = 5 - dec
+                n = 1 << ln
+                w = W >> dec
+                buf = np.zeros((n, n), np.int16)
+                lib.ref_dering(C.c_void_p(rc.h), ptr(buf), n,
+                               C.c_void_p(e[p].ctypes.data + 2 * ((sby << ln) * w + (sbx << ln))), w, ln,
+                               sbx, sby, nhsb, nvsb, int(q[p]), dec, ptr(dirs), p,
+                               C.c_void_p(bskip[p].ctypes.data + (sby << (3 - dec)) * ss + (sbx << (3 - dec))),
+                               ss, impl)
+                out[p][sby << ln:(sby + 1) << ln, sbx << ln:(sbx + 1) << ln] = buf
+    return out
+
+
+def dering_test_frame(rng, nhsb, nvsb, decs=(0, 1, 1), skip_prob=0.5, flag_prob=0.7):
+    """A frame that exercises the filter: oriented edges (so that the direction search has
+    something to find) plus noise, skip flags in patches, superblock decisions."""
+    H, W = nvsb * 32, nhsb * 32
+    yy, xx = np.mgrid[0:H, 0:W]
+    ang = rng.uniform(0, np.pi, size=(nvsb, nhsb)).repeat(32, 0).repeat(32, 1)
+    per = rng.uniform(6, 40)
+    luma = 900 * np.sign(np.sin((xx * np.cos(ang) + yy * np.sin(ang)) * 2 * np.pi / per))
+    luma = luma + rng.normal(0, 120, size=(H, W))
+    planes = [np.clip(luma, -2040, 2040).astype(np.int32) * 16 // 16 * 8]
+    for dec in decs[1:]:
+        c = planes[0][::1 << dec, ::1 << dec] // 2 + rng.integers(-300, 300, size=(H >> dec, W >> dec))
+        planes.append(np.ascontiguousarray(c).astype(np.int32))
+    flags = (rng.random((nvsb, nhsb)) < flag_prob).astype(np.uint8)
+    bskip = []
+    for dec in decs:
+        coarse = rng.random((nvsb * 2, nhsb * 2)) < skip_prob
+        b = np.zeros((nvsb * 8, nhsb * 8), np.uint8)
+        fine = coarse.repeat(4 >> dec, 0).repeat(4 >> dec, 1) & (rng.random((nvsb * 8 >> dec, nhsb * 8 >> dec)) < 0.9)
+        b[:nvsb * 8 >> dec, :nhsb * 8 >> dec] = fine
+        bskip.append(b)
+    return planes, flags, bskip
+
+
 # ----------------------------------------------------------------- ref API --
 class RefCtx:
     """An instance of the reference encoder state for one picture size."""

@@ -295,3 +295,76 @@ def test_cfl_pred_plane_matches_reference(reflib, w, h):
     for bsize in maps:
         d = rng.integers(-30000, 30000, size=(fh, fw)).astype(np.int32)
         assert np.array_equal(ol.port_cfl_pred_plane(d, bsize), ol.ref_cfl_pred_plane(d, bsize))
+
+
+# ---- deringing ----------------------------------------------------
+def test_dering_threshold_table_follows_its_formula():
+    port = ol.port()
+    tab = (C.c_int16 * 18).in_dll(port, "OC_DERING_THRESH_Q8")
+    want = [round(256 * min(3, max(.5, 1.08 * (np.sqrt(2) * 2.0 ** (i + 8) / 65536) ** .16))) for i in range(18)]
+    assert list(tab) == want
+
+
+@pytest.mark.parametrize("bsi", [0, 1])
+def test_dering_filters_match_reference(reflib, bsi):
+    """The direction and orthogonal filters, one block, all 8 directions, against the reference's
+    C functions and whatever its runtime dispatch installs (the SSE2 twins)."""
+    rng = np.random.default_rng(1400 + bsi)
+    port = ol.port()
+    n = 4 << bsi
+    P = 38
+    cfun = [(reflib.od_filter_dering_direction_4x4_c, reflib.od_filter_dering_orthogonal_4x4_c),
+            (reflib.od_filter_dering_direction_8x8_c, reflib.od_filter_dering_orthogonal_8x8_c)][bsi]
+    with ol.RefCtx(64, 64) as rc:
+        for trial in range(40):
+            d = trial % 8
+            thr = int(rng.choice([0, 1, 7, 40, 300, 2000]))   # 14*thr fits 16 bits (SSE2 sums)
+            # 8-bit video range (|x| <= 2048 + filter overshoot): the SSE2 twins work in 16 bits, so
+            # 30000 - x must not wrap
+            buf = rng.integers(-400, 400, size=(n + 6, P)).astype(np.int16) * int(rng.choice([1, 3, 6]))
+            if trial % 5 == 0:
+                buf[:, :4] = 30000       # outside the frame
+            org = rng.integers(-3000, 3000, size=(n, n + 2)).astype(np.int16)
+            inp = buf.ctypes.data + 2 * (3 * P + 3)
+            outs = []
+            for who in ("c", "dispatch", "port"):
+                y1 = np.zeros((n, n + 1), np.int16)
+                y2 = np.zeros((n, n + 1), np.int16)
+                if who == "c":
+                    cfun[0](ptr(y1), n + 1, C.c_void_p(inp), thr, d)
+                    cfun[1](ptr(y2), n + 1, C.c_void_p(inp), ptr(org), n + 2, thr, d)
+                elif who == "dispatch":
+                    reflib.ref_dering_direction(C.c_void_p(rc.h), bsi, ptr(y1), n + 1, C.c_void_p(inp), thr, d)
+                    reflib.ref_dering_orthogonal(C.c_void_p(rc.h), bsi, ptr(y2), n + 1, C.c_void_p(inp),
+                                                 ptr(org), n + 2, thr, d)
+                else:
+                    port.oc_dering_direction(ptr(y1), n + 1, C.c_void_p(inp), 2 + bsi, thr, d)
+                    port.oc_dering_orthogonal(ptr(y2), n + 1, C.c_void_p(inp), ptr(org), n + 2, 2 + bsi, thr, d)
+                outs.append((y1, y2))
+            for y1, y2 in outs[1:]:
+                assert np.array_equal(y1, outs[0][0]) and np.array_equal(y2, outs[0][1])
+
+
+@pytest.mark.parametrize("nhsb,nvsb,q", [(3, 3, 60), (1, 1, 200), (4, 2, 9), (2, 5, 1000), (1, 3, 33)])
+def test_dering_frame_matches_reference(reflib, nhsb, nvsb, q):
+    """Whole frames: every superblock position (corners, edges, interior), random skip maps and
+    decisions, luma directions reused by chroma; the restatement's frame loop against od_dering
+    called the way the decoder calls it, C filters and dispatched filters."""
+    rng = np.random.default_rng(1500 + nhsb * 10 + nvsb)
+    decs = (0, 1, 1)
+    qs = (q, max(1, q * 3 // 4), max(1, q // 2))
+    with ol.RefCtx(64, 64) as rc:
+        for trial in range(3):
+            planes, flags, bskip = ol.dering_test_frame(rng, nhsb, nvsb, decs, skip_prob=(0.2, 0.6, 0.95)[trial])
+            if trial == 2:
+                planes = [rng.integers(-2600, 2600, size=p.shape).astype(np.int32) for p in planes]
+            a = ol.ref_dering_frame(rc, planes, decs, flags, bskip, qs, impl=0)
+            b = ol.ref_dering_frame(rc, planes, decs, flags, bskip, qs, impl=1)
+            c = ol.port_dering_frame(planes, decs, flags, bskip, qs)
+            changed = 0
+            for p in range(3):
+                assert np.array_equal(a[p], b[p]), "reference C vs SIMD, plane %d" % p
+                assert np.array_equal(a[p], c[p]), "restatement, plane %d" % p
+                changed += int(np.count_nonzero(a[p] != planes[p]))
+            if trial == 0 and flags.any():
+                assert changed > 0          # the test frame does exercise the filter

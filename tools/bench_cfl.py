@@ -28,11 +28,13 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--maps", default="", help="override the map kind (quad, uniform0..3)")
     args = ap.parse_args()
     import torch
     import daala_b200
     pic_w, pic_h, nframes, kind = bench.WORKLOADS[args.workload]
     nframes = args.frames or nframes
+    kind = args.maps or kind
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     ctx = daala_b200.TdltContext(pic_w, pic_h, decs=bench.DECS, device=0, max_frames=0)
