@@ -62,6 +62,8 @@ def lib():
         L.od_tdlt_cfl_pred_frames.argtypes = [vp, vp, vp, vp, ci]
         L.od_resample_luma_coeffs_cuda.argtypes = [vp, ci, vp, ci, ci, ci, ci, ci]
         L.od_resample_luma_coeffs_cuda.restype = None
+        L.od_tdlt_dering_batch.argtypes = [vp, arr, arr, vp, arr, C.POINTER(ci), ci, vp]
+        L.od_tdlt_dering_frames.argtypes = [vp, arr, arr, vp, arr, C.POINTER(ci), ci]
         L.od_tdlt_fwd_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_inv_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         iarr, larr = C.POINTER(ci), C.POINTER(ll)
@@ -163,6 +165,13 @@ class TdltContext:
         self._check(self.L.od_tdlt_cfl_pred_batch(self._h, l_ptr, d_luma_ptr, bsize_ptr, nframes,
                                                   stream), "od_tdlt_cfl_pred_batch")
 
+    def dering_batch(self, out_ptrs, in_ptrs, flags_ptr, bskip_ptrs, q, nframes, stream=0):
+        """Device pointers: deringing of the reconstructed planes (od_tdlt_dering_batch)."""
+        qa = (C.c_int * NPLANES_MAX)(*q)
+        self._check(self.L.od_tdlt_dering_batch(self._h, _ptr_array(out_ptrs), _ptr_array(in_ptrs),
+                                                flags_ptr, _ptr_array(bskip_ptrs), qa, nframes, stream),
+                    "od_tdlt_dering_batch")
+
     def pix_to_coeff_batch(self, c_ptr, pix_ptr, pli, nframes, xstride=1, bitdepth_mode=1,
                            lossless=0, stream=0):
         self._check(self.L.od_tdlt_pix_to_coeff_batch(self._h, c_ptr, pix_ptr, pli, nframes, xstride,
@@ -195,6 +204,15 @@ class TdltContext:
         n = bsize.shape[0]
         self._check(self.L.od_tdlt_cfl_pred_frames(self._h, l.ctypes.data, d_luma.ctypes.data,
                                                    bsize.ctypes.data, n), "od_tdlt_cfl_pred_frames")
+
+    def dering_frames(self, out_planes, in_planes, flags, bskip, q):
+        """Host arrays: planes (nframes, h, w) int32; flags (nframes, nvsb, nhsb) uint8; bskip[p]
+        (nframes, nvsb*8, nhsb*8) uint8; q: one quantizer per plane."""
+        qa = (C.c_int * NPLANES_MAX)(*q)
+        self._check(self.L.od_tdlt_dering_frames(
+            self._h, _ptr_array([a.ctypes.data for a in out_planes]),
+            _ptr_array([a.ctypes.data for a in in_planes]), flags.ctypes.data,
+            _ptr_array([a.ctypes.data for a in bskip]), qa, flags.shape[0]), "od_tdlt_dering_frames")
 
     def _pix_args(self, pix_planes, xstride):
         ys = (C.c_int * NPLANES_MAX)()

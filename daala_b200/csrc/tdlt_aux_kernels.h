@@ -29,4 +29,18 @@ void launch_cfl_pred(int *l, int lstride, long long lframe, const int *d_luma, i
                      long long dframe, const unsigned char *bsize, int bw, int bh, int nframes,
                      cudaStream_t st);
 
+// Deringing (tdlt_dering.cu): one CTA per 32x32 luma superblock and frame, all planes.
+struct DeringParams {
+  const int *in[4];
+  int *out[4];
+  const unsigned char *bskip[4];   // per plane: one flag per 4x4 samples, row stride skip_stride
+  const unsigned char *flags;      // one per superblock, nhsb*nvsb per frame
+  long long plane_size[4];
+  long long skip_frame;            // bytes per frame of every bskip plane
+  int dec[4];
+  int thr[4];                      // (int)pow(q, 0.84182) per plane, computed on the host
+  int nplanes, nhsb, nvsb, skip_stride;
+};
+void launch_dering(const DeringParams &P, int nframes, cudaStream_t st);
+
 }  // namespace tdlt

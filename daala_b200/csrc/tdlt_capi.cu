@@ -3,6 +3,7 @@
 // No CPU arithmetic path exists here: every entry point launches CUDA kernels
 // or fails.
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -47,6 +48,8 @@ struct od_tdlt_ctx {
   od_coeff *dev_d[kMaxPlanes];
   void *dev_pix[kMaxPlanes];
   unsigned char *dev_bsize;
+  unsigned char *dev_aux;       // od_tdlt_dering_frames: superblock flags + skip maps
+  size_t dev_aux_bytes;
   cudaStream_t stream;          // kernels
   cudaStream_t s_in, s_out;     // uploads / downloads of the host-pointer calls
   cudaEvent_t ev_in[kMaxChunks], ev_run[kMaxChunks];
@@ -292,6 +295,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
     cudaFree(ctx->dev_pix[p]);
   }
   cudaFree(ctx->dev_bsize);
+  cudaFree(ctx->dev_aux);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
   cudaFree(ctx->order);
@@ -509,6 +513,44 @@ int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma
   return OD_TDLT_SUCCESS;
 }
 
+// Deringing of the reconstructed planes (reference od_dering, src/filter.c:1835-1941, over
+// the superblock loop of src/decode.c:1044-1122): out = in, superblocks whose flag is set
+// filtered.  The thresholds follow the reference's double-precision expression, evaluated
+// on the host exactly as the reference does (src/filter.c:1877).
+int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
+                         const unsigned char *flags, const unsigned char *const bskip[],
+                         const int q[], int nframes, void *stream) {
+  if (!ctx || !out || !in || !flags || !bskip || !q) return OD_TDLT_EFAULT;
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
+  DeringParams P = {};
+  P.nplanes = ctx->g.nplanes;
+  for (int p = 0; p < P.nplanes; p++) {
+    if (!out[p] || !in[p] || !bskip[p]) return OD_TDLT_EFAULT;
+    if (out[p] == in[p]) return fail(ctx, OD_TDLT_EINVAL, "deringing is out of place (plane %d)", p);
+    if (ctx->g.xdec[p] != ctx->g.ydec[p] || ctx->g.xdec[p] > 1 || (p == 0 && ctx->g.xdec[p])) {
+      return fail(ctx, OD_TDLT_EINVAL, "deringing needs 4:4:4 or 4:2:0 planes (the reference "
+                  "asserts xdec == ydec, src/decode.c:1099)");
+    }
+    if (q[p] < 0) return fail(ctx, OD_TDLT_EINVAL, "quantizer %d", q[p]);
+    P.in[p] = in[p];
+    P.out[p] = out[p];
+    P.bskip[p] = bskip[p];
+    P.plane_size[p] = ctx->plane_size[p];
+    P.dec[p] = ctx->g.xdec[p];
+    P.thr[p] = (int)(1.0*pow((double)q[p], 0.84182));
+  }
+  P.flags = flags;
+  P.nhsb = ctx->nhsb;
+  P.nvsb = ctx->nvsb;
+  P.skip_stride = ctx->nhsb*8;
+  P.skip_frame = (long long)ctx->nhsb*8*ctx->nvsb*8;
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_dering(P, nframes, (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------- whole-frame host calls --
@@ -676,6 +718,45 @@ int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_lum
   if (rc) return rc;
   CK(ctx, cudaMemcpyAsync(l, ctx->dev_c[1], (size_t)ctx->plane_size[1]*nframes*sizeof(od_coeff),
                           cudaMemcpyDeviceToHost, st));
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
+                          const unsigned char *flags, const unsigned char *const bskip[],
+                          const int q[], int nframes) {
+  if (!ctx || !out || !in || !flags || !bskip || !q) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  const int np = ctx->g.nplanes;
+  const size_t nsb = (size_t)ctx->nhsb*ctx->nvsb*nframes;
+  const size_t skip = (size_t)ctx->nhsb*8*ctx->nvsb*8*nframes;
+  const size_t want = nsb + skip*np;
+  if (want > ctx->dev_aux_bytes) {
+    cudaFree(ctx->dev_aux);
+    ctx->dev_aux = nullptr;
+    ctx->dev_aux_bytes = 0;
+    CK(ctx, cudaMalloc(&ctx->dev_aux, want));
+    ctx->dev_aux_bytes = want;
+  }
+  cudaStream_t st = ctx->stream;
+  const unsigned char *dskip[kMaxPlanes];
+  CK(ctx, cudaMemcpyAsync(ctx->dev_aux, flags, nsb, cudaMemcpyHostToDevice, st));
+  for (int p = 0; p < np; p++) {
+    if (!out[p] || !in[p] || !bskip[p]) return OD_TDLT_EFAULT;
+    unsigned char *ds = ctx->dev_aux + nsb + skip*p;
+    dskip[p] = ds;
+    CK(ctx, cudaMemcpyAsync(ds, bskip[p], skip, cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemcpyAsync(ctx->dev_c[p], in[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyHostToDevice, st));
+  }
+  rc = od_tdlt_dering_batch(ctx, ctx->dev_d, ctx->dev_c, ctx->dev_aux, dskip, q, nframes, st);
+  if (rc) return rc;
+  for (int p = 0; p < np; p++) {
+    CK(ctx, cudaMemcpyAsync(out[p], ctx->dev_d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
   CK(ctx, cudaStreamSynchronize(st));
   return OD_TDLT_SUCCESS;
 }

@@ -124,6 +124,24 @@ int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c,
 int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
  const unsigned char *bsize, int nframes, void *stream);
 
+/* Deringing of the reconstructed planes, the step after the inverse stage (reference
+   od_dering, src/filter.c:1835-1941, called per 32x32 luma superblock and plane by the loops
+   at src/decode.c:1055-1122 and src/encode.c; includes od_dir_find8, od_compute_thresh and
+   the od_filter_dering_direction / _orthogonal 4x4 and 8x8 filters of the dispatch table).
+   out[p] = in[p] with every superblock whose flag is set filtered; out != in (the reference
+   filters from its unfiltered int16_t copy etmp into ctmp; `in` plays etmp, `out` ctmp, and
+   samples are taken as int16_t exactly as that copy does).
+     flags: nframes x nvsb x nhsb bytes, state->dering_flags after the decision
+            (src/decode.c:1093);
+     bskip[p]: per plane nframes x (nvsb*8) x (nhsb*8) bytes, one skip flag per 4x4 samples of
+            plane p, row stride nhsb*8 for every plane (state->bskip[p], skip_stride,
+            src/state.c:450-463; 4:2:0 chroma uses the upper-left quarter);
+     q[p]:  the plane quantizers (state->quantizer[p]) of this batch, HOST array.
+   4:4:4 or 4:2:0.  DEVICE pointers in out/in/flags/bskip, asynchronous on `stream`. */
+int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
+ const unsigned char *flags, const unsigned char *const bskip[], const int q[], int nframes,
+ void *stream);
+
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
    out as above but in host memory (pinned or pageable).
@@ -136,6 +154,9 @@ int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *co
 /* Host-pointer form of od_tdlt_cfl_pred_batch (synchronous, nframes <= max_frames). */
 int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma,
  const unsigned char *bsize, int nframes);
+/* Host-pointer form of od_tdlt_dering_batch (synchronous, nframes <= max_frames). */
+int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
+ const unsigned char *flags, const unsigned char *const bskip[], const int q[], int nframes);
 /* Same with the pixel conversion done on the device: the host ships 8/16-bit
    reference-buffer samples instead of od_coeff (od_ref_plane_to_coeff,
    src/state.c:1252; od_coeff_to_ref_plane, :1320).  pix[pli] points at the

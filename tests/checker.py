@@ -39,6 +39,17 @@ class Checker:
         f = ol.ref_cfl_pred_plane if self.rc else ol.port_cfl_pred_plane
         return np.stack([f(d_luma[i], bsize[i]) for i in range(d_luma.shape[0])])
 
+    def dering_frames(self, planes, decs, flags, bskip, q):
+        """planes[p]: (nframes, h, w); flags (nframes, nvsb, nhsb); bskip[p] (nframes, nvsb*8,
+        nhsb*8).  The reference's od_dering superblock by superblock when it is available."""
+        out = [np.empty_like(p) for p in planes]
+        for f in range(flags.shape[0]):
+            args = ([p[f] for p in planes], decs, flags[f], [b[f] for b in bskip], q)
+            res = ol.ref_dering_frame(self.rc, *args) if self.rc else ol.port_dering_frame(*args)
+            for p in range(len(planes)):
+                out[p][f] = res[p]
+        return out
+
     def fwd_frames(self, c_planes, bsize, decs, keyframe, haar=0):
         """c_planes[p]: (nframes, h, w) -> list of d planes of the same shape."""
         out = []

@@ -202,8 +202,8 @@ def dering_test_frame(rng, nhsb, nvsb, decs=(0, 1, 1), skip_prob=0.5, flag_prob=
     ang = rng.uniform(0, np.pi, size=(nvsb, nhsb)).repeat(32, 0).repeat(32, 1)
     per = rng.uniform(6, 40)
     luma = 900 * np.sign(np.sin((xx * np.cos(ang) + yy * np.sin(ang)) * 2 * np.pi / per))
-    luma = luma + rng.normal(0, 120, size=(H, W))
-    planes = [np.clip(luma, -2040, 2040).astype(np.int32) * 16 // 16 * 8]
+    luma = luma + rng.normal(0, 40, size=(H, W))
+    planes = [np.clip(luma, -2040, 2040).astype(np.int32)]      # 8-bit video in od_coeff scale
     for dec in decs[1:]:
         c = planes[0][::1 << dec, ::1 << dec] // 2 + rng.integers(-300, 300, size=(H >> dec, W >> dec))
         planes.append(np.ascontiguousarray(c).astype(np.int32))

@@ -330,6 +330,55 @@ def test_resample_luma_block(obs, dec):
         assert np.array_equal(a, b)
 
 
+def _dering_batch(rng, nframes, nhsb, nvsb, decs, skip_prob):
+    fr = [ol.dering_test_frame(rng, nhsb, nvsb, decs, skip_prob=skip_prob) for _ in range(nframes)]
+    planes = [np.stack([f[0][p] for f in fr]) for p in range(len(decs))]
+    flags = np.stack([f[1] for f in fr])
+    bskip = [np.stack([f[2][p] for f in fr]) for p in range(len(decs))]
+    return planes, flags, bskip
+
+
+@pytest.mark.parametrize("pic_w,pic_h,q,skip_prob", [
+    (352, 288, 60, 0.3), (352, 288, 400, 0.7), (200, 136, 12, 0.0), (64, 64, 100, 0.5),
+    (33, 17, 33, 0.2), (1920, 1080, 80, 0.5)])
+def test_dering_frames_match_checker(pic_w, pic_h, q, skip_prob):
+    """The deringing filter over whole frames (every superblock position, random decisions and
+    skip maps, chroma reusing luma's directions) against the reference's od_dering."""
+    rng = np.random.default_rng(pic_w + 3 * pic_h + q)
+    nframes = 2 if pic_w < 1000 else 1
+    chk = Checker(pic_w, pic_h)
+    qs = (q, max(1, 3 * q // 4), max(1, q // 2))
+    with _ctx(pic_w, pic_h, nframes) as ctx:
+        planes, flags, bskip = _dering_batch(rng, nframes, ctx.nhsb, ctx.nvsb, DECS, skip_prob)
+        out = [np.full_like(p, 77777) for p in planes]
+        ctx.dering_frames(out, planes, flags, bskip, qs)
+        want = chk.dering_frames(planes, DECS, flags, bskip, qs)
+        for p in range(3):
+            assert np.array_equal(out[p], want[p]), "plane %d" % p
+        assert any(np.count_nonzero(out[p] != planes[p]) for p in range(3))
+    chk.close()
+
+
+def test_dering_444_and_all_clear():
+    """4:4:4 planes (8x8 filter blocks on every plane) and a batch whose decisions are all
+    clear (pure copy)."""
+    rng = np.random.default_rng(1700)
+    decs = (0, 0, 0)
+    chk = Checker(96, 64)
+    with _ctx(96, 64, 2, decs=decs) as ctx:
+        planes, flags, bskip = _dering_batch(rng, 2, ctx.nhsb, ctx.nvsb, decs, 0.3)
+        out = [np.zeros_like(p) for p in planes]
+        ctx.dering_frames(out, planes, flags, bskip, (90, 70, 70))
+        want = chk.dering_frames(planes, decs, flags, bskip, (90, 70, 70))
+        for p in range(3):
+            assert np.array_equal(out[p], want[p]), "plane %d" % p
+        flags[:] = 0
+        ctx.dering_frames(out, planes, flags, bskip, (90, 70, 70))
+        for p in range(3):
+            assert np.array_equal(out[p], planes[p])
+    chk.close()
+
+
 def test_full_size_properties():
     """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
     size, where the CPU checker is too slow to be run on every frame: (1) the round
