@@ -250,12 +250,6 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
           cudaMemcpy(ctx->order, order.data(), order.size()*sizeof(unsigned short),
                      cudaMemcpyHostToDevice) != cudaSuccess) { rc = OD_TDLT_EFAULT; break; }
     }
-    if (const char *e = getenv("TDLT_L2_FETCH")) {   // experiments: L2 fetch granularity hint (bytes)
-      cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
-      size_t got = 0;
-      cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
-      fprintf(stderr, "daala_tdlt: L2 fetch granularity %zu\n", got);
-    }
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
