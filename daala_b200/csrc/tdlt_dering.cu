@@ -45,7 +45,8 @@ template <int D> struct DirLines {   // pixels on each line, counted at compile 
   }
 };
 
-// Cost of direction D for the 8x8 block at blk (reference src/filter.c:1655-1697): the sum
+// Cost of direction D for the 8x8 block at blk (pixels already shifted down to pixel scale,
+// the reference's x >> OD_COEFF_SHIFT; reference src/filter.c:1655-1697): the sum
 // over the direction's lines of (line sum)^2 / (pixels on the line).  Fully unrolled: the
 // line sums live in registers.
 template <int D> __device__ __forceinline__ int dir_cost(const int *blk) {
@@ -58,7 +59,7 @@ template <int D> __device__ __forceinline__ int dir_cost(const int *blk) {
     int4 b = *reinterpret_cast<const int4 *>(blk + i*kPitch + 4);
     int v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int j = 0; j < 8; j++) s[dir_line<D>(i, j)] += v[j] >> 4;
+    for (int j = 0; j < 8; j++) s[dir_line<D>(i, j)] += v[j];
   }
   constexpr DirLines<D> lines{};
   int cost = 0;
@@ -81,9 +82,243 @@ __constant__ int kDirOff[8][3] = {
     {1*kPitch + 1, 2*kPitch + 2, 3*kPitch + 3}, {1*kPitch, 2*kPitch + 1, 3*kPitch + 1},
     {1*kPitch, 2*kPitch, 3*kPitch}, {1*kPitch, 2*kPitch - 1, 3*kPitch - 1}};
 
-__device__ __forceinline__ int tap(int p, int thr) { return abs(p) < thr ? p : 0; }
+// p if |p| < thr, else 0, with one unsigned compare: |p| < thr  <=>  (unsigned)(p + thr - 1) <
+// 2*thr - 1; the bound is clamped at 0 so that a threshold of 0 accepts nothing.
+struct Gate { int c; unsigned lim; };
+__device__ __forceinline__ Gate gate(int thr) {
+  Gate g;
+  g.c = thr - 1;
+  g.lim = (unsigned)max(2*thr - 1, 0);
+  return g;
+}
+__device__ __forceinline__ int tap(int p, Gate g) { return (unsigned)(p + g.c) < g.lim ? p : 0; }
 
 }  // namespace
+
+// Tile offset of tap K of direction DIR (the table above, as a compile-time value).
+template <int DIR, int K> struct DirOff {
+  static constexpr int dy = DIR == 0 ? -(K + 1) : DIR == 1 ? (K == 0 ? 0 : -1) : DIR == 2 ? 0 :
+                            DIR == 3 ? (K == 0 ? 0 : 1) : K + 1;
+  static constexpr int dx = DIR <= 3 ? K + 1 : DIR == 4 ? K + 1 : DIR == 5 ? (K == 0 ? 0 : 1) :
+                            DIR == 6 ? 0 : (K == 0 ? 0 : -1);
+  static constexpr int value = dy*kPitch + dx;
+};
+
+// Pass 1 of one 8x8 luma block by one warp: this lane's two pixels (a, a + 4 rows).
+template <int DIR>
+__device__ __forceinline__ void pass1_block(const int *a, int *b, int thr) {
+  constexpr int o0 = DirOff<DIR, 0>::value, o1 = DirOff<DIR, 1>::value, o2 = DirOff<DIR, 2>::value;
+  const Gate g = gate(thr);
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int *q = a + h*4*kPitch;
+    const int xx = q[0];
+    int s0 = tap(q[o0] - xx, g) + tap(q[-o0] - xx, g);
+    int s1 = tap(q[o1] - xx, g) + tap(q[-o1] - xx, g) + tap(q[o2] - xx, g) + tap(q[-o2] - xx, g);
+    b[h*4*kPitch] = (short)(xx + ((3*s0 + 2*s1 + 8) >> 4));
+  }
+}
+
+// Pass 2 of one 8x8 luma block by one warp; O = tile offset across the direction.
+template <int O>
+__device__ __forceinline__ void pass2_block(const int *a, const int *b, int *g, int w, int thr) {
+  const int third = thr/3;
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int *bq = b + h*4*kPitch;
+    const int yy = bq[0];
+    const Gate ga = gate(min(thr, third + abs(yy - a[h*4*kPitch])));
+    int sum = tap(bq[O] - yy, ga) + tap(bq[-O] - yy, ga) + tap(bq[2*O] - yy, ga) +
+              tap(bq[-2*O] - yy, ga);
+    g[h*4*(long long)w] = (short)(yy + ((3*sum + 8) >> 4));
+  }
+}
+
+// One plane of one filtered superblock.  DEC is the plane's decimation: n = 32 >> DEC
+// samples a side, filter blocks of 8 >> DEC.
+template <int DEC>
+__device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int frame, int sbx,
+                                             int sby, int *A, int *B, int (*s_cost)[8],
+                                             int *s_dir, int *s_thr) {
+  constexpr int n = kSB >> DEC;
+  constexpr int span = n + 2*kBorder;
+  constexpr int lb = 3 - DEC;
+  const int t = threadIdx.x;
+  const int w = (P.nhsb*kSB) >> DEC;
+  const int *src = P.in[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
+  int *dst = P.out[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
+  int *Ai = A + kBorder*kPitch + kPadL;                 // interior origin
+  int *Bi = B + kBorder*kPitch + kPadL;
+  // ---- load the tile, ring included, as 16-byte vectors: rows -3 .. n+2, columns -4 .. n+3
+  // (the superblock starts on a 16-byte boundary).  What lies outside the frame does so in
+  // whole vectors and rows and becomes "far away" (reference OD_DERING_VERY_LARGE).
+  __syncthreads();                                      // previous plane done with A, B
+  {
+    constexpr int vrow = n/4 + 2;                       // vectors per tile row
+    const bool top = sby == 0, bottom = sby == P.nvsb - 1;
+    const bool left = sbx == 0, right = sbx == P.nhsb - 1;
+    for (int i = t; i < span*vrow; i += kThreads) {
+      const int r = i/vrow, c = i - r*vrow;
+      const int rr = r - kBorder;
+      const bool ring = rr < 0 || rr >= n || c == 0 || c == vrow - 1;
+      const bool outside = (top && rr < 0) || (bottom && rr >= n) || (left && c == 0) ||
+                           (right && c == vrow - 1);
+      int4 v = make_int4(kFar, kFar, kFar, kFar);
+      if (!outside) {
+        v = __ldg(reinterpret_cast<const int4 *>(src + (long long)rr*w - 4) + c);
+        v.x = (short)v.x; v.y = (short)v.y; v.z = (short)v.z; v.w = (short)v.w;  // the int16_t etmp copy
+      }
+      *reinterpret_cast<int4 *>(A + r*kPitch + 4*c) = v;
+      if (p == 0 && !ring) {  // luma: pixel-scale copy for the direction search (B's interior is free until pass 1)
+        v.x >>= 4; v.y >>= 4; v.z >>= 4; v.w >>= 4;
+      }
+      if (p == 0 || ring) *reinterpret_cast<int4 *>(B + r*kPitch + 4*c) = v;
+    }
+  }
+  __syncthreads();
+  // ---- luma: direction search -------------------------------------------------------------
+  if (DEC == 0 && p == 0) {
+    const int blk = t & 15, d = t >> 4;
+    const int *bp = Bi + (blk >> 2)*8*kPitch + (blk & 3)*8;
+    int c;
+    switch (d) {
+      case 0: c = dir_cost<0>(bp); break;
+      case 1: c = dir_cost<1>(bp); break;
+      case 2: c = dir_cost<2>(bp); break;
+      case 3: c = dir_cost<3>(bp); break;
+      case 4: c = dir_cost<4>(bp); break;
+      case 5: c = dir_cost<5>(bp); break;
+      case 6: c = dir_cost<6>(bp); break;
+      default: c = dir_cost<7>(bp); break;
+    }
+    s_cost[blk][d] = c;
+    __syncthreads();
+    if (t < 32) {
+      int var = 0;
+      if (t < 16) {
+        int best = 0, best_cost = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          int ck = s_cost[t][k];
+          if (ck > best_cost) { best_cost = ck; best = k; }
+        }
+        var = best_cost - s_cost[t][(best + 4) & 7];
+        s_dir[t] = best;
+      }
+      int varsum = var;
+#pragma unroll
+      for (int o = 8; o >= 1; o >>= 1) varsum += __shfl_xor_sync(0xffffffffu, varsum, o);
+      if (t < 16) {
+        // reference od_compute_thresh, src/filter.c:1816-1833
+        int v1 = min(32767, var >> 6);
+        int v2 = min(32767, varsum/(kSB*kSB));
+        unsigned prod = (unsigned)(v1*v2);
+        int e = (32 - __clz(prod)) - 9;
+        e = max(0, min(17, e));
+        s_thr[t] = (P.thr[0]*kThreshQ8[e]) >> 8;
+      }
+    }
+  }
+  else if (t < 16) {
+    s_thr[t] = P.thr[p];
+  }
+  // ---- blocks whose units and the ring of units around them are all skipped (reference
+  // src/filter.c:1899-1920; the ring is cut at the frame border only) pass through
+  if (t < 16) {     // the same 16 threads wrote s_thr above
+    constexpr int u = 2 >> DEC;
+    const int by = t >> 2, bx = t & 3;
+    const unsigned char *sk = P.bskip[p] + (long long)frame*P.skip_frame +
+                              (long long)((sby << (3 - DEC)) + by*u)*P.skip_stride +
+                              (sbx << (3 - DEC)) + bx*u;
+    int all = 1;
+    for (int i = sby ? -1 : 0; i < u + (sby != P.nvsb - 1); i++) {
+      for (int j = sbx ? -1 : 0; j < u + (sbx != P.nhsb - 1); j++) {
+        all &= sk[i*P.skip_stride + j] != 0;
+      }
+    }
+    if (all) s_thr[t] = 0;
+  }
+  __syncthreads();
+  // ---- the two passes.  A block with threshold 0 passes through both unchanged.
+  // Luma: one warp per 8x8 block at a time (two pixels per lane, four rows apart), so the
+  // block's direction and threshold are warp-uniform and the tap offsets compile-time
+  // constants; with a row pitch of 40 words the 4 x 8 pixels of a warp access fall into 32
+  // different banks.  Chroma (4x4 blocks): half a warp per block, offsets from the table.
+  const int warp = t >> 5, lane = t & 31;
+  if (DEC == 0) {
+    for (int k = 0; k < 4; k++) {
+      const int b = warp*4 + k;
+      const int thr = s_thr[b];
+      const int off = ((b >> 2)*8 + (lane >> 3))*kPitch + (b & 3)*8 + (lane & 7);
+      if (thr == 0) {
+        Bi[off] = Ai[off];
+        Bi[off + 4*kPitch] = Ai[off + 4*kPitch];
+        continue;
+      }
+      switch (s_dir[b]) {
+        case 0: pass1_block<0>(Ai + off, Bi + off, thr); break;
+        case 1: pass1_block<1>(Ai + off, Bi + off, thr); break;
+        case 2: pass1_block<2>(Ai + off, Bi + off, thr); break;
+        case 3: pass1_block<3>(Ai + off, Bi + off, thr); break;
+        case 4: pass1_block<4>(Ai + off, Bi + off, thr); break;
+        case 5: pass1_block<5>(Ai + off, Bi + off, thr); break;
+        case 6: pass1_block<6>(Ai + off, Bi + off, thr); break;
+        default: pass1_block<7>(Ai + off, Bi + off, thr); break;
+      }
+    }
+    __syncthreads();
+    for (int k = 0; k < 4; k++) {
+      const int b = warp*4 + k;
+      const int thr = s_thr[b];
+      const int r = (b >> 2)*8 + (lane >> 3), c = (b & 3)*8 + (lane & 7);
+      const int off = r*kPitch + c;
+      int *g = dst + (long long)r*w + c;
+      if (thr == 0) {
+        g[0] = Bi[off];
+        g[4*(long long)w] = Bi[off + 4*kPitch];
+      }
+      else if (s_dir[b] <= 4) pass2_block<kPitch>(Ai + off, Bi + off, g, w, thr);
+      else pass2_block<1>(Ai + off, Bi + off, g, w, thr);
+    }
+  }
+  else {
+    const int half = lane >> 4, l16 = lane & 15;
+    for (int k = 0; k < 2; k++) {
+      const int b = (warp*2 + k)*2 + half;              // two horizontally adjacent blocks per warp
+      const int thr = s_thr[b];
+      const int off = ((b >> 2)*4 + (l16 >> 2))*kPitch + (b & 3)*4 + (l16 & 3);
+      const int xx = Ai[off];
+      int yy = xx;
+      if (thr) {
+        const int *a = Ai + off;
+        const int dir = s_dir[b];
+        const int o0 = kDirOff[dir][0], o1 = kDirOff[dir][1], o2 = kDirOff[dir][2];
+        const Gate g = gate(thr);
+        int s0 = tap(a[o0] - xx, g) + tap(a[-o0] - xx, g);
+        int s1 = tap(a[o1] - xx, g) + tap(a[-o1] - xx, g) + tap(a[o2] - xx, g) + tap(a[-o2] - xx, g);
+        yy = (short)(xx + ((3*s0 + 2*s1 + 8) >> 4));
+      }
+      Bi[off] = yy;
+    }
+    __syncthreads();
+    for (int k = 0; k < 2; k++) {
+      const int b = (warp*2 + k)*2 + half;
+      const int thr = s_thr[b];
+      const int r = (b >> 2)*4 + (l16 >> 2), c = (b & 3)*4 + (l16 & 3);
+      const int *bq = Bi + r*kPitch + c;
+      const int yy = bq[0];
+      int out = yy;
+      if (thr) {
+        const int o = s_dir[b] <= 4 ? kPitch : 1;
+        const Gate ga = gate(min(thr, thr/3 + abs(yy - Ai[r*kPitch + c])));
+        int sum = tap(bq[o] - yy, ga) + tap(bq[-o] - yy, ga) + tap(bq[2*o] - yy, ga) +
+                  tap(bq[-2*o] - yy, ga);
+        out = (short)(yy + ((3*sum + 8) >> 4));
+      }
+      dst[(long long)r*w + c] = out;
+    }
+  }
+}
 
 __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
   __shared__ __align__(16) int A[kTile];
@@ -97,135 +332,23 @@ __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
   const int sb = blockIdx.x - frame*per;
   const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
   const bool filtered = P.flags[(long long)frame*per + sb] != 0;
-
   for (int p = 0; p < P.nplanes; p++) {
     const int dec = P.dec[p];
-    const int n = kSB >> dec;
-    const int w = (P.nhsb*kSB) >> dec;
-    const int *src = P.in[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
-    int *dst = P.out[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
     if (!filtered) {
       // copy through: n rows of n words as 16-byte vectors
+      const int n = kSB >> dec;
+      const int w = (P.nhsb*kSB) >> dec;
+      const long long o = frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
       const int vec_per_row = n >> 2;
       for (int i = t; i < n*vec_per_row; i += kThreads) {
         int r = i/vec_per_row, c = i - r*vec_per_row;
-        reinterpret_cast<int4 *>(dst + (long long)r*w)[c] =
-            __ldg(reinterpret_cast<const int4 *>(src + (long long)r*w) + c);
+        reinterpret_cast<int4 *>(P.out[p] + o + (long long)r*w)[c] =
+            __ldg(reinterpret_cast<const int4 *>(P.in[p] + o + (long long)r*w) + c);
       }
       continue;
     }
-    // ---- load the tile with its ring; outside the frame: far away ------------------
-    const int lo_r = sby ? -kBorder : 0, hi_r = n + (sby != P.nvsb - 1 ? kBorder : 0);
-    const int lo_c = sbx ? -kBorder : 0, hi_c = n + (sbx != P.nhsb - 1 ? kBorder : 0);
-    const int span = n + 2*kBorder;
-    __syncthreads();                                    // previous plane done with A, B
-    for (int i = t; i < span*span; i += kThreads) {
-      int r = i/span, c = i - r*span;
-      int rr = r - kBorder, cc = c - kBorder;
-      int v = kFar;
-      if (rr >= lo_r && rr < hi_r && cc >= lo_c && cc < hi_c) {
-        v = (short)__ldg(src + (long long)rr*w + cc);   // the reference's int16_t etmp copy
-      }
-      A[r*kPitch + kPadL - kBorder + c] = v;
-      B[r*kPitch + kPadL - kBorder + c] = v;
-    }
-    __syncthreads();
-    const int *Ai = A + kBorder*kPitch + kPadL;         // interior origin
-    int *Bi = B + kBorder*kPitch + kPadL;
-    // ---- luma: direction search ----------------------------------------------------
-    if (p == 0) {
-      const int blk = t & 15, d = t >> 4;
-      const int *bp = Ai + (blk >> 2)*8*kPitch + (blk & 3)*8;
-      int c;
-      switch (d) {
-        case 0: c = dir_cost<0>(bp); break;
-        case 1: c = dir_cost<1>(bp); break;
-        case 2: c = dir_cost<2>(bp); break;
-        case 3: c = dir_cost<3>(bp); break;
-        case 4: c = dir_cost<4>(bp); break;
-        case 5: c = dir_cost<5>(bp); break;
-        case 6: c = dir_cost<6>(bp); break;
-        default: c = dir_cost<7>(bp); break;
-      }
-      s_cost[blk][d] = c;
-      __syncthreads();
-      if (t < 32) {
-        int var = 0;
-        if (t < 16) {
-          int best = 0, best_cost = 0;
-#pragma unroll
-          for (int k = 0; k < 8; k++) {
-            int ck = s_cost[t][k];
-            if (ck > best_cost) { best_cost = ck; best = k; }
-          }
-          var = best_cost - s_cost[t][(best + 4) & 7];
-          s_dir[t] = best;
-        }
-        int varsum = var;
-#pragma unroll
-        for (int o = 8; o >= 1; o >>= 1) varsum += __shfl_xor_sync(0xffffffffu, varsum, o);
-        if (t < 16) {
-          // reference od_compute_thresh, src/filter.c:1816-1833
-          int v1 = min(32767, var >> 6);
-          int v2 = min(32767, varsum/(kSB*kSB));
-          unsigned prod = (unsigned)(v1*v2);
-          int e = (32 - __clz(prod)) - 9;
-          e = max(0, min(17, e));
-          s_thr[t] = (P.thr[0]*kThreshQ8[e]) >> 8;
-        }
-      }
-    }
-    else if (t < 16) {
-      s_thr[t] = P.thr[p];
-    }
-    __syncthreads();
-    // ---- blocks whose units and the ring of units around them are all skipped -----------
-    if (t < 16) {
-      const int u = 2 >> dec;
-      const int by = t >> 2, bx = t & 3;
-      const unsigned char *sk = P.bskip[p] + (long long)frame*P.skip_frame +
-                                (long long)((sby << (3 - dec)) + by*u)*P.skip_stride +
-                                (sbx << (3 - dec)) + bx*u;
-      int all = 1;
-      for (int i = sby ? -1 : 0; i < u + (sby != P.nvsb - 1); i++) {
-        for (int j = sbx ? -1 : 0; j < u + (sbx != P.nhsb - 1); j++) {
-          all &= sk[i*P.skip_stride + j] != 0;
-        }
-      }
-      if (all) s_thr[t] = 0;
-    }
-    __syncthreads();
-    // ---- the two passes: thread = one column, rows strided --------------------------------
-    const int lb = 3 - dec;
-    const int col = t & (n - 1);
-    const int row0 = t >> (5 - dec);
-    const int rstep = kThreads >> (5 - dec);
-    for (int r = row0; r < n; r += rstep) {
-      const int b = (r >> lb)*4 + (col >> lb);
-      const int thr = s_thr[b], dir = s_dir[b];
-      const int *a = Ai + r*kPitch + col;
-      const int xx = a[0];
-      int sum = 0;
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        const int o = kDirOff[dir][k];
-        const int tp = k == 0 ? 3 : 2;
-        sum += tp*(tap(a[o] - xx, thr) + tap(a[-o] - xx, thr));
-      }
-      Bi[r*kPitch + col] = (short)(xx + ((sum + 8) >> 4));
-    }
-    __syncthreads();
-    for (int r = row0; r < n; r += rstep) {
-      const int b = (r >> lb)*4 + (col >> lb);
-      const int thr = s_thr[b], dir = s_dir[b];
-      const int o = dir <= 4 ? kPitch : 1;
-      const int *bq = Bi + r*kPitch + col;
-      const int yy = bq[0];
-      const int ath = min(thr, thr/3 + abs(yy - Ai[r*kPitch + col]));
-      int sum = tap(bq[o] - yy, ath) + tap(bq[-o] - yy, ath) + tap(bq[2*o] - yy, ath) +
-                tap(bq[-2*o] - yy, ath);
-      dst[(long long)r*w + col] = (short)(yy + ((3*sum + 8) >> 4));
-    }
+    if (dec == 0) dering_plane<0>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr);
+    else dering_plane<1>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr);
   }
 }
 
