@@ -139,7 +139,7 @@ __device__ __forceinline__ void pass2_block(const int *a, const int *b, int *g, 
 template <int DEC>
 __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int frame, int sbx,
                                              int sby, int *A, int *B, int (*s_cost)[8],
-                                             int *s_dir, int *s_thr) {
+                                             int *s_dir, int *s_thr, int *s_coded) {
   constexpr int n = kSB >> DEC;
   constexpr int span = n + 2*kBorder;
   constexpr int lb = 3 - DEC;
@@ -153,6 +153,28 @@ __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int f
   // (the superblock starts on a 16-byte boundary).  What lies outside the frame does so in
   // whole vectors and rows and becomes "far away" (reference OD_DERING_VERY_LARGE).
   __syncthreads();                                      // previous plane done with A, B
+  // Skip test first, so that its loads are in flight under the tile's: a block whose own
+  // 4x4 units and the ring of units around them (lapping reaches there) are all skipped is
+  // left alone (reference src/filter.c:1899-1920; the ring is cut at the frame border only).
+  // Eight lanes per block, two flags of the 4x4 window each.
+  {
+    constexpr int u = 2 >> DEC;
+    const int b = t >> 3;
+    const unsigned char *sk = P.bskip[p] + (long long)frame*P.skip_frame +
+                              (long long)((sby << (3 - DEC)) + (b >> 2)*u)*P.skip_stride +
+                              (sbx << (3 - DEC)) + (b & 3)*u;
+    const int lo_i = sby ? -1 : 0, hi_i = u + (sby != P.nvsb - 1);
+    const int lo_j = sbx ? -1 : 0, hi_j = u + (sbx != P.nhsb - 1);
+    const int wi = ((t & 7) >> 1) - 1;
+    int coded = 0;
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      const int wj = (t & 1)*2 + e - 1;
+      if (wi >= lo_i && wi < hi_i && wj >= lo_j && wj < hi_j) coded |= !__ldg(sk + wi*P.skip_stride + wj);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, coded);
+    if ((t & 7) == 0) s_coded[b] = (m >> (t & 24)) & 0xffu;
+  }
   {
     constexpr int vrow = n/4 + 2;                       // vectors per tile row
     const bool top = sby == 0, bottom = sby == P.nvsb - 1;
@@ -222,22 +244,7 @@ __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int f
   else if (t < 16) {
     s_thr[t] = P.thr[p];
   }
-  // ---- blocks whose units and the ring of units around them are all skipped (reference
-  // src/filter.c:1899-1920; the ring is cut at the frame border only) pass through
-  if (t < 16) {     // the same 16 threads wrote s_thr above
-    constexpr int u = 2 >> DEC;
-    const int by = t >> 2, bx = t & 3;
-    const unsigned char *sk = P.bskip[p] + (long long)frame*P.skip_frame +
-                              (long long)((sby << (3 - DEC)) + by*u)*P.skip_stride +
-                              (sbx << (3 - DEC)) + bx*u;
-    int all = 1;
-    for (int i = sby ? -1 : 0; i < u + (sby != P.nvsb - 1); i++) {
-      for (int j = sbx ? -1 : 0; j < u + (sbx != P.nhsb - 1); j++) {
-        all &= sk[i*P.skip_stride + j] != 0;
-      }
-    }
-    if (all) s_thr[t] = 0;
-  }
+  if (t < 16 && !s_coded[t]) s_thr[t] = 0;            // all skipped: pass through
   __syncthreads();
   // ---- the two passes.  A block with threshold 0 passes through both unchanged.
   // Luma: one warp per 8x8 block at a time (two pixels per lane, four rows apart), so the
@@ -326,6 +333,7 @@ __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
   __shared__ int s_cost[16][8];
   __shared__ int s_dir[16];
   __shared__ int s_thr[16];
+  __shared__ int s_coded[16];
   const int t = threadIdx.x;
   const int per = P.nhsb*P.nvsb;
   const int frame = blockIdx.x/per;
@@ -347,8 +355,8 @@ __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
       }
       continue;
     }
-    if (dec == 0) dering_plane<0>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr);
-    else dering_plane<1>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr);
+    if (dec == 0) dering_plane<0>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr, s_coded);
+    else dering_plane<1>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr, s_coded);
   }
 }
 
