@@ -284,3 +284,68 @@ void oc_dering_frame(oc_coeff *const out[], const oc_coeff *const in[], int npla
   }
   for (p = 0; p < nplanes; p++) free(e[p]);
 }
+
+/* ---------------------------------------------------------- bilinear smoothing -- */
+
+/* reference OD_BILINEAR_STRENGTH, src/filter.c:154 */
+static const int OC_BILINEAR_STRENGTH[4] = {5, 20, 20, 5};
+
+/* reference od_bilinear_smooth, src/filter.c:1952-2008: the block is pulled towards the
+   bilinear interpolation of its four corners, by a Wiener-style weight that falls with the
+   distortion this would cause relative to the quantization noise.  Plain int arithmetic
+   as in the reference (including a11's correction taking the already corrected a10). */
+void oc_bilinear_smooth(oc_coeff *x, int ln, int stride, int q, int pli) {
+  int n = 1 << ln;
+  int a00 = x[0];
+  int a01 = x[n - 1] - x[0];
+  int a10 = x[(n - 1)*stride] - x[0];
+  int a11 = x[(n - 1)*stride + n - 1] + x[0] - x[(n - 1)*stride] - x[n - 1];
+  int shift = 2*4 + 2*ln - 16 > 0 ? 2*4 + 2*ln - 16 : 0;   /* OD_COEFF_SHIFT = 4 */
+  int32_t dist = 0;
+  int w;
+  int i;
+  int j;
+  oc_coeff y[32][32];
+  /* times 1 + 1/n, about n/(n - 1): the loop divides by n */
+  a01 += (a01 + n/2) >> ln;
+  a10 += (a10 + n/2) >> ln;
+  a11 += (2*a10 + n/2) >> ln;
+  for (i = 0; i < n; i++) {
+    int32_t row = 0;
+    for (j = 0; j < n; j++) {
+      int d;
+      y[i][j] = a00 + ((j*a01 + i*a10 + (j*i*a11 >> ln) + n/2) >> ln);
+      d = y[i][j] - x[i*stride + j];
+      row += d*d;
+    }
+    dist += row >> shift;
+  }
+  dist += n/2;
+  dist >>= 2*ln - shift;
+  w = OC_BILINEAR_STRENGTH[pli]*q*q/(1 + 12*dist);
+  if (w > 1024) w = 1024;
+  w = w*w >> 12;
+  for (i = 0; i < n; i++) {
+    for (j = 0; j < n; j++) x[i*stride + j] -= (w*(x[i*stride + j] - y[i][j]) + 128) >> 8;
+  }
+}
+
+/* od_smooth_recursive with min_bs = 32x32 over every superblock, as the decoder calls it on
+   keyframes (src/decode.c:1134-1146, src/filter.c:2010-2039): only superblocks coded as one
+   32x32 block are smoothed, in every plane (4:2:0 chroma: the 16x16 block). */
+void oc_smooth_frame(oc_coeff *const c[], int nplanes, const int dec[], int nhsb, int nvsb,
+ const unsigned char *bsize, int bstride, const int q[]) {
+  int p;
+  int sbx;
+  int sby;
+  for (p = 0; p < nplanes; p++) {
+    int w = nhsb*32 >> dec[p];
+    int ln = 5 - dec[p];
+    for (sby = 0; sby < nvsb; sby++) {
+      for (sbx = 0; sbx < nhsb; sbx++) {
+        if (bsize[4*sby*bstride + 4*sbx] != 3) continue;
+        oc_bilinear_smooth(c[p] + (sby << ln)*w + (sbx << ln), ln, w, q[p], p);
+      }
+    }
+  }
+}

@@ -218,6 +218,35 @@ def dering_test_frame(rng, nhsb, nvsb, decs=(0, 1, 1), skip_prob=0.5, flag_prob=
     return planes, flags, bskip
 
 
+def port_smooth_frame(planes, decs, bsize, q):
+    """Keyframe bilinear smoothing of the 32x32-coded superblocks (restatement); returns new planes."""
+    lib = port()
+    out = [np.ascontiguousarray(p, dtype=np.int32).copy() for p in planes]
+    H, W = out[0].shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    pa = (C.c_void_p * 4)(*[o.ctypes.data for o in out])
+    lib.oc_smooth_frame(pa, len(out), (C.c_int * 4)(*decs), W // 32, H // 32, ptr(bsize), bsize.shape[1],
+                        (C.c_int * 4)(*q))
+    return out
+
+
+def ref_smooth_frame(planes, decs, bsize, q):
+    """The same through the REFERENCE's od_smooth_recursive, called per superblock and plane
+    with the decoder's arguments (src/decode.c:1139-1143)."""
+    lib = ref()
+    out = [np.ascontiguousarray(p, dtype=np.int32).copy() for p in planes]
+    H, W = out[0].shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    f = lib.od_smooth_recursive
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 10
+    for p, dec in enumerate(decs):
+        for sby in range(H // 32):
+            for sbx in range(W // 32):
+                f(ptr(out[p]), ptr(bsize), bsize.shape[1], sbx, sby, 3, W >> dec, dec, dec, 3, int(q[p]), p)
+    return out
+
+
 # ----------------------------------------------------------------- ref API --
 class RefCtx:
     """An instance of the reference encoder state for one picture size."""

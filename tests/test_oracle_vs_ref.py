@@ -368,3 +368,28 @@ def test_dering_frame_matches_reference(reflib, nhsb, nvsb, q):
                 changed += int(np.count_nonzero(a[p] != planes[p]))
             if trial == 0 and flags.any():
                 assert changed > 0          # the test frame does exercise the filter
+
+
+@pytest.mark.parametrize("w,h,q", [(64, 64, 30), (352, 288, 200), (200, 136, 1000)])
+def test_smooth_frame_matches_reference(reflib, w, h, q):
+    """Keyframe bilinear smoothing (od_smooth_recursive / od_bilinear_smooth) of every
+    superblock coded as one 32x32 block, luma and 4:2:0 chroma."""
+    rng = np.random.default_rng(1600 + w)
+    fw, fh = ol.padded_dims(w, h)
+    nhsb, nvsb = fw // 32, fh // 32
+    decs = (0, 1, 1)
+    qs = (q, max(1, 3 * q // 4), max(1, q // 2))
+    for trial in range(3):
+        bsize = ol.random_quadtree_bsize(nhsb, nvsb, rng, 0.4, 0.6, 0.5) if trial < 2 else \
+            np.full((nvsb * 4, nhsb * 4), 3, np.uint8)
+        yy, xx = np.mgrid[0:fh, 0:fw]
+        luma = (xx * rng.uniform(-3, 3) + yy * rng.uniform(-3, 3) + rng.normal(0, (3, 40, 400)[trial], size=(fh, fw)))
+        planes = [np.clip(luma, -2040, 2040).astype(np.int32)]
+        planes += [np.ascontiguousarray(planes[0][::2, ::2] // 2 + rng.integers(-20, 20, size=(fh // 2, fw // 2))).astype(np.int32)
+                   for _ in range(2)]
+        a = ol.ref_smooth_frame(planes, decs, bsize, qs)
+        b = ol.port_smooth_frame(planes, decs, bsize, qs)
+        for p in range(3):
+            assert np.array_equal(a[p], b[p]), "plane %d" % p
+        if (bsize[::4, ::4] == 3).any() and trial == 0 and q >= 200:   # smooth block, coarse quantizer
+            assert any(np.count_nonzero(a[p] != planes[p]) for p in range(3))

@@ -17,6 +17,12 @@ timeout 300 python bench.py --workload 1080p --no-cpu --no-e2e > $O/bench_1080p_
 cat $O/bench_1080p_$TAG.json
 timeout 300 python bench.py --workload 1080p8x8 --no-cpu --no-e2e > $O/bench_1080p8x8_$TAG.json 2> $O/bench_1080p8x8_$TAG.err; echo "bench1080p8x8 rc=$?"
 cat $O/bench_1080p8x8_$TAG.json
+timeout 300 python tools/bench_cfl.py > $O/cfl_4k_$TAG.json 2> $O/cfl_4k_$TAG.err; echo "cfl rc=$?"
+cat $O/cfl_4k_$TAG.json
+timeout 300 python tools/bench_dering.py > $O/dering_4k_$TAG.json 2> $O/dering_4k_$TAG.err; echo "dering rc=$?"
+cat $O/dering_4k_$TAG.json
+timeout 300 python tools/bench_dering.py --no-cpu --flag-prob 1.0 --skip-prob 0 > $O/dering_4k_all_$TAG.json 2>> $O/dering_4k_$TAG.err
+cat $O/dering_4k_all_$TAG.json
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
 timeout 600 $CMD > $O/plain_$TAG.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
