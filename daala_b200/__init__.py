@@ -64,6 +64,8 @@ def lib():
         L.od_resample_luma_coeffs_cuda.restype = None
         L.od_tdlt_dering_batch.argtypes = [vp, arr, arr, vp, arr, C.POINTER(ci), ci, vp]
         L.od_tdlt_dering_frames.argtypes = [vp, arr, arr, vp, arr, C.POINTER(ci), ci]
+        L.od_tdlt_smooth_batch.argtypes = [vp, arr, vp, C.POINTER(ci), ci, vp]
+        L.od_tdlt_smooth_frames.argtypes = [vp, arr, vp, C.POINTER(ci), ci]
         L.od_tdlt_fwd_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_inv_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         iarr, larr = C.POINTER(ci), C.POINTER(ll)
@@ -172,6 +174,12 @@ class TdltContext:
                                                 flags_ptr, _ptr_array(bskip_ptrs), qa, nframes, stream),
                     "od_tdlt_dering_batch")
 
+    def smooth_batch(self, c_ptrs, bsize_ptr, q, nframes, stream=0):
+        """Device pointers: keyframe bilinear smoothing in place (od_tdlt_smooth_batch)."""
+        qa = (C.c_int * NPLANES_MAX)(*q)
+        self._check(self.L.od_tdlt_smooth_batch(self._h, _ptr_array(c_ptrs), bsize_ptr, qa, nframes,
+                                                stream), "od_tdlt_smooth_batch")
+
     def pix_to_coeff_batch(self, c_ptr, pix_ptr, pli, nframes, xstride=1, bitdepth_mode=1,
                            lossless=0, stream=0):
         self._check(self.L.od_tdlt_pix_to_coeff_batch(self._h, c_ptr, pix_ptr, pli, nframes, xstride,
@@ -213,6 +221,13 @@ class TdltContext:
             self._h, _ptr_array([a.ctypes.data for a in out_planes]),
             _ptr_array([a.ctypes.data for a in in_planes]), flags.ctypes.data,
             _ptr_array([a.ctypes.data for a in bskip]), qa, flags.shape[0]), "od_tdlt_dering_frames")
+
+    def smooth_frames(self, c_planes, bsize, q):
+        """Host arrays, in place: planes (nframes, h, w) int32, bsize maps, one quantizer per plane."""
+        qa = (C.c_int * NPLANES_MAX)(*q)
+        self._check(self.L.od_tdlt_smooth_frames(
+            self._h, _ptr_array([a.ctypes.data for a in c_planes]), bsize.ctypes.data, qa,
+            bsize.shape[0]), "od_tdlt_smooth_frames")
 
     def _pix_args(self, pix_planes, xstride):
         ys = (C.c_int * NPLANES_MAX)()

@@ -43,4 +43,15 @@ struct DeringParams {
 };
 void launch_dering(const DeringParams &P, int nframes, cudaStream_t st);
 
+// Keyframe bilinear smoothing of the superblocks coded as one 32x32 block, in place.
+struct SmoothParams {
+  int *c[4];
+  const unsigned char *bsize;      // block-size maps, (nvsb*4) x (nhsb*4) per frame
+  long long plane_size[4];
+  int dec[4];
+  int q[4];
+  int nplanes, nhsb, nvsb;
+};
+void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st);
+
 }  // namespace tdlt

@@ -545,6 +545,37 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
   return OD_TDLT_SUCCESS;
 }
 
+// Keyframe bilinear smoothing (reference od_smooth_recursive with min_bs = 32x32,
+// src/filter.c:2010-2039 / :1952-2008, called per superblock and plane from
+// src/decode.c:1134-1146): in place on the reconstructed planes.
+int od_tdlt_smooth_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
+                         const int q[], int nframes, void *stream) {
+  if (!ctx || !c || !bsize || !q) return OD_TDLT_EFAULT;
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
+  SmoothParams P = {};
+  P.nplanes = ctx->g.nplanes;
+  for (int p = 0; p < P.nplanes; p++) {
+    if (!c[p]) return OD_TDLT_EFAULT;
+    if (ctx->g.xdec[p] != ctx->g.ydec[p] || ctx->g.xdec[p] > 1) {
+      return fail(ctx, OD_TDLT_EINVAL, "smoothing needs 4:4:4 or 4:2:0 planes (the reference "
+                  "asserts xdec == ydec, src/filter.c:2016)");
+    }
+    if (q[p] < 0 || q[p] > 10000) return fail(ctx, OD_TDLT_EINVAL, "quantizer %d", q[p]);
+    P.c[p] = c[p];
+    P.plane_size[p] = ctx->plane_size[p];
+    P.dec[p] = ctx->g.xdec[p];
+    P.q[p] = q[p];
+  }
+  P.bsize = bsize;
+  P.nhsb = ctx->nhsb;
+  P.nvsb = ctx->nvsb;
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_smooth(P, nframes, (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------- whole-frame host calls --
@@ -749,6 +780,31 @@ int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coef
   if (rc) return rc;
   for (int p = 0; p < np; p++) {
     CK(ctx, cudaMemcpyAsync(out[p], ctx->dev_d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_smooth_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
+                          const int q[], int nframes) {
+  if (!ctx || !c || !bsize || !q) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int np = ctx->g.nplanes;
+  for (int p = 0; p < np; p++) {
+    if (!c[p]) return OD_TDLT_EFAULT;
+    CK(ctx, cudaMemcpyAsync(ctx->dev_c[p], c[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyHostToDevice, st));
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, (size_t)od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_smooth_batch(ctx, ctx->dev_c, ctx->dev_bsize, q, nframes, st);
+  if (rc) return rc;
+  for (int p = 0; p < np; p++) {
+    CK(ctx, cudaMemcpyAsync(c[p], ctx->dev_c[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
                             cudaMemcpyDeviceToHost, st));
   }
   CK(ctx, cudaStreamSynchronize(st));

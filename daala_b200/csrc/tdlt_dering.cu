@@ -365,3 +365,86 @@ void launch_dering(const DeringParams &P, int nframes, cudaStream_t st) {
 }
 
 }  // namespace tdlt
+
+// ---------------------------------------------------------------------------
+// Keyframe bilinear smoothing (reference od_bilinear_smooth, src/filter.c:1952-2008, applied
+// by od_smooth_recursive with min_bs = 32x32 from src/decode.c:1134-1146): every superblock
+// coded as ONE 32x32 block is pulled towards the bilinear interpolation of its four
+// corners, by a weight that falls with the distortion this causes relative to the
+// quantization noise.  In place; one CTA per superblock and frame, all planes; a warp takes
+// whole rows (the distortion is truncated per row before it is summed).
+// ---------------------------------------------------------------------------
+namespace tdlt {
+
+namespace {
+__constant__ int kBilinearStrength[4] = {5, 20, 20, 5};   // reference src/filter.c:154
+
+template <int DEC>
+__device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli, int *s_part) {
+  constexpr int ln = 5 - DEC, n = 1 << ln;
+  constexpr int shift = 2*4 + 2*ln - 16 > 0 ? 2*4 + 2*ln - 16 : 0;   // OD_COEFF_SHIFT = 4
+  constexpr int rows_per_step = kThreads/n;             // 4 rows (luma) or 8 (chroma) at a time
+  constexpr int steps = n/rows_per_step;
+  const int t = threadIdx.x;
+  const int j = t & (n - 1), i0 = t >> ln;
+  const int x00 = x[0], x01 = x[n - 1], x10 = x[(long long)(n - 1)*w],
+            x11 = x[(long long)(n - 1)*w + n - 1];
+  int a01 = x01 - x00, a10 = x10 - x00, a11 = x11 + x00 - x10 - x01;
+  a01 += (a01 + n/2) >> ln;
+  a10 += (a10 + n/2) >> ln;
+  a11 += (2*a10 + n/2) >> ln;
+  int xv[steps], yv[steps];
+  int dist = 0;
+#pragma unroll
+  for (int s = 0; s < steps; s++) {
+    const int i = i0 + s*rows_per_step;
+    xv[s] = x[(long long)i*w + j];
+    yv[s] = x00 + ((j*a01 + i*a10 + ((j*i*a11) >> ln) + n/2) >> ln);
+    const int d = yv[s] - xv[s];
+    int row = d*d;
+#pragma unroll
+    for (int o = n/2; o >= 1; o >>= 1) row += __shfl_xor_sync(0xffffffffu, row, o);
+    dist += row >> shift;                               // every lane of the row holds the row's sum
+  }
+  // rows of this thread's lane group -> superblock: one value per row group, summed in shared memory
+  __syncthreads();                                      // s_part free (previous plane)
+  if (j == 0) s_part[i0] = dist;
+  __syncthreads();
+  int total = 0;
+#pragma unroll
+  for (int k = 0; k < rows_per_step; k++) total += s_part[k];
+  total += n/2;
+  total >>= 2*ln - shift;
+  int wgt = min(1024, kBilinearStrength[pli]*q*q/(1 + 12*total));
+  wgt = (wgt*wgt) >> 12;
+#pragma unroll
+  for (int s = 0; s < steps; s++) {
+    const int i = i0 + s*rows_per_step;
+    x[(long long)i*w + j] = xv[s] - ((wgt*(xv[s] - yv[s]) + 128) >> 8);
+  }
+}
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P) {
+  __shared__ int s_part[8];
+  const int per = P.nhsb*P.nvsb;
+  const int frame = blockIdx.x/per;
+  const int sb = blockIdx.x - frame*per;
+  const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
+  // the superblock is one 32x32 block when its first map entry says so
+  if (P.bsize[(long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx] != 3) return;
+  for (int p = 0; p < P.nplanes; p++) {
+    const int dec = P.dec[p];
+    const int n = kSB >> dec;
+    const int w = (P.nhsb*kSB) >> dec;
+    int *x = P.c[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
+    if (dec == 0) smooth_block<0>(x, w, P.q[p], p, s_part);
+    else smooth_block<1>(x, w, P.q[p], p, s_part);
+  }
+}
+
+void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st) {
+  smooth_kernel<<<(unsigned)(P.nhsb*P.nvsb*nframes), kThreads, 0, st>>>(P);
+}
+
+}  // namespace tdlt

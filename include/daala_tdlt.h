@@ -142,6 +142,15 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
  const unsigned char *flags, const unsigned char *const bskip[], const int q[], int nframes,
  void *stream);
 
+/* Keyframe bilinear smoothing, the step after deringing (reference od_smooth_recursive with
+   min_bs = OD_BLOCK_32X32 -> od_bilinear_smooth, src/filter.c:1952-2039, called per
+   superblock and plane at src/decode.c:1134-1146 when quantizer[0] > 0 on keyframes): every
+   superblock the map codes as one 32x32 block is smoothed IN PLACE in every plane.
+   bsize: the block-size maps (layout above); q[p]: plane quantizers, HOST array.  4:4:4 or
+   4:2:0.  DEVICE pointers in c/bsize, asynchronous on `stream`. */
+int od_tdlt_smooth_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
+ const int q[], int nframes, void *stream);
+
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
    out as above but in host memory (pinned or pageable).
@@ -157,6 +166,9 @@ int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_lum
 /* Host-pointer form of od_tdlt_dering_batch (synchronous, nframes <= max_frames). */
 int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
  const unsigned char *flags, const unsigned char *const bskip[], const int q[], int nframes);
+/* Host-pointer form of od_tdlt_smooth_batch (synchronous, in place, nframes <= max_frames). */
+int od_tdlt_smooth_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
+ const int q[], int nframes);
 /* Same with the pixel conversion done on the device: the host ships 8/16-bit
    reference-buffer samples instead of od_coeff (od_ref_plane_to_coeff,
    src/state.c:1252; od_coeff_to_ref_plane, :1320).  pix[pli] points at the

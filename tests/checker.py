@@ -50,6 +50,15 @@ class Checker:
                 out[p][f] = res[p]
         return out
 
+    def smooth_frames(self, planes, decs, bsize, q):
+        out = [np.empty_like(p) for p in planes]
+        f = ol.ref_smooth_frame if self.rc else ol.port_smooth_frame
+        for i in range(bsize.shape[0]):
+            res = f([p[i] for p in planes], decs, bsize[i], q)
+            for p in range(len(planes)):
+                out[p][i] = res[p]
+        return out
+
     def fwd_frames(self, c_planes, bsize, decs, keyframe, haar=0):
         """c_planes[p]: (nframes, h, w) -> list of d planes of the same shape."""
         out = []

@@ -379,6 +379,35 @@ def test_dering_444_and_all_clear():
     chk.close()
 
 
+@pytest.mark.parametrize("pic_w,pic_h,q,decs", [
+    (352, 288, 200, (0, 1, 1)), (200, 136, 1000, (0, 1, 1)), (64, 64, 30, (0, 1, 1)),
+    (96, 64, 300, (0, 0, 0)), (1920, 1080, 150, (0, 1, 1))])
+def test_smooth_frames_match_checker(pic_w, pic_h, q, decs):
+    """Keyframe bilinear smoothing of the 32x32-coded superblocks, in place, against the
+    reference's od_smooth_recursive."""
+    rng = np.random.default_rng(pic_w + pic_h + q)
+    nframes = 2 if pic_w < 1000 else 1
+    chk = Checker(pic_w, pic_h)
+    qs = (q, max(1, 3 * q // 4), max(1, q // 2))
+    with _ctx(pic_w, pic_h, nframes, decs=decs) as ctx:
+        bsize = np.stack([ol.random_quadtree_bsize(ctx.nhsb, ctx.nvsb, rng, 0.4, 0.6, 0.5)
+                          for _ in range(nframes)])
+        yy, xx = np.mgrid[0:chk.fh, 0:chk.fw]
+        luma = np.stack([xx * rng.uniform(-3, 3) + yy * rng.uniform(-3, 3) +
+                         rng.normal(0, 3 + 30 * f, size=(chk.fh, chk.fw)) for f in range(nframes)])
+        planes = [np.clip(luma, -2040, 2040).astype(np.int32)]
+        for dec in decs[1:]:
+            planes.append(np.ascontiguousarray(planes[0][:, ::1 << dec, ::1 << dec] // 2).astype(np.int32))
+        want = chk.smooth_frames(planes, decs, bsize, qs)
+        got = [p.copy() for p in planes]
+        ctx.smooth_frames(got, bsize, qs)
+        for p in range(len(decs)):
+            assert np.array_equal(got[p], want[p]), "plane %d" % p
+        if q >= 150:
+            assert any(np.count_nonzero(got[p] != planes[p]) for p in range(len(decs)))
+    chk.close()
+
+
 def test_full_size_properties():
     """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
     size, where the CPU checker is too slow to be run on every frame: (1) the round
