@@ -54,4 +54,9 @@ struct SmoothParams {
 };
 void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st);
 
+// One block (n = 4 or 8) through one of the two deringing filters; `in` dense with its
+// 3-sample ring (pitch n + 6), x: the unfiltered block (orthogonal filter only).
+void launch_dering_block(short *y, const short *in, const short *x, int n, int thr, int dir,
+                         bool orthogonal, cudaStream_t st);
+
 }  // namespace tdlt

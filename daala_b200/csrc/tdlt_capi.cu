@@ -5,6 +5,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -899,6 +900,48 @@ void od_bin_fdct16x16_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct
 void od_bin_idct16x16_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(2, true, x, xs, y, ys); }
 void od_bin_fdct32x32_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(3, false, y, ys, x, xs); }
 void od_bin_idct32x32_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(3, true, x, xs, y, ys); }
+
+// The deringing filters of the reference's dispatch table (src/filter.h:46-65,
+// src/filter.c:1715-1800), one block, host pointers, synchronous.  `in` points at the
+// block inside a buffer of row pitch OD_FILT_BSTRIDE = 38 with at least three samples
+// around it, exactly as od_dering passes it (src/filter.c:1922-1940).
+static void dering_block(int n, bool orthogonal, int16_t *y, int ystride, const int16_t *in,
+                         const int16_t *x, int xstride, int threshold, int dir) {
+  if (dir < 0 || dir > 7) die("od_filter_dering_*: direction outside 0..7", cudaErrorInvalidValue);
+  const int kInPitch = 38, span = n + 6;
+  short *d = reinterpret_cast<short *>(g_scratch.A(256));
+  short *din = d, *dx = d + 200, *dy = d + 300;       // 14*14 + 8*8 + 8*8 shorts
+  CKF(cudaMemcpy2D(din, (size_t)span*2, in - 3*kInPitch - 3, (size_t)kInPitch*2, (size_t)span*2, span,
+                   cudaMemcpyHostToDevice));
+  if (orthogonal) {
+    CKF(cudaMemcpy2D(dx, (size_t)n*2, x, (size_t)xstride*2, (size_t)n*2, n, cudaMemcpyHostToDevice));
+  }
+  launch_dering_block(dy, din, dx, n, threshold, dir, orthogonal, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  CKF(cudaMemcpy2D(y, (size_t)ystride*2, dy, (size_t)n*2, (size_t)n*2, n, cudaMemcpyDeviceToHost));
+}
+void od_filter_dering_direction_4x4_cuda(int16_t *y, int ystride, int16_t *in, int threshold, int dir) {
+  dering_block(4, false, y, ystride, in, nullptr, 0, threshold, dir);
+}
+void od_filter_dering_direction_8x8_cuda(int16_t *y, int ystride, int16_t *in, int threshold, int dir) {
+  dering_block(8, false, y, ystride, in, nullptr, 0, threshold, dir);
+}
+void od_filter_dering_orthogonal_4x4_cuda(int16_t *y, int ystride, int16_t *in, int16_t *x, int xstride,
+                                          int threshold, int dir) {
+  dering_block(4, true, y, ystride, in, x, xstride, threshold, dir);
+}
+void od_filter_dering_orthogonal_8x8_cuda(int16_t *y, int ystride, int16_t *in, int16_t *x, int xstride,
+                                          int threshold, int dir) {
+  dering_block(8, true, y, ystride, in, x, xstride, threshold, dir);
+}
+void od_tdlt_dering_vtbl_init_cuda(od_tdlt_dering_direction_func direction[],
+                                   od_tdlt_dering_orthogonal_func orthogonal[]) {
+  direction[0] = od_filter_dering_direction_4x4_cuda;
+  direction[1] = od_filter_dering_direction_8x8_cuda;
+  orthogonal[0] = od_filter_dering_orthogonal_4x4_cuda;
+  orthogonal[1] = od_filter_dering_orthogonal_8x8_cuda;
+}
 
 void od_tdlt_opt_vtbl_init_cuda(od_tdlt_dct_func_2d fdct_2d[], od_tdlt_dct_func_2d idct_2d[]) {
   fdct_2d[0] = od_bin_fdct4x4_cuda;   idct_2d[0] = od_bin_idct4x4_cuda;

@@ -448,3 +448,46 @@ void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st) {
 }
 
 }  // namespace tdlt
+
+// ---------------------------------------------------------------------------
+// The two filters with the reference's own signatures, one block (the entries of its
+// dispatch table, od_filter_dering_direction / _orthogonal, src/filter.h:46-65): parity
+// surface behind the *_cuda calls, one thread per pixel.  `in`: the block with its 3-sample
+// ring, dense, pitch n + 6.
+// ---------------------------------------------------------------------------
+namespace tdlt {
+
+__global__ void dering_block_kernel(short *y, const short *in, const short *x, int n, int thr,
+                                    int dir, int orthogonal) {
+  const int i = threadIdx.x/n, j = threadIdx.x - i*n;
+  if (i >= n) return;
+  const int pitch = n + 2*kBorder;
+  const short *a = in + (i + kBorder)*pitch + j + kBorder;
+  const int xx = a[0];
+  if (!orthogonal) {
+    const Gate g = gate(thr);
+    int s[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      // the table is in tile pitch: back to (dy, dx)
+      const int o = kDirOff[dir][k];
+      const int dy = (o + 3*kPitch + kPitch/2)/kPitch - 3, dx = o - dy*kPitch;
+      const int oo = dy*pitch + dx;
+      s[k] = tap(a[oo] - xx, g) + tap(a[-oo] - xx, g);
+    }
+    y[i*n + j] = (short)(xx + ((3*s[0] + 2*(s[1] + s[2]) + 8) >> 4));
+  }
+  else {
+    const int o = dir <= 4 ? pitch : 1;
+    const Gate g = gate(min(thr, thr/3 + abs(xx - x[i*n + j])));
+    const int sum = tap(a[o] - xx, g) + tap(a[-o] - xx, g) + tap(a[2*o] - xx, g) + tap(a[-2*o] - xx, g);
+    y[i*n + j] = (short)(xx + ((3*sum + 8) >> 4));
+  }
+}
+
+void launch_dering_block(short *y, const short *in, const short *x, int n, int thr, int dir,
+                         bool orthogonal, cudaStream_t st) {
+  dering_block_kernel<<<1, 64, 0, st>>>(y, in, x, n, thr, dir, orthogonal ? 1 : 0);
+}
+
+}  // namespace tdlt

@@ -202,6 +202,29 @@ void od_bin_idct32x32_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystr
 typedef void (*od_tdlt_dct_func_2d)(od_coeff *out, int out_stride, const od_coeff *in,
  int in_stride);
 void od_tdlt_opt_vtbl_init_cuda(od_tdlt_dct_func_2d fdct_2d[], od_tdlt_dct_func_2d idct_2d[]);
+
+/* The deringing filters of the same table (od_filter_dering_direction_func /
+   od_filter_dering_orthogonal_func, src/filter.h:46-65; entries [0] = 4x4, [1] = 8x8,
+   src/state.h:120-121; C versions src/filter.c:1715-1800, SSE2 twins in
+   src/x86/sse2filter.c).  Host pointers, synchronous, one launch per block: for checking
+   through od_dering's own call sites (src/filter.c:1922-1940), not for speed.  `in` points
+   at the block inside a buffer of row pitch OD_FILT_BSTRIDE (38) with three samples around it.
+     od_tdlt_dering_vtbl_init_cuda(state->opt_vtbl.filter_dering_direction,
+                                   state->opt_vtbl.filter_dering_orthogonal);  */
+typedef void (*od_tdlt_dering_direction_func)(int16_t *y, int ystride, int16_t *in,
+ int threshold, int dir);
+typedef void (*od_tdlt_dering_orthogonal_func)(int16_t *y, int ystride, int16_t *in,
+ int16_t *x, int xstride, int threshold, int dir);
+void od_filter_dering_direction_4x4_cuda(int16_t *y, int ystride, int16_t *in, int threshold,
+ int dir);
+void od_filter_dering_direction_8x8_cuda(int16_t *y, int ystride, int16_t *in, int threshold,
+ int dir);
+void od_filter_dering_orthogonal_4x4_cuda(int16_t *y, int ystride, int16_t *in, int16_t *x,
+ int xstride, int threshold, int dir);
+void od_filter_dering_orthogonal_8x8_cuda(int16_t *y, int ystride, int16_t *in, int16_t *x,
+ int xstride, int threshold, int dir);
+void od_tdlt_dering_vtbl_init_cuda(od_tdlt_dering_direction_func direction[],
+ od_tdlt_dering_orthogonal_func orthogonal[]);
 /* Many blocks in one launch: nblocks blocks of (4<<bs)^2, block i at x + i*xblock
    (resp. y + i*yblock); the useful form of the above for parity sweeps. */
 int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,

@@ -408,6 +408,38 @@ def test_smooth_frames_match_checker(pic_w, pic_h, q, decs):
     chk.close()
 
 
+@pytest.mark.parametrize("bsi", [0, 1])
+def test_dering_block_filters(bsi):
+    """The deringing filters with the reference's dispatch-table signatures, one block, all
+    eight directions, installed through od_tdlt_dering_vtbl_init_cuda."""
+    import ctypes as C
+    import daala_b200
+    L, port = daala_b200.lib(), ol.port()
+    DIRF = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int)
+    ORTF = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int)
+    dtab, otab = (DIRF * 2)(), (ORTF * 2)()
+    L.od_tdlt_dering_vtbl_init_cuda.argtypes = [C.c_void_p, C.c_void_p]
+    L.od_tdlt_dering_vtbl_init_cuda.restype = None
+    L.od_tdlt_dering_vtbl_init_cuda(dtab, otab)
+    rng = np.random.default_rng(1800 + bsi)
+    n, P = 4 << bsi, 38
+    for trial in range(24):
+        d = trial % 8
+        thr = int(rng.choice([0, 1, 7, 40, 300, 2000]))
+        buf = rng.integers(-400, 400, size=(n + 6, P)).astype(np.int16) * int(rng.choice([1, 3, 6]))
+        if trial % 5 == 0:
+            buf[:, :4] = 30000
+        org = rng.integers(-3000, 3000, size=(n, n + 2)).astype(np.int16)
+        inp = buf.ctypes.data + 2 * (3 * P + 3)
+        y1, y2 = np.full((n, n + 1), 5, np.int16), np.full((n, n + 1), 5, np.int16)
+        w1, w2 = y1.copy(), y2.copy()
+        dtab[bsi](y1.ctypes.data, n + 1, inp, thr, d)
+        otab[bsi](y2.ctypes.data, n + 1, inp, org.ctypes.data, n + 2, thr, d)
+        port.oc_dering_direction(ol.ptr(w1), n + 1, C.c_void_p(inp), 2 + bsi, thr, d)
+        port.oc_dering_orthogonal(ol.ptr(w2), n + 1, C.c_void_p(inp), ol.ptr(org), n + 2, 2 + bsi, thr, d)
+        assert np.array_equal(y1, w1) and np.array_equal(y2, w2)
+
+
 def test_full_size_properties():
     """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
     size, where the CPU checker is too slow to be run on every frame: (1) the round
