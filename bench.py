@@ -367,9 +367,10 @@ def main():
         # Two host threads, one context each (contexts are
         # independent), each running whole steps on its own batch, started half a step
         # apart: the forward call is download-heavy (pixels up, od_coeff down), the inverse
-        # call upload-heavy.  Measured on this pool: 4.3 -> 4.9 Gpixel/s from one to two
-        # threads and no more from three or from forcing strict alternation -- the two
-        # directions together stop at ~70 GB/s, close to what one direction does alone.
+        # call upload-heavy.  Measured on this pool: 4.3 -> 5.1 Gpixel/s from one to two
+        # threads, 5.3 / 5.4 with three / four (each thread pins another 4 GB of host
+        # memory, so two stays the default) -- the two directions together stop at about
+        # 80 GB/s, not far above what one direction does alone.
         nthr = max(1, args.e2e_threads)
         hp = [torch.empty(t.shape, dtype=torch.uint8, pin_memory=True) for t in c]
         for a_, b_ in zip(hp, c):
