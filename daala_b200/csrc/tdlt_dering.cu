@@ -371,8 +371,8 @@ void launch_dering(const DeringParams &P, int nframes, cudaStream_t st) {
 // by od_smooth_recursive with min_bs = 32x32 from src/decode.c:1134-1146): every superblock
 // coded as ONE 32x32 block is pulled towards the bilinear interpolation of its four
 // corners, by a weight that falls with the distortion this causes relative to the
-// quantization noise.  In place; one CTA per superblock and frame, all planes; a warp takes
-// whole rows (the distortion is truncated per row before it is summed).
+// quantization noise.  In place; one CTA per superblock, frame and plane; a warp takes whole
+// rows (the distortion is truncated per row before it is summed).
 // ---------------------------------------------------------------------------
 namespace tdlt {
 
@@ -425,26 +425,55 @@ __device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli, int 
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P) {
+__global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P, int nunits) {
   __shared__ int s_part[8];
+  __shared__ int s_list[kThreads];
+  __shared__ int s_count;
+  // Work unit = (superblock, frame, plane).  Most superblocks are split and have nothing to
+  // do, so a fixed-size grid walks the units 128 at a time: every thread looks one unit's map
+  // entry up (the loads of a chunk are in flight together), the units that are one 32x32
+  // block are collected in shared memory, then the CTA smooths them one after the other.
+  const int t = threadIdx.x;
   const int per = P.nhsb*P.nvsb;
-  const int frame = blockIdx.x/per;
-  const int sb = blockIdx.x - frame*per;
-  const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
-  // the superblock is one 32x32 block when its first map entry says so
-  if (P.bsize[(long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx] != 3) return;
-  for (int p = 0; p < P.nplanes; p++) {
-    const int dec = P.dec[p];
-    const int n = kSB >> dec;
-    const int w = (P.nhsb*kSB) >> dec;
-    int *x = P.c[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
-    if (dec == 0) smooth_block<0>(x, w, P.q[p], p, s_part);
-    else smooth_block<1>(x, w, P.q[p], p, s_part);
+  for (int base = blockIdx.x*kThreads; base < nunits; base += gridDim.x*kThreads) {
+    if (t == 0) s_count = 0;
+    __syncthreads();
+    const int unit = base + t;
+    if (unit < nunits) {
+      const int fs = unit/P.nplanes;
+      const int frame = fs/per;
+      const int sb = fs - frame*per;
+      const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
+      // the superblock is one 32x32 block when its first map entry says so
+      if (__ldg(P.bsize + (long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx) == 3) {
+        s_list[atomicAdd(&s_count, 1)] = unit;
+      }
+    }
+    __syncthreads();
+    const int count = s_count;
+    for (int k = 0; k < count; k++) {
+      const int u = s_list[k];
+      const int p = u % P.nplanes;
+      const int fs = u/P.nplanes;
+      const int frame = fs/per;
+      const int sb = fs - frame*per;
+      const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
+      const int dec = P.dec[p];
+      const int n = kSB >> dec;
+      const int w = (P.nhsb*kSB) >> dec;
+      int *x = P.c[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
+      if (dec == 0) smooth_block<0>(x, w, P.q[p], p, s_part);
+      else smooth_block<1>(x, w, P.q[p], p, s_part);
+    }
+    __syncthreads();                                    // s_list, s_count free for the next chunk
   }
 }
 
 void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st) {
-  smooth_kernel<<<(unsigned)(P.nhsb*P.nvsb*nframes), kThreads, 0, st>>>(P);
+  const long long nunits = (long long)P.nhsb*P.nvsb*nframes*P.nplanes;
+  const long long chunks = (nunits + kThreads - 1)/kThreads;
+  const int grid = (int)(chunks < 148*16 ? chunks : 148*16);    // up to 16 CTAs of 128 threads per SM
+  smooth_kernel<<<grid, kThreads, 0, st>>>(P, (int)nunits);
 }
 
 }  // namespace tdlt
