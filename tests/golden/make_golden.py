@@ -225,6 +225,20 @@ def main():
         tag = "pix_%d_%d_%d" % (mode, lossless, xs)
         G[tag + "_src"], G[tag + "_coeff"], G[tag + "_co"], G[tag + "_buf"] = src, a, co, pb
 
+    # ---- the reference's scan tables (OD_ZIGZAG4/8/16/32, src/zigzag*.c): inputs of the
+    # coding-order calls, which take them from the caller; stored so that the GPU box, where
+    # the reference may be absent, can still drive those calls with the real tables
+    for k, t in enumerate(ol.scan_tables()):
+        G["scan_table_%d" % (4 << k)] = t
+    rng_d = np.ascontiguousarray(lcg_ints(99, 32 * 32, -30000, 30000).reshape(32, 32))
+    for bs in range(4):
+        n = 4 << bs
+        v = np.zeros(n * n, np.int32)
+        R.od_raster_to_coding_order.restype = None
+        R.od_raster_to_coding_order(ptr(v), n, ptr(rng_d), 32)
+        G["scan_block_%d" % n] = v
+    G["scan_block_src"] = rng_d
+
     np.savez_compressed(OUT, **G)
     print("wrote %s: %d arrays, %d bytes" % (OUT, len(G), os.path.getsize(OUT)))
 

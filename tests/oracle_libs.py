@@ -247,6 +247,45 @@ def ref_smooth_frame(planes, decs, bsize, q):
     return out
 
 
+SCAN_TABLE_LEN = (15, 48, 192, 768)      # entries of OD_ZIGZAG4/8/16/32
+# how many of them the layouts order: OD_LAYOUT*.band_offsets[nb_bands] (src/partition.c:43-73);
+# the 32x32 layout stops after two bands of 128
+SCAN_LEN = (15, 48, 192, 256)
+
+
+def scan_tables():
+    """The reference's scan tables OD_ZIGZAG4/8/16/32 (src/zigzag*.c) as four (len, 2) uint8 arrays
+    of (x, y): read from the compiled reference when it is here, else from the golden fixture
+    tests/golden/make_golden.py took from it."""
+    if have_ref():
+        lib = ref()
+        return [np.ctypeslib.as_array((C.c_ubyte * (2 * n)).in_dll(lib, "OD_ZIGZAG%d" % (4 << k))).reshape(n, 2).copy()
+                for k, n in enumerate(SCAN_TABLE_LEN)]
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tdlt_golden.npz"))
+    return [G["scan_table_%d" % (4 << k)] for k in range(4)]
+
+
+def _scan_arg(tables):
+    tables = [np.ascontiguousarray(t, dtype=np.uint8) for t in tables]
+    return tables, (C.c_void_p * 4)(*[t.ctypes.data for t in tables]), (C.c_int * 4)(*SCAN_LEN)
+
+
+def port_coding_order_plane(src, bsize, dec, tables, to_coding=True, out=None):
+    """to_coding: raster plane d -> block-linear plane v of every block's coding-order vector;
+    else the inverse.  Entries the scans do not cover (half of every 32x32 block) keep what `out`
+    held (zeros when it is not given).  Returns the produced plane."""
+    lib = port()
+    src = np.ascontiguousarray(src, dtype=np.int32).copy()
+    out = np.zeros_like(src) if out is None else out
+    H, W = src.shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    keep, sa, la = _scan_arg(tables)
+    v, d = (out, src) if to_coding else (src, out)
+    lib.oc_coding_order_plane(ptr(v), ptr(d), (W << dec) // 32, (H << dec) // 32, dec, ptr(bsize),
+                              bsize.shape[1], sa, la, 1 if to_coding else 0)
+    return out
+
+
 # ----------------------------------------------------------------- ref API --
 class RefCtx:
     """An instance of the reference encoder state for one picture size."""

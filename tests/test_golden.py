@@ -119,6 +119,17 @@ def test_port_cfl_pred_plane(G):
     assert np.array_equal(ol.port_cfl_pred_plane(G["plane_0_dq"], G["plane_bsize"]), G["plane_cfl"])
 
 
+def test_port_coding_order_blocks(G):
+    port = ol.port()
+    keep, sa, la = ol._scan_arg([G["scan_table_%d" % (4 << k)] for k in range(4)])
+    src = np.ascontiguousarray(G["scan_block_src"])
+    for bs in range(4):
+        n = 4 << bs
+        v = np.zeros(n * n, np.int32)
+        port.oc_raster_to_coding_order(ol.ptr(v), n, ol.ptr(src), 32, sa, la)
+        assert np.array_equal(v, G["scan_block_%d" % n])
+
+
 def test_port_cif_keyframe(G):
     """BASELINE config 1: CIF keyframe with the block sizes the reference encoder's
     RDO chose; the coefficient planes are pinned by SHA-256."""

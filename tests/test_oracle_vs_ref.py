@@ -393,3 +393,70 @@ def test_smooth_frame_matches_reference(reflib, w, h, q):
             assert np.array_equal(a[p], b[p]), "plane %d" % p
         if (bsize[::4, ::4] == 3).any() and trial == 0 and q >= 200:   # smooth block, coarse quantizer
             assert any(np.count_nonzero(a[p] != planes[p]) for p in range(3))
+
+
+@pytest.mark.parametrize("bs", [0, 1, 2, 3])
+def test_coding_order_block_matches_reference(reflib, bs):
+    """od_raster_to_coding_order / od_coding_order_to_raster (src/partition.c:143-199), the
+    restatement driven by the reference's own scan tables."""
+    rng = np.random.default_rng(1900 + bs)
+    port = ol.port()
+    n = 4 << bs
+    keep, sa, la = ol._scan_arg(ol.scan_tables())
+    ncoded = min(n * n, 512)              # a 32x32 block has 512 coded coefficients
+    for f in (reflib.od_raster_to_coding_order, reflib.od_coding_order_to_raster):
+        f.restype = None
+    for trial in range(3):
+        src = rng.integers(-30000, 30000, size=(n, n + 3)).astype(np.int32)
+        a = np.zeros(n * n, np.int32)
+        b = np.zeros(n * n, np.int32)
+        reflib.od_raster_to_coding_order(ptr(a), n, ptr(src), n + 3)
+        port.oc_raster_to_coding_order(ptr(b), n, ptr(src), n + 3, sa, la)
+        assert np.array_equal(a, b)
+        assert not a[ncoded:].any()                                          # left alone
+        if n < 32:
+            assert sorted(a.tolist()) == sorted(src[:, :n].ravel().tolist())     # a permutation
+        ra = np.full((n, n + 2), 9, np.int32)
+        rb = ra.copy()
+        reflib.od_coding_order_to_raster(ptr(ra), n + 2, ptr(a), n)
+        port.oc_coding_order_to_raster(ptr(rb), n + 2, ptr(a), n, sa, la)
+        assert np.array_equal(ra, rb)
+        assert np.all(ra[:, n:] == 9)
+        covered = ra[:, :n] != 9
+        assert np.count_nonzero(covered) >= ncoded - 3 and np.array_equal(ra[:, :n][covered], src[:, :n][covered])
+
+
+@pytest.mark.parametrize("dec", [0, 1])
+def test_coding_order_plane_round_trip_and_layout(reflib, dec):
+    """The whole-plane driver: every block's vector equals the reference's for that block, at the
+    block-linear position; the way back restores the plane."""
+    rng = np.random.default_rng(1950 + dec)
+    tables = ol.scan_tables()
+    port = ol.port()
+    port.oc_block_linear_offset.restype = C.c_longlong
+    nhsb, nvsb = 3, 2
+    bsize = ol.random_quadtree_bsize(nhsb, nvsb, rng)
+    H, W = (nvsb * 32) >> dec, (nhsb * 32) >> dec
+    d = rng.integers(-30000, 30000, size=(H, W)).astype(np.int32)
+    v = ol.port_coding_order_plane(d, bsize, dec, tables, True)
+    back = ol.port_coding_order_plane(v, bsize, dec, tables, False, out=np.full_like(d, 123456))
+    covered = back != 123456
+    assert np.array_equal(back[covered], d[covered])
+    # everything is covered except the uncoded half of the 32x32 blocks (16x16 with 4:2:0: all coded)
+    n32 = int(np.count_nonzero(bsize[::4, ::4] == 3)) if dec == 0 else 0
+    assert np.count_nonzero(~covered) == 512 * n32
+    reflib.od_raster_to_coding_order.restype = None
+    flat = v.ravel()
+    for uy in range(nvsb * 4):
+        for ux in range(nhsb * 4):
+            obs = int(bsize[uy, ux])
+            lu = max(obs - 1, 0)
+            if (ux & ((1 << lu) - 1)) or (uy & ((1 << lu) - 1)):
+                continue
+            n = max(4, (4 << obs) >> dec)
+            x0, y0 = (ux * 8) >> dec, (uy * 8) >> dec
+            want = np.zeros(n * n, np.int32)
+            blk = np.ascontiguousarray(d[y0:y0 + n, x0:x0 + n])
+            reflib.od_raster_to_coding_order(ptr(want), n, ptr(blk), n)
+            off = port.oc_block_linear_offset(x0, y0, W, 32 >> dec)
+            assert np.array_equal(flat[off:off + n * n], want)
