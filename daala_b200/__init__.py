@@ -66,6 +66,9 @@ def lib():
         L.od_tdlt_dering_frames.argtypes = [vp, arr, arr, vp, arr, C.POINTER(ci), ci]
         L.od_tdlt_smooth_batch.argtypes = [vp, arr, vp, C.POINTER(ci), ci, vp]
         L.od_tdlt_smooth_frames.argtypes = [vp, arr, vp, C.POINTER(ci), ci]
+        L.od_tdlt_set_scan_tables.argtypes = [vp, arr, C.POINTER(ci)]
+        L.od_tdlt_coding_order_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
+        L.od_tdlt_coding_order_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_fwd_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_inv_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         iarr, larr = C.POINTER(ci), C.POINTER(ll)
@@ -180,6 +183,17 @@ class TdltContext:
         self._check(self.L.od_tdlt_smooth_batch(self._h, _ptr_array(c_ptrs), bsize_ptr, qa, nframes,
                                                 stream), "od_tdlt_smooth_batch")
 
+    def set_scan_tables(self, tables, lens):
+        """tables: four contiguous uint8 numpy arrays of (x, y) pairs (the reference's
+        OD_ZIGZAG4/8/16/32); lens: how many entries of each the reference's layouts order."""
+        self._check(self.L.od_tdlt_set_scan_tables(self._h, _ptr_array([t.ctypes.data for t in tables]),
+                                                   (C.c_int * 4)(*lens)), "od_tdlt_set_scan_tables")
+
+    def coding_order_batch(self, v_ptrs, d_ptrs, bsize_ptr, nframes, to_coding=True, stream=0):
+        self._check(self.L.od_tdlt_coding_order_batch(self._h, _ptr_array(v_ptrs), _ptr_array(d_ptrs),
+                                                      bsize_ptr, nframes, 1 if to_coding else 0, stream),
+                    "od_tdlt_coding_order_batch")
+
     def pix_to_coeff_batch(self, c_ptr, pix_ptr, pli, nframes, xstride=1, bitdepth_mode=1,
                            lossless=0, stream=0):
         self._check(self.L.od_tdlt_pix_to_coeff_batch(self._h, c_ptr, pix_ptr, pli, nframes, xstride,
@@ -228,6 +242,13 @@ class TdltContext:
         self._check(self.L.od_tdlt_smooth_frames(
             self._h, _ptr_array([a.ctypes.data for a in c_planes]), bsize.ctypes.data, qa,
             bsize.shape[0]), "od_tdlt_smooth_frames")
+
+    def coding_order_frames(self, v_planes, d_planes, bsize, to_coding=True):
+        """Host arrays: to_coding fills v_planes from d_planes, else the other way round."""
+        self._check(self.L.od_tdlt_coding_order_frames(
+            self._h, _ptr_array([a.ctypes.data for a in v_planes]),
+            _ptr_array([a.ctypes.data for a in d_planes]), bsize.ctypes.data, bsize.shape[0],
+            1 if to_coding else 0), "od_tdlt_coding_order_frames")
 
     def _pix_args(self, pix_planes, xstride):
         ys = (C.c_int * NPLANES_MAX)()

@@ -54,6 +54,19 @@ struct SmoothParams {
 };
 void launch_smooth(const SmoothParams &P, int nframes, cudaStream_t st);
 
+// Raster <-> coding order of every transform block (tdlt_dering.cu).
+struct CodingParams {
+  int *v[4];                       // block-linear planes of coding-order vectors
+  int *d[4];                       // raster coefficient planes
+  const unsigned char *bsize;
+  const unsigned char *scan;       // device copy of the four scan tables, (x, y) byte pairs
+  long long plane_size[4];
+  int scan_len[4];
+  int dec[4];
+  int nplanes, nhsb, nvsb, to_coding;
+};
+void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st);
+
 // One block (n = 4 or 8) through one of the two deringing filters; `in` dense with its
 // 3-sample ring (pitch n + 6), x: the unfiltered block (orthogonal filter only).
 void launch_dering_block(short *y, const short *in, const short *x, int n, int thr, int dir,

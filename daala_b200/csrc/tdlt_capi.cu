@@ -50,6 +50,8 @@ struct od_tdlt_ctx {
   void *dev_pix[kMaxPlanes];
   unsigned char *dev_bsize;
   unsigned char *dev_aux;       // od_tdlt_dering_frames: superblock flags + skip maps
+  unsigned char *dev_scan;      // the caller's scan tables (od_tdlt_set_scan_tables)
+  int scan_len[4];
   size_t dev_aux_bytes;
   cudaStream_t stream;          // kernels
   cudaStream_t s_in, s_out;     // uploads / downloads of the host-pointer calls
@@ -291,6 +293,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   }
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->dev_aux);
+  cudaFree(ctx->dev_scan);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
   cudaFree(ctx->order);
@@ -577,6 +580,68 @@ int od_tdlt_smooth_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned c
   return OD_TDLT_SUCCESS;
 }
 
+// Raster <-> coding order (reference src/partition.c:95-200).  The scan tables are the
+// caller's: OD_ZIGZAG4/8/16/32 as they lie in the reference (src/zigzag*.c; 15, 48, 192 and
+// 768 (x, y) byte pairs) and how many entries of each its layouts order
+// (OD_LAYOUT*.band_offsets[nb_bands], src/partition.c:43-73: 15, 48, 192, 256).
+int od_tdlt_set_scan_tables(od_tdlt_ctx *ctx, const unsigned char *const tables[4],
+                            const int lens[4]) {
+  static const int kTableLen[4] = {15, 48, 192, 768};
+  if (!ctx || !tables || !lens) return OD_TDLT_EFAULT;
+  unsigned char host[2*(15 + 48 + 192 + 768)];
+  int off = 0;
+  for (int k = 0; k < 4; k++) {
+    if (!tables[k]) return OD_TDLT_EFAULT;
+    if (lens[k] < 0 || lens[k] > kTableLen[k]) {
+      return fail(ctx, OD_TDLT_EINVAL, "scan length %d of table %d", lens[k], k);
+    }
+    for (int i = 0; i < lens[k]; i++) {
+      if (tables[k][2*i] >= (4 << k) || tables[k][2*i + 1] >= (4 << k)) {
+        return fail(ctx, OD_TDLT_EINVAL, "scan table %d, entry %d outside the block", k, i);
+      }
+    }
+    memcpy(host + off, tables[k], 2*kTableLen[k]);
+    off += 2*kTableLen[k];
+  }
+  CK(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->dev_scan) CK(ctx, cudaMalloc(&ctx->dev_scan, sizeof(host)));
+  CK(ctx, cudaMemcpy(ctx->dev_scan, host, sizeof(host), cudaMemcpyHostToDevice));
+  for (int k = 0; k < 4; k++) ctx->scan_len[k] = lens[k];
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *const d[],
+                               const unsigned char *bsize, int nframes, int to_coding,
+                               void *stream) {
+  if (!ctx || !v || !d || !bsize) return OD_TDLT_EFAULT;
+  if (!ctx->dev_scan) return fail(ctx, OD_TDLT_EINVAL, "od_tdlt_set_scan_tables has not been called");
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
+  CodingParams P = {};
+  P.nplanes = ctx->g.nplanes;
+  for (int p = 0; p < P.nplanes; p++) {
+    if (!v[p] || !d[p]) return OD_TDLT_EFAULT;
+    if (v[p] == d[p]) return fail(ctx, OD_TDLT_EINVAL, "coding order is out of place (plane %d)", p);
+    if (ctx->g.xdec[p] != ctx->g.ydec[p] || ctx->g.xdec[p] > 1) {
+      return fail(ctx, OD_TDLT_EINVAL, "coding order needs 4:4:4 or 4:2:0 planes");
+    }
+    P.v[p] = v[p];
+    P.d[p] = d[p];
+    P.plane_size[p] = ctx->plane_size[p];
+    P.dec[p] = ctx->g.xdec[p];
+  }
+  for (int k = 0; k < 4; k++) P.scan_len[k] = ctx->scan_len[k];
+  P.bsize = bsize;
+  P.scan = ctx->dev_scan;
+  P.nhsb = ctx->nhsb;
+  P.nvsb = ctx->nvsb;
+  P.to_coding = to_coding != 0;
+  CK(ctx, cudaSetDevice(ctx->device));
+  launch_coding_order(P, nframes, (cudaStream_t)stream);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------- whole-frame host calls --
@@ -806,6 +871,34 @@ int od_tdlt_smooth_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned 
   if (rc) return rc;
   for (int p = 0; p < np; p++) {
     CK(ctx, cudaMemcpyAsync(c[p], ctx->dev_c[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff),
+                            cudaMemcpyDeviceToHost, st));
+  }
+  CK(ctx, cudaStreamSynchronize(st));
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_coding_order_frames(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *const d[],
+                                const unsigned char *bsize, int nframes, int to_coding) {
+  if (!ctx || !v || !d || !bsize) return OD_TDLT_EFAULT;
+  int rc = check_frames(ctx, nframes);
+  if (rc) return rc;
+  CK(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int np = ctx->g.nplanes;
+  // both sides go up: entries the scans do not cover keep what the destination held
+  for (int p = 0; p < np; p++) {
+    if (!v[p] || !d[p]) return OD_TDLT_EFAULT;
+    const size_t bytes = (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff);
+    CK(ctx, cudaMemcpyAsync(ctx->dev_c[p], v[p], bytes, cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemcpyAsync(ctx->dev_d[p], d[p], bytes, cudaMemcpyHostToDevice, st));
+  }
+  CK(ctx, cudaMemcpyAsync(ctx->dev_bsize, bsize, (size_t)od_tdlt_bsize_size(ctx)*nframes,
+                          cudaMemcpyHostToDevice, st));
+  rc = od_tdlt_coding_order_batch(ctx, ctx->dev_c, ctx->dev_d, ctx->dev_bsize, nframes, to_coding, st);
+  if (rc) return rc;
+  for (int p = 0; p < np; p++) {
+    const size_t bytes = (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff);
+    CK(ctx, cudaMemcpyAsync(to_coding ? v[p] : d[p], to_coding ? ctx->dev_c[p] : ctx->dev_d[p], bytes,
                             cudaMemcpyDeviceToHost, st));
   }
   CK(ctx, cudaStreamSynchronize(st));

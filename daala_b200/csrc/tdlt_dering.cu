@@ -520,3 +520,78 @@ void launch_dering_block(short *y, const short *in, const short *x, int n, int t
 }
 
 }  // namespace tdlt
+
+// ---------------------------------------------------------------------------
+// Raster <-> coding order (reference od_raster_to_coding_order /
+// od_coding_order_to_raster, src/partition.c:95-200): every transform block's coefficients
+// permuted into the order the PVQ coder takes them in.  The scan tables are data of the
+// caller (od_tdlt_set_scan_tables); the vectors go to a block-linear plane: superblocks in
+// raster order, inside a superblock the 4x4-sample units in Z order, 16 entries per unit, so
+// that a quadtree-aligned n x n block owns n*n consecutive entries.  One thread per entry of
+// that plane: to_coding gathers (coalesced writes), the way back scatters (coalesced reads).
+// Entries the scans do not cover (the upper half of a 32x32 block's vector) are left alone,
+// as the reference leaves them.  A fixed grid walks the superblocks; the tables sit in
+// shared memory.
+// ---------------------------------------------------------------------------
+namespace tdlt {
+
+namespace {
+constexpr int kScanEntries = 15 + 48 + 192 + 768;
+constexpr int kCoThreads = 256;
+}  // namespace
+
+__global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P, int nunits) {
+  __shared__ unsigned short s_scan[kScanEntries];       // (x, y) byte pairs
+  for (int i = threadIdx.x; i < kScanEntries; i += kCoThreads) {
+    s_scan[i] = reinterpret_cast<const unsigned short *>(P.scan)[i];
+  }
+  __syncthreads();
+  const int per = P.nhsb*P.nvsb;
+  for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+    const int frame = unit/per;
+    const int sb = unit - frame*per;
+    const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
+    const unsigned char *map = P.bsize + (long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx;
+    for (int p = 0; p < P.nplanes; p++) {
+      const int dec = P.dec[p];
+      const int S = kSB >> dec;
+      const int w = (P.nhsb*kSB) >> dec;
+      const long long fo = frame*P.plane_size[p];
+      int *v = P.v[p] + fo + (long long)sb*S*S;
+      int *d = P.d[p] + fo + (long long)(sby*S)*w + sbx*S;
+      for (int e = threadIdx.x; e < S*S; e += kCoThreads) {
+        const int z = e >> 4;
+        // Z order -> unit coordinates (4x4 samples of this plane)
+        const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
+        const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
+        const int obs = map[((uy << dec) >> 1)*(4*P.nhsb) + ((ux << dec) >> 1)];
+        const int ln4 = max(obs - dec, 0);              // log2 of the block side in units
+        const int zb = z & ~((1 << 2*ln4) - 1);         // the block's first unit in Z order
+        const int i = ((z - zb) << 4) | (e & 15);       // index in the block's vector
+        int x = 0, y = 0;
+        if (i) {
+          const int k = i < 16 ? 0 : i < 64 ? 1 : i < 256 ? 2 : 3;
+          const int first = k == 0 ? 1 : 4 << 2*k;       // 1, 16, 64, 256
+          const int j = i - first;
+          if (j >= P.scan_len[k]) continue;               // not ordered by the codec
+          const int toff = k == 0 ? 0 : k == 1 ? 15 : k == 2 ? 63 : 255;
+          const unsigned short xy = s_scan[toff + j];
+          x = xy & 255;
+          y = xy >> 8;
+        }
+        const int bx = (ux & ~((1 << ln4) - 1)) << 2, by = (uy & ~((1 << ln4) - 1)) << 2;
+        int *q = d + (long long)(by + y)*w + bx + x;
+        if (P.to_coding) v[e] = *q;
+        else *q = v[e];
+      }
+    }
+  }
+}
+
+void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st) {
+  const long long nunits = (long long)P.nhsb*P.nvsb*nframes;
+  const int grid = (int)(nunits < 148*8 ? nunits : 148*8);
+  coding_order_kernel<<<grid, kCoThreads, 0, st>>>(P, (int)nunits);
+}
+
+}  // namespace tdlt

@@ -151,6 +151,29 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
 int od_tdlt_smooth_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
  const int q[], int nframes, void *stream);
 
+/* Raster <-> coding order of every transform block (reference od_raster_to_coding_order /
+   od_coding_order_to_raster, src/partition.c:143-199; call sites src/encode.c:1160-1161,
+   1219-1220, src/decode.c:580-581, 630): the permutation the PVQ coder wants next.
+   The scan tables are data of the reference and are handed over by the caller once per
+   context: tables[k] = OD_ZIGZAG4/8/16/32 ((x, y) byte pairs: 15, 48, 192, 768 of them,
+   src/zigzag*.c), lens[k] = how many entries layout k orders
+   (OD_LAYOUT*.band_offsets[nb_bands], src/partition.c:43-73: 15, 48, 192, 256). */
+int od_tdlt_set_scan_tables(od_tdlt_ctx *ctx, const unsigned char *const tables[4],
+ const int lens[4]);
+/* d[p]: raster coefficient planes (layout above).  v[p]: planes of the same size holding
+   every block's coding-order vector: superblocks (32x32 luma samples, 16x16 with 4:2:0) in
+   raster order, inside a superblock the 4x4-sample units in Z order (x bit 0, y bit 0,
+   x bit 1, ...), 16 entries per unit -- a quadtree-aligned n x n block at plane position
+   (x0, y0) owns the n*n consecutive entries starting at
+     ((y0/S)*(w/S) + x0/S)*S*S + 16*zorder((x0%S)/4, (y0%S)/4),   S = 32 >> dec.
+   to_coding != 0: v <- d (od_raster_to_coding_order per block); else d <- v.  Entries the
+   scans do not cover (a 32x32 block orders 512 of its 1024 coefficients) are left as they
+   were in the destination, as the reference leaves them.  Block sizes follow the map as in
+   the transform calls (4:2:0 chroma halves them, not below 4x4).  DEVICE pointers,
+   asynchronous on `stream`; v != d. */
+int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *const d[],
+ const unsigned char *bsize, int nframes, int to_coding, void *stream);
+
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
    out as above but in host memory (pinned or pageable).
@@ -169,6 +192,10 @@ int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coef
 /* Host-pointer form of od_tdlt_smooth_batch (synchronous, in place, nframes <= max_frames). */
 int od_tdlt_smooth_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned char *bsize,
  const int q[], int nframes);
+/* Host-pointer form of od_tdlt_coding_order_batch (synchronous, nframes <= max_frames; the
+   destination's previous contents are kept where the scans do not write). */
+int od_tdlt_coding_order_frames(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *const d[],
+ const unsigned char *bsize, int nframes, int to_coding);
 /* Same with the pixel conversion done on the device: the host ships 8/16-bit
    reference-buffer samples instead of od_coeff (od_ref_plane_to_coeff,
    src/state.c:1252; od_coeff_to_ref_plane, :1320).  pix[pli] points at the

@@ -440,6 +440,47 @@ def test_dering_block_filters(bsi):
         assert np.array_equal(y1, w1) and np.array_equal(y2, w2)
 
 
+@pytest.mark.parametrize("pic_w,pic_h,kind,decs", [
+    (352, 288, "quad", (0, 1, 1)), (200, 136, "deep", (0, 1, 1)), (64, 64, "uniform3", (0, 1, 1)),
+    (96, 64, "quad", (0, 0, 0)), (352, 288, "uniform0", (0, 1, 1)), (1920, 1080, "quad", (0, 1, 1))])
+def test_coding_order_frames_match_checker(pic_w, pic_h, kind, decs):
+    """Raster <-> coding order of every transform block with the reference's scan tables: the
+    block-linear vectors against the restatement (pinned block by block against the reference's
+    od_raster_to_coding_order on the CPU), the uncovered entries left alone, and the way back."""
+    rng = np.random.default_rng(pic_w * 3 + pic_h + sum(map(ord, kind)))
+    nframes = 2 if pic_w < 1000 else 1
+    tables = ol.scan_tables()
+    with _ctx(pic_w, pic_h, nframes, decs=decs) as ctx:
+        ctx.set_scan_tables(tables, ol.SCAN_LEN)
+        bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+        d = _rand_planes(ctx.plane_shapes, nframes, rng, -30000, 30000)
+        v = [np.full_like(a, 424242) for a in d]
+        ctx.coding_order_frames(v, d, bsize, True)
+        for p, dec in enumerate(decs):
+            for f in range(nframes):
+                want = ol.port_coding_order_plane(d[p][f], bsize[f], dec, tables, True,
+                                                  out=np.full_like(d[p][f], 424242))
+                assert np.array_equal(v[p][f], want), "to coding order, plane %d frame %d" % (p, f)
+        back = [np.full_like(a, -7) for a in d]
+        ctx.coding_order_frames(v, back, bsize, False)
+        for p, dec in enumerate(decs):
+            for f in range(nframes):
+                want = ol.port_coding_order_plane(v[p][f], bsize[f], dec, tables, False,
+                                                  out=np.full_like(d[p][f], -7))
+                assert np.array_equal(back[p][f], want), "to raster, plane %d frame %d" % (p, f)
+            covered = back[p] != -7
+            assert np.array_equal(back[p][covered], d[p][covered])
+
+
+def test_coding_order_needs_tables():
+    import daala_b200
+    with _ctx(64, 64, 1) as ctx:
+        a = [np.zeros((1,) + s, np.int32) for s in ctx.plane_shapes]
+        b = [np.zeros((1,) + s, np.int32) for s in ctx.plane_shapes]
+        with pytest.raises(daala_b200.TdltError):
+            ctx.coding_order_frames(a, b, np.zeros((1, 8, 8), np.uint8), True)
+
+
 def test_full_size_properties():
     """BASELINE config 4 shape (4K 4:2:0, 10-bit samples in 16-bit words) at full
     size, where the CPU checker is too slow to be run on every frame: (1) the round
