@@ -540,6 +540,55 @@ constexpr int kScanEntries = 15 + 48 + 192 + 768;
 constexpr int kCoThreads = 256;
 }  // namespace
 
+// One plane of one superblock: S*S entries, S*S/256 per thread, all of a thread's loads in
+// flight before its first store.  (Staging the tile through shared memory so that every
+// global access is a coalesced vector was measured and is no faster: the kernel is bound by
+// the latency of one superblock after the other per CTA at four CTAs per SM, not by the
+// sector count of the gathers.)
+template <int DEC>
+__device__ __forceinline__ void coding_order_sb(const CodingParams &P, const unsigned short *s_scan,
+                                                const unsigned char *map, int *v, int *d, int w) {
+  constexpr int S = kSB >> DEC;
+  constexpr int iters = S*S/kCoThreads;
+  int *q[iters];
+  int val[iters];
+#pragma unroll
+  for (int it = 0; it < iters; it++) {
+    const int e = threadIdx.x + it*kCoThreads;
+    const int z = e >> 4;
+    // Z order -> unit coordinates (4x4 samples of this plane)
+    const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
+    const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
+    const int obs = __ldg(map + ((uy << DEC) >> 1)*(4*P.nhsb) + ((ux << DEC) >> 1));
+    const int ln4 = max(obs - DEC, 0);                  // log2 of the block side in units
+    const int zb = z & ~((1 << 2*ln4) - 1);             // the block's first unit in Z order
+    const int i = ((z - zb) << 4) | (e & 15);           // index in the block's vector
+    int x = 0, y = 0;
+    bool ordered = true;
+    if (i) {
+      const int k = i < 16 ? 0 : i < 64 ? 1 : i < 256 ? 2 : 3;
+      const int first = k == 0 ? 1 : 4 << 2*k;           // 1, 16, 64, 256
+      const int j = i - first;
+      ordered = j < P.scan_len[k];                        // else: not ordered by the codec
+      const int toff = k == 0 ? 0 : k == 1 ? 15 : k == 2 ? 63 : 255;
+      const unsigned short xy = s_scan[toff + (ordered ? j : 0)];
+      x = xy & 255;
+      y = xy >> 8;
+    }
+    const int bx = (ux & ~((1 << ln4) - 1)) << 2, by = (uy & ~((1 << ln4) - 1)) << 2;
+    q[it] = ordered ? d + (long long)(by + y)*w + bx + x : nullptr;
+    if (P.to_coding) val[it] = ordered ? *q[it] : 0;
+    else val[it] = v[e];
+  }
+#pragma unroll
+  for (int it = 0; it < iters; it++) {
+    const int e = threadIdx.x + it*kCoThreads;
+    if (!q[it]) continue;                               // left alone, as the reference leaves it
+    if (P.to_coding) v[e] = val[it];
+    else *q[it] = val[it];
+  }
+}
+
 __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P, int nunits) {
   __shared__ unsigned short s_scan[kScanEntries];       // (x, y) byte pairs
   for (int i = threadIdx.x; i < kScanEntries; i += kCoThreads) {
@@ -559,38 +608,16 @@ __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P
       const long long fo = frame*P.plane_size[p];
       int *v = P.v[p] + fo + (long long)sb*S*S;
       int *d = P.d[p] + fo + (long long)(sby*S)*w + sbx*S;
-      for (int e = threadIdx.x; e < S*S; e += kCoThreads) {
-        const int z = e >> 4;
-        // Z order -> unit coordinates (4x4 samples of this plane)
-        const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
-        const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
-        const int obs = map[((uy << dec) >> 1)*(4*P.nhsb) + ((ux << dec) >> 1)];
-        const int ln4 = max(obs - dec, 0);              // log2 of the block side in units
-        const int zb = z & ~((1 << 2*ln4) - 1);         // the block's first unit in Z order
-        const int i = ((z - zb) << 4) | (e & 15);       // index in the block's vector
-        int x = 0, y = 0;
-        if (i) {
-          const int k = i < 16 ? 0 : i < 64 ? 1 : i < 256 ? 2 : 3;
-          const int first = k == 0 ? 1 : 4 << 2*k;       // 1, 16, 64, 256
-          const int j = i - first;
-          if (j >= P.scan_len[k]) continue;               // not ordered by the codec
-          const int toff = k == 0 ? 0 : k == 1 ? 15 : k == 2 ? 63 : 255;
-          const unsigned short xy = s_scan[toff + j];
-          x = xy & 255;
-          y = xy >> 8;
-        }
-        const int bx = (ux & ~((1 << ln4) - 1)) << 2, by = (uy & ~((1 << ln4) - 1)) << 2;
-        int *q = d + (long long)(by + y)*w + bx + x;
-        if (P.to_coding) v[e] = *q;
-        else *q = v[e];
-      }
+      if (dec == 0) coding_order_sb<0>(P, s_scan, map, v, d, w);
+      else coding_order_sb<1>(P, s_scan, map, v, d, w);
     }
   }
 }
 
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st) {
   const long long nunits = (long long)P.nhsb*P.nvsb*nframes;
-  const int grid = (int)(nunits < 148*8 ? nunits : 148*8);
+  const long long cap = 148ll*16;                       // a fixed grid walks the superblocks
+  const int grid = (int)(nunits < cap ? nunits : cap);
   coding_order_kernel<<<grid, kCoThreads, 0, st>>>(P, (int)nunits);
 }
 
