@@ -540,59 +540,94 @@ constexpr int kScanEntries = 15 + 48 + 192 + 768;
 constexpr int kCoThreads = 256;
 }  // namespace
 
-// One plane of one superblock: S*S entries, S*S/256 per thread, all of a thread's loads in
-// flight before its first store.  (Staging the tile through shared memory so that every
-// global access is a coalesced vector was measured and is no faster: the kernel is bound by
-// the latency of one superblock after the other per CTA at four CTAs per SM, not by the
-// sector count of the gathers.)
+// Where entry e of a superblock's block-linear range comes from when the block it lies in
+// has a side of 4 << ln4 samples: position inside the superblock (row*S + column), or kNoPos
+// when the codec does not order that entry.  Depends on nothing but (e, ln4) and the scan
+// tables, so every CTA tabulates it once in shared memory.
+constexpr unsigned short kNoPos = 0xffff;
 template <int DEC>
-__device__ __forceinline__ void coding_order_sb(const CodingParams &P, const unsigned short *s_scan,
+__device__ __forceinline__ unsigned short coding_source_pos(int e, int ln4, const unsigned short *s_scan,
+                                                            const int *scan_len) {
+  constexpr int S = kSB >> DEC;
+  const int z = e >> 4;
+  // Z order -> unit coordinates (4x4 samples of this plane)
+  const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
+  const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
+  const int zb = z & ~((1 << 2*ln4) - 1);               // the block's first unit in Z order
+  const int i = ((z - zb) << 4) | (e & 15);             // index in the block's vector
+  int x = 0, y = 0;
+  if (i) {
+    const int k = i < 16 ? 0 : i < 64 ? 1 : i < 256 ? 2 : 3;
+    const int first = k == 0 ? 1 : 4 << 2*k;             // 1, 16, 64, 256
+    const int j = i - first;
+    if (j >= scan_len[k]) return kNoPos;
+    const int toff = k == 0 ? 0 : k == 1 ? 15 : k == 2 ? 63 : 255;
+    const unsigned short xy = s_scan[toff + j];
+    x = xy & 255;
+    y = xy >> 8;
+  }
+  const int bx = (ux & ~((1 << ln4) - 1)) << 2, by = (uy & ~((1 << ln4) - 1)) << 2;
+  return (unsigned short)((by + y)*S + bx + x);
+}
+
+// One plane of one superblock: S*S entries, S*S/256 per thread, all of a thread's loads in
+// flight before its first store.  mo[]: this thread's map offsets (fixed per thread).
+template <int DEC>
+__device__ __forceinline__ void coding_order_sb(int to_coding, const unsigned short *tab, const int *mo,
                                                 const unsigned char *map, int *v, int *d, int w) {
   constexpr int S = kSB >> DEC;
+  constexpr int lS = 5 - DEC;
   constexpr int iters = S*S/kCoThreads;
-  int *q[iters];
+  int off[iters];
   int val[iters];
 #pragma unroll
   for (int it = 0; it < iters; it++) {
     const int e = threadIdx.x + it*kCoThreads;
-    const int z = e >> 4;
-    // Z order -> unit coordinates (4x4 samples of this plane)
-    const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
-    const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
-    const int obs = __ldg(map + ((uy << DEC) >> 1)*(4*P.nhsb) + ((ux << DEC) >> 1));
-    const int ln4 = max(obs - DEC, 0);                  // log2 of the block side in units
-    const int zb = z & ~((1 << 2*ln4) - 1);             // the block's first unit in Z order
-    const int i = ((z - zb) << 4) | (e & 15);           // index in the block's vector
-    int x = 0, y = 0;
-    bool ordered = true;
-    if (i) {
-      const int k = i < 16 ? 0 : i < 64 ? 1 : i < 256 ? 2 : 3;
-      const int first = k == 0 ? 1 : 4 << 2*k;           // 1, 16, 64, 256
-      const int j = i - first;
-      ordered = j < P.scan_len[k];                        // else: not ordered by the codec
-      const int toff = k == 0 ? 0 : k == 1 ? 15 : k == 2 ? 63 : 255;
-      const unsigned short xy = s_scan[toff + (ordered ? j : 0)];
-      x = xy & 255;
-      y = xy >> 8;
-    }
-    const int bx = (ux & ~((1 << ln4) - 1)) << 2, by = (uy & ~((1 << ln4) - 1)) << 2;
-    q[it] = ordered ? d + (long long)(by + y)*w + bx + x : nullptr;
-    if (P.to_coding) val[it] = ordered ? *q[it] : 0;
+    const int ln4 = max((int)__ldg(map + mo[it]) - DEC, 0);   // log2 of the block side in 4-sample units
+    const int pos = tab[ln4*S*S + e];
+    off[it] = pos == kNoPos ? -1 : (pos >> lS)*w + (pos & (S - 1));
+    if (to_coding) val[it] = off[it] >= 0 ? d[off[it]] : 0;
     else val[it] = v[e];
   }
 #pragma unroll
   for (int it = 0; it < iters; it++) {
     const int e = threadIdx.x + it*kCoThreads;
-    if (!q[it]) continue;                               // left alone, as the reference leaves it
-    if (P.to_coding) v[e] = val[it];
-    else *q[it] = val[it];
+    if (off[it] < 0) continue;                          // left alone, as the reference leaves it
+    if (to_coding) v[e] = val[it];
+    else d[off[it]] = val[it];
   }
 }
 
 __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P, int nunits) {
   __shared__ unsigned short s_scan[kScanEntries];       // (x, y) byte pairs
-  for (int i = threadIdx.x; i < kScanEntries; i += kCoThreads) {
+  __shared__ unsigned short s_tab0[4*kSB*kSB];          // planes at full size: block sides 4..32
+  __shared__ unsigned short s_tab1[3*(kSB/2)*(kSB/2)];  // 4:2:0 chroma: block sides 4..16
+  __shared__ int s_len[4];
+  const int t = threadIdx.x;
+  for (int i = t; i < kScanEntries; i += kCoThreads) {
     s_scan[i] = reinterpret_cast<const unsigned short *>(P.scan)[i];
+  }
+  if (t < 4) s_len[t] = P.scan_len[t];
+  __syncthreads();
+  for (int i = t; i < 4*kSB*kSB; i += kCoThreads) {
+    s_tab0[i] = coding_source_pos<0>(i & (kSB*kSB - 1), i >> 10, s_scan, s_len);
+  }
+  for (int i = t; i < 3*(kSB/2)*(kSB/2); i += kCoThreads) {
+    s_tab1[i] = coding_source_pos<1>(i & 255, i >> 8, s_scan, s_len);
+  }
+  // this thread's entries and the map entries they depend on, the same for every superblock
+  int mo0[kSB*kSB/kCoThreads], mo1[1];
+#pragma unroll
+  for (int it = 0; it < kSB*kSB/kCoThreads; it++) {
+    const int z = (t + it*kCoThreads) >> 4;
+    const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4);
+    const int uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
+    mo0[it] = (uy >> 1)*(4*P.nhsb) + (ux >> 1);
+  }
+  {
+    const int z = t >> 4;
+    const int ux = (z & 1) | ((z >> 1) & 2), uy = ((z >> 1) & 1) | ((z >> 2) & 2);
+    mo1[0] = uy*(4*P.nhsb) + ux;
   }
   __syncthreads();
   const int per = P.nhsb*P.nvsb;
@@ -608,8 +643,8 @@ __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P
       const long long fo = frame*P.plane_size[p];
       int *v = P.v[p] + fo + (long long)sb*S*S;
       int *d = P.d[p] + fo + (long long)(sby*S)*w + sbx*S;
-      if (dec == 0) coding_order_sb<0>(P, s_scan, map, v, d, w);
-      else coding_order_sb<1>(P, s_scan, map, v, d, w);
+      if (dec == 0) coding_order_sb<0>(P.to_coding, s_tab0, mo0, map, v, d, w);
+      else coding_order_sb<1>(P.to_coding, s_tab1, mo1, map, v, d, w);
     }
   }
 }
