@@ -64,6 +64,7 @@ struct CodingParams {
   int scan_len[4];
   int dec[4];
   int nplanes, nhsb, nvsb, to_coding;
+  unsigned recip_nhsb;             // ceil(2^32 / nhsb): row of a superblock by multiply-high
 };
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st);
 

@@ -635,6 +635,8 @@ int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *
   P.nhsb = ctx->nhsb;
   P.nvsb = ctx->nvsb;
   P.to_coding = to_coding != 0;
+  if ((long long)ctx->nhsb*ctx->nvsb >= 65536) return fail(ctx, OD_TDLT_EINVAL, "frame too large for the coding-order walk");
+  P.recip_nhsb = (unsigned)(((1ull << 32) + ctx->nhsb - 1)/ctx->nhsb);
   CK(ctx, cudaSetDevice(ctx->device));
   launch_coding_order(P, nframes, (cudaStream_t)stream);
   g_launches++;
