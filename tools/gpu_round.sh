@@ -23,6 +23,8 @@ timeout 300 python tools/bench_dering.py > $O/dering_4k_$TAG.json 2> $O/dering_4
 cat $O/dering_4k_$TAG.json
 timeout 300 python tools/bench_dering.py --no-cpu --flag-prob 1.0 --skip-prob 0 > $O/dering_4k_all_$TAG.json 2>> $O/dering_4k_$TAG.err
 cat $O/dering_4k_all_$TAG.json
+timeout 300 python tools/bench_coding.py > $O/coding_4k_$TAG.json 2> $O/coding_4k_$TAG.err; echo "coding rc=$?"
+cat $O/coding_4k_$TAG.json
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
 timeout 600 $CMD > $O/plain_$TAG.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
