@@ -82,6 +82,12 @@ __constant__ int kDirOff[8][3] = {
     {1*kPitch + 1, 2*kPitch + 2, 3*kPitch + 3}, {1*kPitch, 2*kPitch + 1, 3*kPitch + 1},
     {1*kPitch, 2*kPitch, 3*kPitch}, {1*kPitch, 2*kPitch - 1, 3*kPitch - 1}};
 
+// the same taps as (dy, dx) steps, for the block calls whose buffers have another pitch
+__constant__ signed char kDirStep[8][3][2] = {
+    {{-1, 1}, {-2, 2}, {-3, 3}}, {{0, 1}, {-1, 2}, {-1, 3}}, {{0, 1}, {0, 2}, {0, 3}},
+    {{0, 1}, {1, 2}, {1, 3}},    {{1, 1}, {2, 2}, {3, 3}},   {{1, 0}, {2, 1}, {3, 1}},
+    {{1, 0}, {2, 0}, {3, 0}},    {{1, 0}, {2, -1}, {3, -1}}};
+
 // p if |p| < thr, else 0, with one unsigned compare: |p| < thr  <=>  (unsigned)(p + thr - 1) <
 // 2*thr - 1; the bound is clamped at 0 so that a threshold of 0 accepts nothing.
 struct Gate { int c; unsigned lim; };
@@ -499,10 +505,7 @@ __global__ void dering_block_kernel(short *y, const short *in, const short *x, i
     int s[3];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-      // the table is in tile pitch: back to (dy, dx)
-      const int o = kDirOff[dir][k];
-      const int dy = (o + 3*kPitch + kPitch/2)/kPitch - 3, dx = o - dy*kPitch;
-      const int oo = dy*pitch + dx;
+      const int oo = kDirStep[dir][k][0]*pitch + kDirStep[dir][k][1];
       s[k] = tap(a[oo] - xx, g) + tap(a[-oo] - xx, g);
     }
     y[i*n + j] = (short)(xx + ((3*s[0] + 2*(s[1] + s[2]) + 8) >> 4));
