@@ -378,68 +378,67 @@ void launch_dering(const DeringParams &P, int nframes, cudaStream_t st) {
 // by od_smooth_recursive with min_bs = 32x32 from src/decode.c:1134-1146): every superblock
 // coded as ONE 32x32 block is pulled towards the bilinear interpolation of its four
 // corners, by a weight that falls with the distortion this causes relative to the
-// quantization noise.  In place; one CTA per superblock, frame and plane; a warp takes whole
-// rows (the distortion is truncated per row before it is summed).
+// quantization noise.  In place; work unit = (superblock, frame, plane), one warp per unit; a
+// warp takes whole rows (the distortion is truncated per row before it is summed).
 // ---------------------------------------------------------------------------
 namespace tdlt {
 
 namespace {
 __constant__ int kBilinearStrength[4] = {5, 20, 20, 5};   // reference src/filter.c:154
 
+// One unit by ONE warp, two passes over its rows (distortion, then update; the second pass
+// re-reads the block from L1/L2): no barrier and no shared memory, so the four warps of a
+// CTA smooth four units side by side.
 template <int DEC>
-__device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli, int *s_part) {
+__device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli) {
   constexpr int ln = 5 - DEC, n = 1 << ln;
   constexpr int shift = 2*4 + 2*ln - 16 > 0 ? 2*4 + 2*ln - 16 : 0;   // OD_COEFF_SHIFT = 4
-  constexpr int rows_per_step = kThreads/n;             // 4 rows (luma) or 8 (chroma) at a time
+  constexpr int rows_per_step = 32/n;                   // one row per warp step (luma) or two (chroma)
   constexpr int steps = n/rows_per_step;
-  const int t = threadIdx.x;
-  const int j = t & (n - 1), i0 = t >> ln;
+  const int lane = threadIdx.x & 31;
+  const int j = lane & (n - 1), i0 = lane >> ln;
   const int x00 = x[0], x01 = x[n - 1], x10 = x[(long long)(n - 1)*w],
             x11 = x[(long long)(n - 1)*w + n - 1];
   int a01 = x01 - x00, a10 = x10 - x00, a11 = x11 + x00 - x10 - x01;
   a01 += (a01 + n/2) >> ln;
   a10 += (a10 + n/2) >> ln;
   a11 += (2*a10 + n/2) >> ln;
-  int xv[steps], yv[steps];
   int dist = 0;
-#pragma unroll
+#pragma unroll 4
   for (int s = 0; s < steps; s++) {
     const int i = i0 + s*rows_per_step;
-    xv[s] = x[(long long)i*w + j];
-    yv[s] = x00 + ((j*a01 + i*a10 + ((j*i*a11) >> ln) + n/2) >> ln);
-    const int d = yv[s] - xv[s];
+    const int xv = x[(long long)i*w + j];
+    const int yv = x00 + ((j*a01 + i*a10 + ((j*i*a11) >> ln) + n/2) >> ln);
+    const int d = yv - xv;
     int row = d*d;
 #pragma unroll
     for (int o = n/2; o >= 1; o >>= 1) row += __shfl_xor_sync(0xffffffffu, row, o);
-    dist += row >> shift;                               // every lane of the row holds the row's sum
+    dist += row >> shift;                               // truncated per row, as the reference does
   }
-  // rows of this thread's lane group -> superblock: one value per row group, summed in shared memory
-  __syncthreads();                                      // s_part free (previous plane)
-  if (j == 0) s_part[i0] = dist;
-  __syncthreads();
-  int total = 0;
-#pragma unroll
-  for (int k = 0; k < rows_per_step; k++) total += s_part[k];
+  int total = dist;                                     // every lane holds its row group's sum
+  if (rows_per_step == 2) total += __shfl_xor_sync(0xffffffffu, dist, 16);
   total += n/2;
   total >>= 2*ln - shift;
   int wgt = min(1024, kBilinearStrength[pli]*q*q/(1 + 12*total));
   wgt = (wgt*wgt) >> 12;
-#pragma unroll
+#pragma unroll 4
   for (int s = 0; s < steps; s++) {
     const int i = i0 + s*rows_per_step;
-    x[(long long)i*w + j] = xv[s] - ((wgt*(xv[s] - yv[s]) + 128) >> 8);
+    int *px = x + (long long)i*w + j;
+    const int xv = *px;
+    const int yv = x00 + ((j*a01 + i*a10 + ((j*i*a11) >> ln) + n/2) >> ln);
+    *px = xv - ((wgt*(xv - yv) + 128) >> 8);
   }
 }
 }  // namespace
 
 __global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P, int nunits) {
-  __shared__ int s_part[8];
   __shared__ int s_list[kThreads];
   __shared__ int s_count;
   // Work unit = (superblock, frame, plane).  Most superblocks are split and have nothing to
   // do, so a fixed-size grid walks the units 128 at a time: every thread looks one unit's map
   // entry up (the loads of a chunk are in flight together), the units that are one 32x32
-  // block are collected in shared memory, then the CTA smooths them one after the other.
+  // block are collected in shared memory, then each warp smooths one of them at a time.
   const int t = threadIdx.x;
   const int per = P.nhsb*P.nvsb;
   for (int base = blockIdx.x*kThreads; base < nunits; base += gridDim.x*kThreads) {
@@ -458,7 +457,7 @@ __global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P, int nu
     }
     __syncthreads();
     const int count = s_count;
-    for (int k = 0; k < count; k++) {
+    for (int k = t >> 5; k < count; k += kThreads/32) {   // one unit per warp
       const int u = s_list[k];
       const int p = u % P.nplanes;
       const int fs = u/P.nplanes;
@@ -469,8 +468,8 @@ __global__ void __launch_bounds__(kThreads) smooth_kernel(SmoothParams P, int nu
       const int n = kSB >> dec;
       const int w = (P.nhsb*kSB) >> dec;
       int *x = P.c[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
-      if (dec == 0) smooth_block<0>(x, w, P.q[p], p, s_part);
-      else smooth_block<1>(x, w, P.q[p], p, s_part);
+      if (dec == 0) smooth_block<0>(x, w, P.q[p], p);
+      else smooth_block<1>(x, w, P.q[p], p);
     }
     __syncthreads();                                    // s_list, s_count free for the next chunk
   }
