@@ -404,7 +404,7 @@ __device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli) {
   a10 += (a10 + n/2) >> ln;
   a11 += (2*a10 + n/2) >> ln;
   int dist = 0;
-#pragma unroll 4
+#pragma unroll 8
   for (int s = 0; s < steps; s++) {
     const int i = i0 + s*rows_per_step;
     const int xv = x[(long long)i*w + j];
@@ -421,7 +421,7 @@ __device__ __forceinline__ void smooth_block(int *x, int w, int q, int pli) {
   total >>= 2*ln - shift;
   int wgt = min(1024, kBilinearStrength[pli]*q*q/(1 + 12*total));
   wgt = (wgt*wgt) >> 12;
-#pragma unroll 4
+#pragma unroll 8
   for (int s = 0; s < steps; s++) {
     const int i = i0 + s*rows_per_step;
     int *px = x + (long long)i*w + j;
