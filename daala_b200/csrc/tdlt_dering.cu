@@ -573,31 +573,39 @@ __device__ __forceinline__ unsigned short coding_source_pos(int e, int ln4, cons
   return (unsigned short)((by + y)*S + bx + x);
 }
 
-// One plane of one superblock: S*S entries, S*S/256 per thread, all of a thread's loads in
-// flight before its first store.  mo[]: this thread's map offsets (fixed per thread).
-template <int DEC>
+// One plane of NSB superblocks at once: S*S entries each, S*S/256 per thread and superblock,
+// all of a thread's loads in flight before its first store (the kernel is bound by the
+// bytes in flight per SM).  mo[]: this thread's map offsets (fixed per thread).
+template <int DEC, int NSB>
 __device__ __forceinline__ void coding_order_sb(int to_coding, const unsigned short *tab, const int *mo,
-                                                const unsigned char *map, int *v, int *d, int w) {
+                                                const unsigned char *const map[], int *const v[],
+                                                int *const d[], int w) {
   constexpr int S = kSB >> DEC;
   constexpr int lS = 5 - DEC;
   constexpr int iters = S*S/kCoThreads;
-  int off[iters];
-  int val[iters];
+  int off[NSB][iters];
+  int val[NSB][iters];
 #pragma unroll
-  for (int it = 0; it < iters; it++) {
-    const int e = threadIdx.x + it*kCoThreads;
-    const int ln4 = max((int)__ldg(map + mo[it]) - DEC, 0);   // log2 of the block side in 4-sample units
-    const int pos = tab[ln4*S*S + e];
-    off[it] = pos == kNoPos ? -1 : (pos >> lS)*w + (pos & (S - 1));
-    if (to_coding) val[it] = off[it] >= 0 ? d[off[it]] : 0;
-    else val[it] = v[e];
+  for (int u = 0; u < NSB; u++) {
+#pragma unroll
+    for (int it = 0; it < iters; it++) {
+      const int e = threadIdx.x + it*kCoThreads;
+      const int ln4 = max((int)__ldg(map[u] + mo[it]) - DEC, 0);   // log2 of the block side in 4-sample units
+      const int pos = tab[ln4*S*S + e];
+      off[u][it] = pos == kNoPos ? -1 : (pos >> lS)*w + (pos & (S - 1));
+      if (to_coding) val[u][it] = off[u][it] >= 0 ? d[u][off[u][it]] : 0;
+      else val[u][it] = v[u][e];
+    }
   }
 #pragma unroll
-  for (int it = 0; it < iters; it++) {
-    const int e = threadIdx.x + it*kCoThreads;
-    if (off[it] < 0) continue;                          // left alone, as the reference leaves it
-    if (to_coding) v[e] = val[it];
-    else d[off[it]] = val[it];
+  for (int u = 0; u < NSB; u++) {
+#pragma unroll
+    for (int it = 0; it < iters; it++) {
+      const int e = threadIdx.x + it*kCoThreads;
+      if (off[u][it] < 0) continue;                     // left alone, as the reference leaves it
+      if (to_coding) v[u][e] = val[u][it];
+      else d[u][off[u][it]] = val[u][it];
+    }
   }
 }
 
@@ -633,36 +641,42 @@ __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P
     mo1[0] = uy*(4*P.nhsb) + ux;
   }
   __syncthreads();
-  // walk the superblocks without dividing: (frame, superblock in frame) advance by the grid
-  // size, the row by a multiply-high with the host's reciprocal (exact below 65536)
+  // walk the superblocks, two horizontal neighbours at a time (the frame is a multiple of 64
+  // samples wide, so nhsb is even), without dividing: (frame, pair in frame) advance by the
+  // grid size, the row by a multiply-high with the host's reciprocal (exact below 65536)
   const int per = P.nhsb*P.nvsb;
-  int frame = blockIdx.x/per;
-  int sb = blockIdx.x - frame*per;
-  const int step_f = gridDim.x/per, step_sb = gridDim.x - step_f*per;
+  const int per2 = per >> 1;
+  int frame = blockIdx.x/per2;
+  int pr = blockIdx.x - frame*per2;
+  const int step_f = gridDim.x/per2, step_pr = gridDim.x - step_f*per2;
   for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+    const int sb = 2*pr;
     const int sby = (int)__umulhi((unsigned)sb, P.recip_nhsb), sbx = sb - sby*P.nhsb;
-    const unsigned char *map = P.bsize + (long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx;
+    const unsigned char *map0 = P.bsize + (long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx;
+    const unsigned char *const map[2] = {map0, map0 + 4};
     for (int p = 0; p < P.nplanes; p++) {
       const int dec = P.dec[p];
       const int S = kSB >> dec;
       const int w = (P.nhsb*kSB) >> dec;
       const long long fo = frame*P.plane_size[p];
-      int *v = P.v[p] + fo + (long long)sb*S*S;
-      int *d = P.d[p] + fo + (long long)(sby*S)*w + sbx*S;
-      if (dec == 0) coding_order_sb<0>(P.to_coding, s_tab0, mo0, map, v, d, w);
-      else coding_order_sb<1>(P.to_coding, s_tab1, mo1, map, v, d, w);
+      int *v0 = P.v[p] + fo + (long long)sb*S*S;
+      int *d0 = P.d[p] + fo + (long long)(sby*S)*w + sbx*S;
+      int *const v[2] = {v0, v0 + S*S};
+      int *const d[2] = {d0, d0 + S};
+      if (dec == 0) coding_order_sb<0, 2>(P.to_coding, s_tab0, mo0, map, v, d, w);
+      else coding_order_sb<1, 2>(P.to_coding, s_tab1, mo1, map, v, d, w);
     }
     frame += step_f;
-    sb += step_sb;
-    if (sb >= per) {
-      sb -= per;
+    pr += step_pr;
+    if (pr >= per2) {
+      pr -= per2;
       frame++;
     }
   }
 }
 
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st) {
-  const long long nunits = (long long)P.nhsb*P.nvsb*nframes;
+  const long long nunits = (long long)(P.nhsb/2)*P.nvsb*nframes;   // pairs of superblocks
   const long long cap = 148ll*12;                       // a fixed grid walks the superblocks (6 and 12
                                                         // CTAs per SM measure the same, 16+ is 8 % slower)
   const int grid = (int)(nunits < cap ? nunits : cap);
