@@ -17,6 +17,12 @@
  *      synchronous; they exist so the reference's own call sites and
  *      OD_CHECKASM-style cross-checks can run against the GPU.
  *
+ * The same three forms exist for the neighbours of the path built so far:
+ *   chroma-from-luma predictor planes  od_tdlt_cfl_pred_batch / _frames, od_resample_luma_coeffs_cuda
+ *   deringing                          od_tdlt_dering_batch / _frames, od_filter_dering_*_cuda
+ *   keyframe bilinear smoothing        od_tdlt_smooth_batch / _frames
+ *   raster <-> coding order            od_tdlt_set_scan_tables, od_tdlt_coding_order_batch / _frames
+ *
  * There is no CPU fallback anywhere in this library: a call either runs on
  * the GPU or fails (int-returning calls return OD_EFAULT; void calls abort,
  * mirroring OD_FATAL in reference src/internal.h:128-158).
