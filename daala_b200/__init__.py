@@ -56,6 +56,7 @@ def lib():
         arr = C.POINTER(vp)
         L.od_tdlt_fwd_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_inv_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
+        L.od_tdlt_fwd_batch_static.argtypes = [C.POINTER(Geometry), arr, arr, vp, ci, ci, vp]
         L.od_tdlt_pix_to_coeff_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_coeff_to_pix_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_cfl_pred_batch.argtypes = [vp, vp, vp, vp, ci, vp]
@@ -293,6 +294,19 @@ def region_order(pic_width, pic_height, decs=(0, 1, 1), rows_in_flight=3):
     if n < 0:
         raise TdltError("od_tdlt_region_order failed: %d" % n)
     return out[:n].copy()
+
+
+def fwd_batch_static(pic_width, pic_height, decs, d_ptrs, c_ptrs, bsize_ptr, nframes, flags=0, stream=0):
+    """od_tdlt_fwd_batch_static: the forward batch call without a context and without any
+    allocation (plan records in a static device array); current CUDA device.  Returns the
+    library's error code instead of raising, so that callers can test the size limit."""
+    g = Geometry()
+    g.pic_width, g.pic_height, g.nplanes = pic_width, pic_height, len(decs)
+    for i, d in enumerate(decs):
+        g.xdec[i] = d
+        g.ydec[i] = d
+    return lib().od_tdlt_fwd_batch_static(C.byref(g), _ptr_array(d_ptrs), _ptr_array(c_ptrs),
+                                          bsize_ptr, nframes, flags, stream)
 
 
 def launch_count():

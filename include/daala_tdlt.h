@@ -112,6 +112,27 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
 int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
  const unsigned char *bsize, int nframes, int flags, void *stream);
 
+/* The forward batch call for callers that must not allocate (code under CUDA graph
+   capture, serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in
+   the reference.
+   Same arguments and results as od_tdlt_fwd_batch, but no context: the geometry is passed
+   directly and the CURRENT CUDA device is used.  The only scratch memory of the forward
+   stage (1 KB of plan per 128x64 region of a plane) lives in a file-scope __device__ array
+   of OD_TDLT_STATIC_MAX_REGIONS records (4 MiB, held by every GPU that loads the library
+   until the process exits); the call makes no cudaMalloc / cudaFree / allocating library
+   call.  regions = nframes * sum over planes of ceil(w/128)*ceil(h/64) of the padded
+   planes (1080p 4:2:0: 399 per frame, 4K 4:2:0: 1530); more than the maximum returns
+   OD_TDLT_EINVAL with a message on stderr.  All calls share the one array: calls that
+   overlap on the GPU (two streams, two host threads) race on it and must be serialised by
+   the caller.  The first call on a device looks the array's address up
+   (cudaGetSymbolAddress) and sets the kernels' attributes: make it outside graph capture.
+   Errors: OD_TDLT_EFAULT / OD_TDLT_EINVAL, message on stderr (there is no context to hold
+   it).  Asynchronous on `stream`. */
+#define OD_TDLT_STATIC_MAX_REGIONS (4096)
+int od_tdlt_fwd_batch_static(const od_tdlt_geometry *geom, od_coeff *const d[],
+ const od_coeff *const c[], const unsigned char *bsize, int nframes, int flags,
+ void *stream);
+
 /* Pixel <-> coefficient conversion on device batches
    (od_ref_buf_to_coeff / od_coeff_to_ref_buf, src/state.c:1209-1316).
    pix: DEVICE pointer to nframes tightly packed planes of (fw>>xdec) x (fh>>ydec)
