@@ -82,6 +82,7 @@ def lib():
                 fn.restype = None
         L.od_tdlt_dct2d_blocks.argtypes = [ci, ci, vp, ci, ll, vp, ci, ll, ci]
         L.od_tdlt_lap_filter_vectors.argtypes = [ci, ci, vp, vp, ci]
+        L.od_tdlt_dct1d_vectors.argtypes = [ci, ci, vp, vp, ci]
         for f in ("od_haar_cuda", "od_haar_inv_cuda"):
             getattr(L, f).argtypes = [vp, ci, vp, ci, ci]
             getattr(L, f).restype = None

@@ -225,6 +225,39 @@ void launch_lap_vectors(int f, bool inverse, int *out, const int *in, int nvec, 
 #undef TDLT_CASE
 }
 
+// 1-D DCTs of many vectors (reference OD_FDCT_1D / OD_IDCT_1D, src/dct.c:58-72), natural
+// order in and out: what the self-test's check_bias streams through (src/dct.c:3565-3598).
+template <int N, bool kInverse>
+__global__ void dct1d_vectors_kernel(int *__restrict__ out, const int *__restrict__ in, int nvec) {
+  int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if (i >= nvec) return;
+  int t[N];
+  const int4 *src = reinterpret_cast<const int4 *>(in + (long long)i*N);
+#pragma unroll
+  for (int k = 0; k < N/4; k++) {
+    int4 q = src[k];
+    t[4*k] = q.x; t[4*k + 1] = q.y; t[4*k + 2] = q.z; t[4*k + 3] = q.w;
+  }
+  if (kInverse) LineDct<N>::i(t); else LineDct<N>::f(t);
+  int4 *dst = reinterpret_cast<int4 *>(out + (long long)i*N);
+#pragma unroll
+  for (int k = 0; k < N/4; k++) dst[k] = make_int4(t[4*k], t[4*k + 1], t[4*k + 2], t[4*k + 3]);
+}
+
+void launch_dct1d_vectors(int bs, bool inverse, int *out, const int *in, int nvec, cudaStream_t st) {
+  int grid = (nvec + 127)/128;
+#define TDLT_CASE(N) \
+  if (inverse) dct1d_vectors_kernel<N, true><<<grid, 128, 0, st>>>(out, in, nvec); \
+  else dct1d_vectors_kernel<N, false><<<grid, 128, 0, st>>>(out, in, nvec)
+  switch (bs) {
+    case 0: TDLT_CASE(4); break;
+    case 1: TDLT_CASE(8); break;
+    case 2: TDLT_CASE(16); break;
+    default: TDLT_CASE(32); break;
+  }
+#undef TDLT_CASE
+}
+
 // Strided line filters used by the host-pointer forms of od_prefilter_split /
 // od_apply_prefilter_frame_sbs and their inverses: `count` lines, line i
 // starts at base + i*line_step and its 4 taps are tap_step apart.

@@ -12,6 +12,7 @@ void launch_dct2d_blocks(int bs, bool inverse, int *out, int ostride, long long 
                          const int *in, int istride, long long iblock, int nblocks,
                          cudaStream_t st);
 void launch_lap_vectors(int f, bool inverse, int *out, const int *in, int nvec, cudaStream_t st);
+void launch_dct1d_vectors(int bs, bool inverse, int *out, const int *in, int nvec, cudaStream_t st);
 void launch_lap4_lines(bool inverse, int *base, long long line_step, long long tap_step,
                        int count, cudaStream_t st);
 void launch_haar_block(bool inverse, int *y, int ystride, const int *x, int xstride, int ln,

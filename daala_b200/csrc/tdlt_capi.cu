@@ -1052,11 +1052,26 @@ int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long l
   // Stage densely: block i at i*n*n.
   size_t tot = (size_t)nblocks*n*n;
   int *din = g_scratch.A(tot), *dout = g_scratch.B(tot);
-  for (int i = 0; i < nblocks; i++) h2d_rect(din + (size_t)i*n*n, in + i*iblock, istride, n, n);
+  // tightly packed blocks travel in one copy
+  if (istride == n && iblock == (long long)n*n) CKF(cudaMemcpy(din, in, tot*4, cudaMemcpyHostToDevice));
+  else for (int i = 0; i < nblocks; i++) h2d_rect(din + (size_t)i*n*n, in + i*iblock, istride, n, n);
   launch_dct2d_blocks(bs, inverse != 0, dout, n, (long long)n*n, din, n, (long long)n*n, nblocks, 0);
   g_launches++;
   if (cudaGetLastError() != cudaSuccess) return OD_TDLT_EFAULT;
-  for (int i = 0; i < nblocks; i++) d2h_rect(out + i*oblock, ostride, dout + (size_t)i*n*n, n, n);
+  if (ostride == n && oblock == (long long)n*n) CKF(cudaMemcpy(out, dout, tot*4, cudaMemcpyDeviceToHost));
+  else for (int i = 0; i < nblocks; i++) d2h_rect(out + i*oblock, ostride, dout + (size_t)i*n*n, n, n);
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_dct1d_vectors(int bs, int inverse, od_coeff *out, const od_coeff *in, int nvec) {
+  if (bs < 0 || bs > 3 || nvec < 1 || !out || !in) return OD_TDLT_EINVAL;
+  size_t tot = (size_t)nvec*(4 << bs);
+  int *din = g_scratch.A(tot), *dout = g_scratch.B(tot);
+  CKF(cudaMemcpy(din, in, tot*4, cudaMemcpyHostToDevice));
+  launch_dct1d_vectors(bs, inverse != 0, dout, din, nvec, 0);
+  g_launches++;
+  if (cudaGetLastError() != cudaSuccess) return OD_TDLT_EFAULT;
+  CKF(cudaMemcpy(out, dout, tot*4, cudaMemcpyDeviceToHost));
   return OD_TDLT_SUCCESS;
 }
 

@@ -283,6 +283,11 @@ void od_tdlt_dering_vtbl_init_cuda(od_tdlt_dering_direction_func direction[],
    (resp. y + i*yblock); the useful form of the above for parity sweeps. */
 int od_tdlt_dct2d_blocks(int bs, int inverse, od_coeff *out, int ostride, long long oblock,
  const od_coeff *in, int istride, long long iblock, int nblocks);
+/* The 1-D transforms od_bin_fdct{4,8,16,32} / od_bin_idct* behind the reference's tables
+   OD_FDCT_1D / OD_IDCT_1D (src/dct.c:58-72; src/dct.c:74-135, 151-333, 349-772, 1757-1958):
+   nvec vectors of 4<<bs values, tightly packed, natural order in and out -- what the
+   reference's check_bias streams through (src/dct.c:3565-3598). */
+int od_tdlt_dct1d_vectors(int bs, int inverse, od_coeff *out, const od_coeff *in, int nvec);
 /* od_pre_filter{4,8,16,32} / od_post_filter*, reference src/filter.c:174-1373;
    nvec vectors of 4<<f samples, tightly packed. */
 int od_tdlt_lap_filter_vectors(int f, int inverse, od_coeff *out, const od_coeff *in, int nvec);

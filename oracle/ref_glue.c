@@ -330,3 +330,29 @@ void ref_dering_orthogonal(void *h, int bsi, int16_t *y, int ystride, int16_t *i
   (*r->enc->state.opt_vtbl.filter_dering_orthogonal[bsi])(y, ystride, in, x, xstride, threshold,
    dir);
 }
+
+/* ---- batched transforms for the self-test streams (src/dct.c:3439-3469, 3565-3598) ----
+   nblocks n x n blocks, tightly packed, through the 2-D tables: impl 0 = OD_FDCT_2D_C /
+   OD_IDCT_2D_C, 1 = the tables the runtime dispatch installs (SSE2 / SSE4.1 / AVX2). */
+void ref_dct2d_blocks(void *h, int bs, int inverse, int impl, od_coeff *out,
+ const od_coeff *in, int nblocks) {
+  ref_ctx *r = (ref_ctx *)h;
+  int n;
+  int k;
+  od_dct_func_2d f;
+  n = 4 << bs;
+  ref_pick_vtbl(r, impl);
+  f = inverse ? r->enc->state.opt_vtbl.idct_2d[bs] : r->enc->state.opt_vtbl.fdct_2d[bs];
+  for (k = 0; k < nblocks; k++) (*f)(out + (size_t)k*n*n, n, in + (size_t)k*n*n, n);
+}
+
+/* nvec vectors of n = 4 << bs values through the 1-D tables (src/dct.c:58-72). */
+void ref_dct1d_vectors(int bs, int inverse, od_coeff *out, const od_coeff *in, int nvec) {
+  int n;
+  int k;
+  n = 4 << bs;
+  for (k = 0; k < nvec; k++) {
+    if (inverse) (*OD_IDCT_1D[bs])(out + (size_t)k*n, 1, in + (size_t)k*n);
+    else (*OD_FDCT_1D[bs])(out + (size_t)k*n, in + (size_t)k*n, 1);
+  }
+}

@@ -111,6 +111,26 @@ void oc_idct2d(int bs, oc_coeff *x, int xstride, const oc_coeff *y, int ystride)
   for (i = 0; i < n; i++) oc_idct1d(bs, x + i, xstride, z + n*i);
 }
 
+/* Batched forms for the self-test streams (src/dct.c:3439-3469, 3565-3598): nblocks
+   tightly packed n x n blocks / nvec tightly packed vectors. */
+void oc_dct2d_blocks(int bs, int inverse, oc_coeff *out, const oc_coeff *in, int nblocks) {
+  int n = 4 << bs;
+  int k;
+  for (k = 0; k < nblocks; k++) {
+    if (inverse) oc_idct2d(bs, out + (size_t)k*n*n, n, in + (size_t)k*n*n, n);
+    else oc_fdct2d(bs, out + (size_t)k*n*n, n, in + (size_t)k*n*n, n);
+  }
+}
+
+void oc_dct1d_vectors(int bs, int inverse, oc_coeff *out, const oc_coeff *in, int nvec) {
+  int n = 4 << bs;
+  int k;
+  for (k = 0; k < nvec; k++) {
+    if (inverse) oc_idct1d(bs, out + (size_t)k*n, 1, in + (size_t)k*n);
+    else oc_fdct1d(bs, out + (size_t)k*n, in + (size_t)k*n, 1);
+  }
+}
+
 /* ------------------------------------------------------ lapping filters -- */
 
 /* Parameter tables: n/2 scale factors s[], then n/2-1 "p" and n/2-1 "u"

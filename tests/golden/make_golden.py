@@ -51,6 +51,44 @@ def cif_frame(t=0, w=352, h=288):
     return y, u, v
 
 
+def lcg_ints_fast(seed, n, lo, hi):
+    """lcg_ints without the Python loop (same values)."""
+    s, _ = ol.lcg_stream_fast(seed, n)
+    return (lo + ((s.astype(np.int64) >> 8) % (hi - lo))).astype(np.int32)
+
+
+def hd_frame(t=0, w=1920, h=1080):
+    """SURVEY 8d C2/C3 stand-in for "textured 1080p frames", integer-only so that it is
+    reproducible bit for bit anywhere: a gradient plus noise at three scales whose amplitude
+    changes from one 64x64 area to the next (flat areas next to busy ones, so that the
+    reference encoder's RDO picks every block size)."""
+    yy, xx = np.mgrid[0:h, 0:w]
+    base = 60 + (xx * 90) // w + (yy * 50) // h
+    nbx, nby = (w + 63) // 64, (h + 63) // 64
+    amps = np.array([0, 1, 3, 8, 20, 40], np.int32)
+    amp = amps[lcg_ints_fast(500 + t, nbx * nby, 0, 6)].reshape(nby, nbx)
+    amp = np.repeat(np.repeat(amp, 64, 0), 64, 1)[:h, :w]
+    fine = lcg_ints_fast(600 + t, w * h, -8, 9).reshape(h, w)
+    mid = lcg_ints_fast(700 + t, ((h + 3) // 4) * ((w + 3) // 4), -8, 9).reshape((h + 3) // 4, (w + 3) // 4)
+    mid = np.repeat(np.repeat(mid, 4, 0), 4, 1)[:h, :w]
+    coarse = lcg_ints_fast(800 + t, ((h + 15) // 16) * ((w + 15) // 16), -8, 9).reshape((h + 15) // 16, (w + 15) // 16)
+    coarse = np.repeat(np.repeat(coarse, 16, 0), 16, 1)[:h, :w]
+    y = np.clip(base + (amp * (fine + 2 * mid + 3 * coarse)) // 16, 0, 255).astype(np.uint8)
+    hw, hh = w // 2, h // 2
+    u = np.clip(128 + (xx[::2, ::2] - hw) // 24 + (amp[::2, ::2] * coarse[::2, ::2]) // 32
+                + lcg_ints_fast(900 + t, hw * hh, -2, 3).reshape(hh, hw), 0, 255).astype(np.uint8)
+    v = np.clip(128 - (yy[::2, ::2] - hh) // 24 + (amp[::2, ::2] * mid[::2, ::2]) // 32
+                + lcg_ints_fast(1000 + t, hw * hh, -2, 3).reshape(hh, hw), 0, 255).astype(np.uint8)
+    return y, u, v
+
+
+def planes_to_coeff(yuv, fw, fh):
+    """8-bit picture planes -> padded int32 coefficient planes, (pix - 128) << 4
+    (od_ref_buf_to_coeff, src/state.c:1221-1230, on edge-extended planes)."""
+    return [(pad_plane(p, fh >> dec, fw >> dec).astype(np.int32) - 128) << 4
+            for p, dec in zip(yuv, (0, 1, 1))]
+
+
 def pad_plane(p, H, W):
     """Edge-extend a picture plane to the padded frame (what od_img_edge_ext leaves
     in the coded area, src/state.c:170-217, is not on the TDLT path; any fill does)."""
@@ -243,5 +281,48 @@ def main():
     print("wrote %s: %d arrays, %d bytes" % (OUT, len(G), os.path.getsize(OUT)))
 
 
+OUT_CONFIGS = os.path.join(HERE, "tdlt_golden_configs.npz")
+
+
+def main_configs():
+    """BASELINE configs at their stated size (second file, so that the first keeps its bytes):
+    config 1 -- ALL ten CIF frames, each a keyframe (keyframe_rate = 1) with the block sizes the
+    reference encoder's RDO chose for it; config 3(i) -- a 1080p frame with its RDO map.
+    Stored: the maps and the SHA-256 of every coefficient plane the reference's forward stage
+    produces from them."""
+    assert ol.have_ref(), "needs oracle/_ref/libdaala_ref.so (make -C oracle ref)"
+    G = {}
+    maps, hashes = [], []
+    for t in range(10):
+        with ol.RefCtx(352, 288) as rc:
+            yuv = cif_frame(t)
+            bs = rc.encode_keyframe_bsize(*yuv, quality=20, complexity=7)
+            maps.append(bs)
+            row = []
+            for pli, (c, dec) in enumerate(zip(planes_to_coeff(yuv, rc.fw, rc.fh), (0, 1, 1))):
+                row.append(sha(rc.fwd_plane(c, bs, dec, 1, impl=0)[0]))
+            hashes.append(row)
+    G["cif10_bsize"] = np.stack(maps)
+    G["cif10_d_sha256"] = np.array(hashes)
+    with ol.RefCtx(1920, 1080) as rc:
+        yuv = hd_frame(0)
+        bs = rc.encode_keyframe_bsize(*yuv, quality=20, complexity=7)
+        G["hd_bsize"] = bs
+        G["hd_d_sha256"] = np.array([sha(rc.fwd_plane(c, bs, dec, 1, impl=0)[0])
+                                     for c, dec in zip(planes_to_coeff(yuv, rc.fw, rc.fh), (0, 1, 1))])
+        c8 = planes_to_coeff(yuv, rc.fw, rc.fh)
+        u8 = np.full_like(bs, 1)
+        G["hd_d_sha256_8x8"] = np.array([sha(rc.fwd_plane(c, u8, dec, 1, impl=0)[0])
+                                         for c, dec in zip(c8, (0, 1, 1))])
+    np.savez_compressed(OUT_CONFIGS, **G)
+    print("wrote %s: %d arrays, %d bytes" % (OUT_CONFIGS, len(G), os.path.getsize(OUT_CONFIGS)))
+    print("hd map histogram:", np.bincount(G["hd_bsize"].ravel(), minlength=4))
+    print("cif maps differ:", len({m.tobytes() for m in maps}))
+
+
 if __name__ == "__main__":
-    main()
+    if "--configs" in sys.argv:
+        main_configs()
+    else:
+        main()
+        main_configs()

@@ -194,6 +194,23 @@ def ref_dering_frame(rc, planes, decs, flags, bskip, q, impl=1):
     return out
 
 
+def ref_dering_block(rc, impl, bsi, y1, y2, ystride, inp, org, ostride, thr, d):
+    """One block through the REFERENCE's deringing filters: impl 0 = the C functions
+    (od_filter_dering_*_c, src/filter.c:1715-1789), 1 = what a fresh state's dispatch table
+    holds (the SSE2 twins, src/x86/x86state.c).  y1 <- direction filter, y2 <- orthogonal."""
+    lib = rc.lib
+    n = 4 << bsi
+    if impl == 0:
+        fd = getattr(lib, "od_filter_dering_direction_%dx%d_c" % (n, n))
+        fo = getattr(lib, "od_filter_dering_orthogonal_%dx%d_c" % (n, n))
+        fd(ptr(y1), ystride, C.c_void_p(inp), thr, d)
+        fo(ptr(y2), ystride, C.c_void_p(inp), ptr(org), ostride, thr, d)
+    else:
+        lib.ref_dering_direction(C.c_void_p(rc.h), bsi, ptr(y1), ystride, C.c_void_p(inp), thr, d)
+        lib.ref_dering_orthogonal(C.c_void_p(rc.h), bsi, ptr(y2), ystride, C.c_void_p(inp),
+                                  ptr(org), ostride, thr, d)
+
+
 def dering_test_frame(rng, nhsb, nvsb, decs=(0, 1, 1), skip_prob=0.5, flag_prob=0.7):
     """A frame that exercises the filter: oriented edges (so that the direction search has
     something to find) plus noise, skip flags in patches, superblock decisions."""
@@ -286,6 +303,48 @@ def port_coding_order_plane(src, bsize, dec, tables, to_coding=True, out=None):
     return out
 
 
+def ref_coding_order_plane(src, bsize, dec, to_coding=True, out=None):
+    """The same planes from the REFERENCE's od_raster_to_coding_order / od_coding_order_to_raster
+    (src/partition.c:144-200) called block by block over the map, as its call sites do
+    (src/encode.c:1160-1161, src/decode.c:630); only the block-linear placement of the vectors
+    (oc_block_linear_offset, this library's own layout) comes from the port."""
+    R, P = ref(), port()
+    R.od_raster_to_coding_order.restype = None
+    R.od_coding_order_to_raster.restype = None
+    P.oc_block_linear_offset.restype = C.c_longlong
+    src = np.ascontiguousarray(src, dtype=np.int32)
+    out = np.zeros_like(src) if out is None else out
+    H, W = src.shape
+    flat_in, flat_out = src.ravel(), out.reshape(-1)
+    for uy in range(bsize.shape[0]):
+        for ux in range(bsize.shape[1]):
+            obs = int(bsize[uy, ux])
+            lu = max(obs - 1, 0)
+            if (ux & ((1 << lu) - 1)) or (uy & ((1 << lu) - 1)):
+                continue
+            n = max(4, (4 << obs) >> dec)
+            xu, yu = (ux * 8) >> dec, (uy * 8) >> dec
+            # an 8x8 luma unit coded as 4x4 blocks holds four of them (one in 4:2:0 chroma)
+            subs = ((0, 0), (4, 0), (0, 4), (4, 4)) if (obs == 0 and dec == 0) else ((0, 0),)
+            for sx, sy in subs:
+              x0, y0 = xu + sx, yu + sy
+              off = P.oc_block_linear_offset(x0, y0, W, 32 >> dec)
+              if to_coding:
+                  blk = np.ascontiguousarray(src[y0:y0 + n, x0:x0 + n])
+                  vec = np.ascontiguousarray(flat_out[off:off + n * n])
+                  ncoded = min(n * n, 512)
+                  tmp = np.zeros(n * n, np.int32)
+                  R.od_raster_to_coding_order(ptr(tmp), n, ptr(blk), n)
+                  vec[:ncoded] = tmp[:ncoded]
+                  flat_out[off:off + n * n] = vec
+              else:
+                  vec = np.ascontiguousarray(flat_in[off:off + n * n])
+                  blk = np.ascontiguousarray(out[y0:y0 + n, x0:x0 + n])
+                  R.od_coding_order_to_raster(ptr(blk), n, ptr(vec), n)
+                  out[y0:y0 + n, x0:x0 + n] = blk
+    return out
+
+
 # ----------------------------------------------------------------- ref API --
 class RefCtx:
     """An instance of the reference encoder state for one picture size."""
@@ -337,6 +396,26 @@ class RefCtx:
         return out
 
 
+def dct2d_blocks(which, bs, inverse, X, rc=None, impl=0):
+    """nblocks tightly packed blocks through a checker: which = "port" or "ref" (ref needs a
+    RefCtx; impl 0 = the C tables, 1 = the x86 dispatch)."""
+    X = np.ascontiguousarray(X, dtype=np.int32)
+    out = np.zeros_like(X)
+    if which == "ref":
+        rc.lib.ref_dct2d_blocks(C.c_void_p(rc.h), bs, int(inverse), impl, ptr(out), ptr(X), X.shape[0])
+    else:
+        port().oc_dct2d_blocks(bs, int(inverse), ptr(out), ptr(X), X.shape[0])
+    return out
+
+
+def dct1d_vectors(which, bs, inverse, X):
+    X = np.ascontiguousarray(X, dtype=np.int32)
+    out = np.zeros_like(X)
+    f = ref().ref_dct1d_vectors if which == "ref" else port().oc_dct1d_vectors
+    f(bs, int(inverse), ptr(out), ptr(X), X.shape[0])
+    return out
+
+
 # ------------------------------------------------------------- generators --
 def lcg_stream(seed, n):
     """The IEEE-1180 style LCG the reference's self-test seeds its vectors with
@@ -347,6 +426,36 @@ def lcg_stream(seed, n):
         x = (x * 1103515245 + 12345) & 0xFFFFFFFF
         out[i] = x
     return out
+
+
+def lcg_stream_fast(seed, n):
+    """lcg_stream without the Python loop: the n-step affine map is built by doubling
+    (x -> a*x + c composed with itself), all in uint32 arithmetic.  Returns (values, next
+    seed) with values uint32, bit-identical to lcg_stream."""
+    a = np.uint64(1103515245)
+    c = np.uint64(12345)
+    m = np.uint64(0xFFFFFFFF)
+    out = np.empty(max(n, 1), dtype=np.uint64)
+    out[0] = (np.uint64(seed & 0xFFFFFFFF) * a + c) & m
+    have = 1
+    A, Cc = a, c                      # the `have`-step map
+    while have < n:
+        take = min(have, n - have)
+        out[have:have + take] = (out[:take] * A + Cc) & m
+        Cc = (A * Cc + Cc) & m
+        A = (A * A) & m
+        have += take
+    out = out[:n]
+    return out.astype(np.uint32), (int(out[-1]) if n else seed)
+
+
+def ieee1180_rand(seed, n, l, h):
+    """n values of the reference self-test's ieee1180_rand(l, h) (src/dct.c:2378-2389),
+    starting from generator state `seed`; returns (int32 values, next state)."""
+    x, nxt = lcg_stream_fast(seed, n)
+    i = (x & np.uint32(0x7FFFFFFE)).astype(np.float64)
+    v = (i / float(0x7FFFFFFF) * (l + h + 1)).astype(np.int64) - l
+    return v.astype(np.int32), nxt
 
 
 def random_quadtree_bsize(nhsb, nvsb, rng, p32=0.8, p16=0.6, p8=0.5):

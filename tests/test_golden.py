@@ -273,3 +273,79 @@ def test_cuda_cif_keyframe(G):
         ctx.inv_frames(c2, d, bs, daala_b200.OD_TDLT_KEYFRAME)
         for p in range(3):
             assert np.array_equal(c2[p], c[p])
+
+
+# ---------------------------------------------- BASELINE configs at their stated size --
+@pytest.fixture(scope="module")
+def GC():
+    return np.load(os.path.join(HERE, "golden", "tdlt_golden_configs.npz"))
+
+
+def test_port_cif_ten_frames(GC):
+    """Config 1 as BASELINE.json states it: all ten frames, each with the map the reference
+    encoder's RDO chose for it (the moving square makes them differ)."""
+    import make_golden as mg
+    assert len({GC["cif10_bsize"][t].tobytes() for t in range(10)}) > 1
+    for t in range(10):
+        bs = GC["cif10_bsize"][t]
+        for pli, (c, dec) in enumerate(zip(mg.planes_to_coeff(mg.cif_frame(t), 384, 320), (0, 1, 1))):
+            d, _ = ol.port_fwd_plane(c, bs, dec, 352, 288, 1)
+            assert _sha(d) == str(GC["cif10_d_sha256"][t][pli]), (t, pli)
+
+
+def test_port_hd_frame_rdo_map_and_uniform_8x8(GC):
+    """Configs 2 and 3(i) at 1080p: fixed 8x8 blocks, and the RDO map of the textured frame."""
+    import make_golden as mg
+    c = mg.planes_to_coeff(mg.hd_frame(0), 1920, 1088)
+    for key, bs in (("hd_d_sha256", GC["hd_bsize"]), ("hd_d_sha256_8x8", np.full_like(GC["hd_bsize"], 1))):
+        for pli, dec in enumerate((0, 1, 1)):
+            d, _ = ol.port_fwd_plane(c[pli], bs, dec, 1920, 1080, 1)
+            assert _sha(d) == str(GC[key][pli]), (key, pli)
+
+
+@pytest.mark.gpu
+def test_cuda_cif_ten_frames(GC):
+    import daala_b200
+    import make_golden as mg
+    frames = [mg.planes_to_coeff(mg.cif_frame(t), 384, 320) for t in range(10)]
+    c = [np.ascontiguousarray(np.stack([f[p] for f in frames])) for p in range(3)]
+    bs = np.ascontiguousarray(GC["cif10_bsize"])
+    with daala_b200.TdltContext(352, 288, decs=(0, 1, 1), device=0, max_frames=10) as ctx:
+        d = [np.zeros_like(a) for a in c]
+        ctx.fwd_frames(d, c, bs, daala_b200.OD_TDLT_KEYFRAME)
+        for t in range(10):
+            for p in range(3):
+                assert _sha(d[p][t]) == str(GC["cif10_d_sha256"][t][p]), (t, p)
+        c2 = [np.zeros_like(a) for a in c]
+        ctx.inv_frames(c2, d, bs, daala_b200.OD_TDLT_KEYFRAME)
+        for p in range(3):
+            assert np.array_equal(c2[p], c[p])
+
+
+@pytest.mark.gpu
+def test_cuda_hd_frame_rdo_map_and_uniform_8x8(GC):
+    import daala_b200
+    import make_golden as mg
+    c = [np.ascontiguousarray(p)[None] for p in mg.planes_to_coeff(mg.hd_frame(0), 1920, 1088)]
+    with daala_b200.TdltContext(1920, 1080, decs=(0, 1, 1), device=0, max_frames=1) as ctx:
+        for key, bs in (("hd_d_sha256", GC["hd_bsize"]), ("hd_d_sha256_8x8", np.full_like(GC["hd_bsize"], 1))):
+            bs = np.ascontiguousarray(bs)[None]
+            d = [np.zeros_like(a) for a in c]
+            ctx.fwd_frames(d, c, bs, daala_b200.OD_TDLT_KEYFRAME)
+            for p in range(3):
+                assert _sha(d[p][0]) == str(GC[key][p]), (key, p)
+            c2 = [np.zeros_like(a) for a in c]
+            ctx.inv_frames(c2, d, bs, daala_b200.OD_TDLT_KEYFRAME)
+            for p in range(3):
+                assert np.array_equal(c2[p], c[p])
+            if ol.have_ref():
+                # and the decoder side on arbitrary coefficients, against the reference itself
+                from checker import Checker
+                chk = Checker(1920, 1080)
+                rng = np.random.default_rng(5)
+                dq = [rng.integers(-30000, 30000, size=a.shape).astype(np.int32) for a in c]
+                ctx.inv_frames(c2, dq, bs, daala_b200.OD_TDLT_KEYFRAME)
+                c_ref = chk.inv_frames(dq, bs, (0, 1, 1), 1)
+                for p in range(3):
+                    assert np.array_equal(c2[p], c_ref[p]), (key, p)
+                chk.close()

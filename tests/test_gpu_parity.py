@@ -27,6 +27,7 @@ FRAME_CASES = [
     (352, 288, "uniform0", 1), (352, 288, "uniform1", 0), (352, 288, "uniform2", 1),
     (352, 288, "uniform3", 1), (200, 136, "quad", 1), (200, 136, "deep", 0),
     (64, 64, "quad", 1), (33, 17, "deep", 1), (1920, 1080, "quad", 1),
+    (1920, 1080, "uniform1", 1),      # BASELINE config 2 at its stated size
 ]
 
 
@@ -155,6 +156,12 @@ def test_pixel_paths_match_checker(xstride, mode, lossless):
                 port.oc_buf_to_coeff(mode, ol.ptr(cc[f]), v.shape[2], lossless,
                                      ol.ptr(src.view(np.uint8)), xstride, src.strides[0],
                                      v.shape[2], v.shape[1])
+                if ol.have_ref():     # od_ref_buf_to_coeff itself (src/state.c:1209)
+                    cr = np.zeros_like(cc[f])
+                    ol.ref().ref_buf_to_coeff(mode, ol.ptr(cr), v.shape[2], lossless,
+                                              ol.ptr(src.view(np.uint8)), xstride, src.strides[0],
+                                              v.shape[2], v.shape[1])
+                    assert np.array_equal(cr, cc[f])
             c.append(cc)
         d_ref = chk.fwd_frames(c, bsize, DECS, 1)
         for p in range(3):
@@ -173,6 +180,11 @@ def test_pixel_paths_match_checker(xstride, mode, lossless):
                 port.oc_coeff_to_buf(mode, ol.ptr(tmp), xstride, w * xstride, ol.ptr(c_ref[p][f]), w,
                                      lossless, w, h)
                 exp[f] = tmp.view(pix[p].dtype).reshape(h, w)
+                if ol.have_ref():     # od_coeff_to_ref_buf itself (src/state.c:1274)
+                    tr = np.zeros_like(tmp)
+                    ol.ref().ref_coeff_to_buf(mode, ol.ptr(tr), xstride, w * xstride,
+                                              ol.ptr(c_ref[p][f]), w, lossless, w, h)
+                    assert np.array_equal(tr, tmp)
             assert np.array_equal(oviews[p], exp)
             border = outs[p].copy()
             border[:, pad:pad + h, pad:pad + w] = 7
@@ -208,6 +220,11 @@ def test_dct_block_sweep(bs):
         assert np.array_equal(F[k], y)
         port.oc_idct2d(bs, ol.ptr(y), n, ol.ptr(X[k]), n)
         assert np.array_equal(I[k], y)
+    if ol.have_ref():     # the compiled reference itself: C tables and the x86 dispatch
+        with ol.RefCtx(64, 64) as rc:
+            for impl in (0, 1):
+                assert np.array_equal(F, ol.dct2d_blocks("ref", bs, 0, X, rc, impl))
+                assert np.array_equal(I, ol.dct2d_blocks("ref", bs, 1, X, rc, impl))
     # perfect reconstruction, and strided single-block calls inside a larger plane
     R = np.zeros_like(X)
     assert L.od_tdlt_dct2d_blocks(bs, 1, R.ctypes.data, n, n * n, F.ctypes.data, n, n * n, nb) == 0
@@ -247,6 +264,13 @@ def test_lap_filter_sweep(f):
         assert np.array_equal(P[k], y)
         port.oc_post_filter(f, ol.ptr(y), ol.ptr(X[k]))
         assert np.array_equal(Q[k], y)
+    if ol.have_ref():
+        pre, post = getattr(ol.ref(), "od_pre_filter%d" % n), getattr(ol.ref(), "od_post_filter%d" % n)
+        for k in range(X.shape[0]):
+            pre(ol.ptr(y), ol.ptr(X[k]))
+            assert np.array_equal(P[k], y)
+            post(ol.ptr(y), ol.ptr(X[k]))
+            assert np.array_equal(Q[k], y)
     R = np.zeros_like(X)
     assert L.od_tdlt_lap_filter_vectors(f, 1, R.ctypes.data, P.ctypes.data, X.shape[0]) == 0
     assert np.array_equal(R, X)
@@ -257,6 +281,11 @@ def test_split_and_sb_edge_filters():
     reference's own signatures (host pointers, in place)."""
     import daala_b200
     L, port = daala_b200.lib(), ol.port()
+    R = ol.ref() if ol.have_ref() else None
+    if R:
+        for fn in (R.od_prefilter_split, R.od_postfilter_split, R.od_apply_prefilter_frame_sbs,
+                   R.od_apply_postfilter_frame_sbs):
+            fn.restype = None
     rng = np.random.default_rng(1200)
     for bs in (1, 2, 3):
         n = 4 << bs
@@ -264,22 +293,36 @@ def test_split_and_sb_edge_filters():
             stride = n + 9
             a = rng.integers(-2048, 2048, size=(n, stride)).astype(np.int32)
             b = a.copy()
+            r = a.copy()
             L.od_prefilter_split_cuda(a.ctypes.data, stride, bs, 0, hf, vf)
             port.oc_prefilter_split(ol.ptr(b), stride, bs, 0, hf, vf)
             assert np.array_equal(a, b)
+            if R:
+                R.od_prefilter_split(ol.ptr(r), stride, bs, 0, hf, vf)
+                assert np.array_equal(a, r)
             L.od_postfilter_split_cuda(a.ctypes.data, stride, bs, 0, 0, None, 0, hf, vf)
             port.oc_postfilter_split(ol.ptr(b), stride, bs, 0, hf, vf)
             assert np.array_equal(a, b)
+            if R:
+                R.od_postfilter_split(ol.ptr(r), stride, bs, 0, 0, None, 0, hf, vf)
+                assert np.array_equal(a, r)
     for nhsb, nvsb, dec in ((5, 3, 0), (6, 4, 1), (1, 1, 0), (1, 3, 1)):
         w, h = (nhsb * 32) >> dec, (nvsb * 32) >> dec
         a = rng.integers(-2048, 2048, size=(h, w)).astype(np.int32)
         b = a.copy()
+        r = a.copy()
         L.od_apply_prefilter_frame_sbs_cuda(a.ctypes.data, w, nhsb, nvsb, dec, dec)
         port.oc_apply_prefilter_frame_sbs(ol.ptr(b), w, nhsb, nvsb, dec, dec)
         assert np.array_equal(a, b)
+        if R:
+            R.od_apply_prefilter_frame_sbs(ol.ptr(r), w, nhsb, nvsb, dec, dec)
+            assert np.array_equal(a, r)
         L.od_apply_postfilter_frame_sbs_cuda(a.ctypes.data, w, nhsb, nvsb, dec, dec, 0, None, 0)
         port.oc_apply_postfilter_frame_sbs(ol.ptr(b), w, nhsb, nvsb, dec, dec)
         assert np.array_equal(a, b)
+        if R:
+            R.od_apply_postfilter_frame_sbs(ol.ptr(r), w, nhsb, nvsb, dec, dec, 0, None, 0)
+            assert np.array_equal(a, r)
 
 
 CFL_CASES = [(352, 288, "quad"), (352, 288, "deep"), (200, 136, "quad"), (33, 17, "deep"),
@@ -328,6 +371,11 @@ def test_resample_luma_block(obs, dec):
         L.od_resample_luma_coeffs_cuda(a.ctypes.data, n + 5, luma.ctypes.data, ln + 7, dec, dec, bs, obs)
         port.oc_resample_luma_coeffs(ol.ptr(b), n + 5, ol.ptr(luma), ln + 7, dec, dec, bs, obs)
         assert np.array_equal(a, b)
+        if ol.have_ref():         # od_resample_luma_coeffs itself (src/intra.c:72)
+            r = np.full((n, n + 5), 99, np.int32)
+            ol.ref().od_resample_luma_coeffs.restype = None
+            ol.ref().od_resample_luma_coeffs(ol.ptr(r), n + 5, ol.ptr(luma), ln + 7, dec, dec, bs, obs)
+            assert np.array_equal(a, r)
 
 
 def _dering_batch(rng, nframes, nhsb, nvsb, decs, skip_prob):
@@ -423,6 +471,8 @@ def test_dering_block_filters(bsi):
     L.od_tdlt_dering_vtbl_init_cuda(dtab, otab)
     rng = np.random.default_rng(1800 + bsi)
     n, P = 4 << bsi, 38
+    ref_pitch = 38                      # OD_FILT_BSTRIDE, the row pitch the reference's `in` has
+    rc = ol.RefCtx(64, 64) if ol.have_ref() else None
     for trial in range(24):
         d = trial % 8
         thr = int(rng.choice([0, 1, 7, 40, 300, 2000]))
@@ -438,6 +488,13 @@ def test_dering_block_filters(bsi):
         port.oc_dering_direction(ol.ptr(w1), n + 1, C.c_void_p(inp), 2 + bsi, thr, d)
         port.oc_dering_orthogonal(ol.ptr(w2), n + 1, C.c_void_p(inp), ol.ptr(org), n + 2, 2 + bsi, thr, d)
         assert np.array_equal(y1, w1) and np.array_equal(y2, w2)
+        if rc is not None and P == ref_pitch:
+            # the reference's own filters through its dispatch table (C and the SSE2 twins;
+            # the SSE2 ones need 30000 - x and 14*threshold in 16 bits: thresholds <= 2000 do)
+            for impl in (0, 1):
+                r1, r2 = np.full((n, n + 1), 5, np.int16), np.full((n, n + 1), 5, np.int16)
+                ol.ref_dering_block(rc, impl, bsi, r1, r2, n + 1, inp, org, n + 2, thr, d)
+                assert np.array_equal(y1, r1) and np.array_equal(y2, r2), (impl, trial)
 
 
 @pytest.mark.parametrize("pic_w,pic_h,kind,decs", [
@@ -461,6 +518,10 @@ def test_coding_order_frames_match_checker(pic_w, pic_h, kind, decs):
                 want = ol.port_coding_order_plane(d[p][f], bsize[f], dec, tables, True,
                                                   out=np.full_like(d[p][f], 424242))
                 assert np.array_equal(v[p][f], want), "to coding order, plane %d frame %d" % (p, f)
+                if ol.have_ref() and pic_w < 1000:
+                    want = ol.ref_coding_order_plane(d[p][f], bsize[f], dec, True,
+                                                     out=np.full_like(d[p][f], 424242))
+                    assert np.array_equal(v[p][f], want), "vs reference, plane %d frame %d" % (p, f)
         back = [np.full_like(a, -7) for a in d]
         ctx.coding_order_frames(v, back, bsize, False)
         for p, dec in enumerate(decs):
@@ -468,6 +529,10 @@ def test_coding_order_frames_match_checker(pic_w, pic_h, kind, decs):
                 want = ol.port_coding_order_plane(v[p][f], bsize[f], dec, tables, False,
                                                   out=np.full_like(d[p][f], -7))
                 assert np.array_equal(back[p][f], want), "to raster, plane %d frame %d" % (p, f)
+                if ol.have_ref() and pic_w < 1000:
+                    want = ol.ref_coding_order_plane(v[p][f], bsize[f], dec, False,
+                                                     out=np.full_like(d[p][f], -7))
+                    assert np.array_equal(back[p][f], want), "vs reference, plane %d frame %d" % (p, f)
             covered = back[p] != -7
             assert np.array_equal(back[p][covered], d[p][covered])
 
