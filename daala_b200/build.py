@@ -14,11 +14,28 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-Xcompiler", "-fPIC"]
 
 
+def source_hash():
+    """SHA-256 over every file the library is built from (all of csrc/ and include/) and the
+    compiler flags: the library is rebuilt whenever it differs from the sidecar written next
+    to the .so, so a stale binary cannot survive a header-only edit."""
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    inc = os.path.join(HERE, "..", "include")
+    files = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".h"))]
+    files += [os.path.join(inc, f) for f in sorted(os.listdir(inc)) if f.endswith(".h")]
+    for f in files:
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()
+
+
+STAMP = LIB + ".sha256"
+
+
 def _stale():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
+    return open(STAMP).read().strip() != source_hash()
 
 
 def build(force=False, verbose=False, trace=False):
@@ -45,6 +62,8 @@ def build(force=False, verbose=False, trace=False):
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
     cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart_static" if False else "-lcudart"]
     subprocess.check_call(cmd)
+    with open(STAMP, "w") as f:
+        f.write(source_hash() + "\n")
     return LIB
 
 

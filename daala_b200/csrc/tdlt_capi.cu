@@ -78,6 +78,22 @@ static int fail(od_tdlt_ctx *ctx, int code, const char *fmt, ...) {
     } \
   } while (0)
 
+// Every context entry point makes the context's device current for the duration of the
+// call and puts the caller's device back on return (a process may hold one context per GPU).
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false, switched = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev == dev) { ok = true; return; }
+    ok = cudaSetDevice(dev) == cudaSuccess;
+    switched = ok;
+  }
+  ~DeviceGuard() { if (switched && prev >= 0) cudaSetDevice(prev); }
+  DeviceGuard(const DeviceGuard &) = delete;
+  DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+
 // cuTensorMapEncodeTiled is a driver-API symbol; fetch it through the runtime
 // so the library does not link against libcuda directly.
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
@@ -96,6 +112,11 @@ static encode_tiled_fn get_encode_tiled() {
     }
   }
   return fn;
+}
+
+static bool ranges_overlap(const void *a, const void *b, size_t bytes) {
+  const uintptr_t x = (uintptr_t)a, y = (uintptr_t)b;
+  return x < y + bytes && y < x + bytes;
 }
 
 // 3-D map (x, y, frame) over nframes planes of w x h int32; box bx x by x 1.
@@ -236,8 +257,7 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
       // frames, ms per launch incl. plan): frame-major raster 2.23; frame-interleaved with
       // b = 1 / 2 / 3 / 5 / 8 rows of regions in flight 2.12 / 2.09 / 2.08 / 2.08 / 2.09;
       // whole diagonals 2.14 - 2.25.  Three tables, the batch size picks one: about 200
-      // tickets between a region and its left neighbour.  TDLT_INV_BANDS (experiments)
-      // overrides b of all three.
+      // tickets between a region and its left neighbour.
       if (rb.regs_per_frame > 65535) { rc = OD_TDLT_EINVAL; break; }
       const int nreg = rb.regs_per_frame;
       std::vector<unsigned short> order((size_t)kOrderTables*nreg), one;
@@ -245,7 +265,6 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
       for (int p = 0; p < g->nplanes; p++) opl[p] = OrderPlane{rb.pl[p].nrx, rb.pl[p].nry, rb.pl[p].reg0};
       for (int tb = 0; tb < kOrderTables; tb++) {
         int bands = kOrderBands[tb];
-        if (const char *e = getenv("TDLT_INV_BANDS")) bands = std::max(1, atoi(e));
         build_region_order(opl, g->nplanes, bands, one);
         memcpy(&order[(size_t)tb*nreg], one.data(), (size_t)nreg*sizeof(unsigned short));
       }
@@ -361,7 +380,8 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
                       const unsigned char *bsize, int nframes, int flags, void *stream) {
   if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
   RegionBatch rb = ctx->rb;
@@ -373,6 +393,9 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   for (int p = 0; p < rb.nplanes; p++) {
     if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
+    }
+    if (ranges_overlap(c[p], d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff))) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane %d: c and d overlap (the stage is out of place)", p);
     }
     int rc = make_tmap(ctx, &maps.in[p], c[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
     if (rc) return rc;
@@ -413,7 +436,8 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
                       const unsigned char *bsize, int nframes, int flags, void *stream) {
   if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.inv_nframes = 1.0f/(float)nframes;
@@ -425,6 +449,9 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   for (int p = 0; p < rb.nplanes; p++) {
     if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
+    }
+    if (ranges_overlap(c[p], d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff))) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane %d: c and d overlap (the stage is out of place)", p);
     }
     int trc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
     if (trc) return trc;
@@ -468,7 +495,8 @@ int od_tdlt_pix_to_coeff_batch(od_tdlt_ctx *ctx, od_coeff *c, const void *pix, i
       bitdepth_mode > 3) {
     return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");
   }
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_pix_to_coeff(c, pix, ctx->plane_size[pli]*nframes, xstride,
                       conv_shift(xstride, bitdepth_mode, lossless_p), (cudaStream_t)stream);
   g_launches++;
@@ -484,7 +512,8 @@ int od_tdlt_coeff_to_pix_batch(od_tdlt_ctx *ctx, void *pix, const od_coeff *c, i
       bitdepth_mode > 3) {
     return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");
   }
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_coeff_to_pix(pix, c, ctx->plane_size[pli]*nframes, xstride,
                       conv_shift(xstride, bitdepth_mode, lossless_p), (cudaStream_t)stream);
   g_launches++;
@@ -503,7 +532,8 @@ int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma
                 "plane 1 halved both ways); with 4:4:4 the predictor is the luma plane itself");
   }
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes %d", nframes);
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_cfl_pred(l, ctx->fw >> 1, ctx->plane_size[1], d_luma, ctx->fw, ctx->plane_size[0], bsize,
                   ctx->nhsb*4, ctx->nvsb*4, nframes, (cudaStream_t)stream);
   g_launches++;
@@ -542,7 +572,8 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
   P.nvsb = ctx->nvsb;
   P.skip_stride = ctx->nhsb*8;
   P.skip_frame = (long long)ctx->nhsb*8*ctx->nvsb*8;
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_dering(P, nframes, (cudaStream_t)stream);
   g_launches++;
   CK(ctx, cudaGetLastError());
@@ -573,7 +604,8 @@ int od_tdlt_smooth_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned c
   P.bsize = bsize;
   P.nhsb = ctx->nhsb;
   P.nvsb = ctx->nvsb;
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_smooth(P, nframes, (cudaStream_t)stream);
   g_launches++;
   CK(ctx, cudaGetLastError());
@@ -603,7 +635,8 @@ int od_tdlt_set_scan_tables(od_tdlt_ctx *ctx, const unsigned char *const tables[
     memcpy(host + off, tables[k], 2*kTableLen[k]);
     off += 2*kTableLen[k];
   }
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   if (!ctx->dev_scan) CK(ctx, cudaMalloc(&ctx->dev_scan, sizeof(host)));
   CK(ctx, cudaMemcpy(ctx->dev_scan, host, sizeof(host), cudaMemcpyHostToDevice));
   for (int k = 0; k < 4; k++) ctx->scan_len[k] = lens[k];
@@ -637,7 +670,8 @@ int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *
   P.to_coding = to_coding != 0;
   if ((long long)ctx->nhsb*ctx->nvsb >= 65536) return fail(ctx, OD_TDLT_EINVAL, "frame too large for the coding-order walk");
   P.recip_nhsb = (unsigned)(((1ull << 32) + ctx->nhsb - 1)/ctx->nhsb);
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_coding_order(P, nframes, (cudaStream_t)stream);
   g_launches++;
   CK(ctx, cudaGetLastError());
@@ -673,10 +707,11 @@ struct FramesJob {
   int nframes, flags, xstride, bitdepth_mode, lossless_p;
 };
 
-static int run_frames(od_tdlt_ctx *ctx, const FramesJob &j) {
-  int rc = check_frames(ctx, j.nframes);
-  if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
+// Queues the whole pipeline; any error returns at once -- run_frames below drains the
+// streams whatever happened, so no copy is still touching the caller's buffers when
+// the call returns.
+static int run_frames_queue(od_tdlt_ctx *ctx, const FramesJob &j) {
+  int rc = OD_TDLT_SUCCESS;
   const int np = ctx->g.nplanes;
   long long frame_samples = 0;
   for (int p = 0; p < np; p++) frame_samples += ctx->plane_size[p];
@@ -768,9 +803,22 @@ static int run_frames(od_tdlt_ctx *ctx, const FramesJob &j) {
       }
     }
   }
-  CK(ctx, cudaStreamSynchronize(s_out));
-  CK(ctx, cudaStreamSynchronize(s_run));
-  CK(ctx, cudaStreamSynchronize(s_in));
+  return OD_TDLT_SUCCESS;
+}
+
+static int run_frames(od_tdlt_ctx *ctx, const FramesJob &j) {
+  int rc = check_frames(ctx, j.nframes);
+  if (rc) return rc;
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
+  rc = run_frames_queue(ctx, j);
+  // drain all three streams on every path (an error above must not leave copies in flight)
+  const cudaError_t e0 = cudaStreamSynchronize(ctx->s_in);
+  const cudaError_t e1 = cudaStreamSynchronize(ctx->stream);
+  const cudaError_t e2 = cudaStreamSynchronize(ctx->s_out);
+  if (rc) return rc;
+  const cudaError_t e = e0 != cudaSuccess ? e0 : (e1 != cudaSuccess ? e1 : e2);
+  if (e != cudaSuccess) return fail(ctx, OD_TDLT_EFAULT, "host-pointer call: %s", cudaGetErrorString(e));
   return OD_TDLT_SUCCESS;
 }
 
@@ -799,7 +847,8 @@ int od_tdlt_cfl_pred_frames(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_lum
   int rc = check_frames(ctx, nframes);
   if (rc) return rc;
   if (ctx->g.nplanes < 2) return fail(ctx, OD_TDLT_EINVAL, "no chroma plane");
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   // staging: the luma coefficient plane and the predictor plane in the slots the
   // transform calls use for them (plane 0 coefficients, plane 1 samples)
   cudaStream_t st = ctx->stream;
@@ -821,7 +870,8 @@ int od_tdlt_dering_frames(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coef
   if (!ctx || !out || !in || !flags || !bskip || !q) return OD_TDLT_EFAULT;
   int rc = check_frames(ctx, nframes);
   if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   const int np = ctx->g.nplanes;
   const size_t nsb = (size_t)ctx->nhsb*ctx->nvsb*nframes;
   const size_t skip = (size_t)ctx->nhsb*8*ctx->nvsb*8*nframes;
@@ -859,7 +909,8 @@ int od_tdlt_smooth_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const unsigned 
   if (!ctx || !c || !bsize || !q) return OD_TDLT_EFAULT;
   int rc = check_frames(ctx, nframes);
   if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   cudaStream_t st = ctx->stream;
   const int np = ctx->g.nplanes;
   for (int p = 0; p < np; p++) {
@@ -884,7 +935,8 @@ int od_tdlt_coding_order_frames(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff 
   if (!ctx || !v || !d || !bsize) return OD_TDLT_EFAULT;
   int rc = check_frames(ctx, nframes);
   if (rc) return rc;
-  CK(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   cudaStream_t st = ctx->stream;
   const int np = ctx->g.nplanes;
   // both sides go up: entries the scans do not cover keep what the destination held
@@ -948,21 +1000,34 @@ static void die(const char *what, cudaError_t e) {
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) die(#call, e_); } while (0)
 
 namespace {
+// Scratch of the reference-signature wrappers: one pair of buffers per host thread AND per
+// device (the wrappers run on whatever device is current, as the reference's functions run
+// on whatever core calls them), so two threads or two GPUs never share or free each other's
+// memory.  Buffers live until the process ends.
 struct Scratch {
-  int *a = nullptr, *b = nullptr;
-  size_t na = 0, nb = 0;
+  static constexpr int kMaxDev = 64;
+  int *a[kMaxDev] = {}, *b[kMaxDev] = {};
+  size_t na[kMaxDev] = {}, nb[kMaxDev] = {};
+  static int dev() {
+    int d = 0;
+    CKF(cudaGetDevice(&d));
+    if (d < 0 || d >= kMaxDev) die("device index outside the scratch table", cudaErrorInvalidDevice);
+    return d;
+  }
   int *get(int *&p, size_t &n, size_t want) {
     if (want > n) {
       if (p) CKF(cudaFree(p));
+      p = nullptr;
+      n = 0;
       CKF(cudaMalloc(&p, want*sizeof(int)));
       n = want;
     }
     return p;
   }
-  int *A(size_t want) { return get(a, na, want); }
-  int *B(size_t want) { return get(b, nb, want); }
+  int *A(size_t want) { const int d = dev(); return get(a[d], na[d], want); }
+  int *B(size_t want) { const int d = dev(); return get(b[d], nb[d], want); }
 };
-Scratch g_scratch;
+thread_local Scratch g_scratch;
 
 // Copies a strided host rectangle (rows x cols ints) to a dense device buffer.
 void h2d_rect(int *dev, const od_coeff *host, int stride, int rows, int cols) {

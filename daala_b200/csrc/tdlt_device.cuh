@@ -1,5 +1,5 @@
 // Device-side building blocks of the TDLT kernels: the 4-tap lapping filters,
-// the Haar butterfly, the shared-memory tile layouts and the block-edge logic.
+// the Haar butterfly and the mbarrier / TMA wrappers.
 // Hand-written for sm_100a; no dependency beyond the CUDA runtime headers.
 #pragma once
 #include <stdint.h>
@@ -12,7 +12,6 @@ namespace tdlt {
 // Geometry shared by host and device
 // ---------------------------------------------------------------------------
 constexpr int kTile = 32;                    // a tile is 32x32 samples of one plane
-constexpr int kBBytes = kTile*kTile*4;       // 4096, TMA SWIZZLE_128B layout
 constexpr int kMaxPlanes = 4;
 
 // ---------------------------------------------------------------------------
@@ -52,7 +51,7 @@ __device__ __forceinline__ void post4(int &y0, int &y1, int &y2, int &y3) {
   // (t*64)/75 and (t*64)/85, C division (truncating), as one multiply-high each:
   // trunc(t*64/d) = floor(t*M/2^32) + (t < 0) with M = ceil(2^38/d), exact for
   // |t| < 2^25, the range in which the reference's own t*64 does not overflow
-  // (checked exhaustively on the host, tests/test_lifting_header.py).
+  // (checked exhaustively on the host, tests/test_cabi_and_host.py::test_post_filter_division_is_exact).
   t3 = __mulhi(t3, kPostM75) + t3 + (int)((unsigned)t3 >> 31);
   t2 = __mulhi(t2, kPostM85) + t2 + (int)((unsigned)t2 >> 31);
   t0 += t3 >> 1;
@@ -72,16 +71,6 @@ __device__ __forceinline__ void haar2x2(int &ll, int &lh, int &hl, int &hh) {
   hl = m - hl;
   ll -= lh;
   hh += hl;
-}
-
-// ---------------------------------------------------------------------------
-// Tile layout B: 32x32 words in the TMA SWIZZLE_128B pattern (16-byte chunk index
-// XOR row&7; the buffer is 1024-byte aligned) -- conflict free for 128-bit row
-// accesses by 8 consecutive rows AND for column-wise accesses, and exactly what a
-// TMA tile load / store produces / consumes.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ int b_off(int r, int c) {
-  return r*32 + ((((c >> 2) ^ (r & 7)) << 2) | (c & 3));
 }
 
 // ---------------------------------------------------------------------------
@@ -111,15 +100,6 @@ __device__ __forceinline__ void mbar_wait(void *bar, int parity) {
       "DONE_%=:\n"
       "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-// Barrier `id` (1..15) among `nthreads` threads (whole warps) of the CTA.
-__device__ __forceinline__ void bar_sync_named(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
-}
-// Non-blocking arrival at barrier `id`, which completes when `nthreads` threads have
-// arrived (bar.arrive) or are waiting (bar.sync).
-__device__ __forceinline__ void bar_arrive_named(int id, int nthreads) {
-  asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
-}
 // 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16),
 // completing on `bar`.
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, int bytes, void *bar) {
@@ -136,18 +116,4 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, void *b
       :: "r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
       : "memory");
 }
-__device__ __forceinline__ void tma_store_3d(const void *tmap, const void *src,
-                                             int x, int y, int z) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-      :: "l"(tmap), "r"(smem_u32(src)), "r"(x), "r"(y), "r"(z) : "memory");
-}
-__device__ __forceinline__ void tma_store_commit_and_wait_read() {
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async_smem() {
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-
 }  // namespace tdlt

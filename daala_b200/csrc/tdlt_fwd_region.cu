@@ -5,7 +5,7 @@
 // One CTA per 128x64 region of one plane; see tdlt_region.cuh for the layout
 // and the task vocabulary.  A region needs only INPUT samples from its
 // neighbours (a 2-sample ring), so regions are independent.  Everything happens
-// in place in one shared-memory buffer: TMA load with halo -> lapping ->
+// in place in one shared-memory buffer: TMA load with halo -> lapping (one pass) ->
 // transforms -> DC pyramid -> 16-byte stores.
 #include <cuda.h>
 #include "tdlt_tasks.cuh"
@@ -48,17 +48,11 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 2);
 
   if (!haar) {
-    // ---- lapping, level by level, coarse to fine (level 4 is done in registers
+    // ---- lapping of the levels superblock .. 8, one pass (level 4 is done in registers
     // by the transform tasks of the units it concerns) ---------------------------
     if (!(TDLT_ABLATE & 1)) {
-      const int sb = 32 >> pd.dec;
-#pragma unroll 1
-      for (int lv = sb; lv >= 8; lv >>= 1) {
-        region_lap_cols<false>(s.A, s.msk, lv, sb, warp, lane);
-        __syncthreads();
-        region_lap_rows<false>(s.A, s.msk, lv, sb, warp, lane, false);
-        __syncthreads();
-      }
+      region_lap_pass<false>(s.A, s.ub, s.msk, kCellsFwd, warp, lane);
+      __syncthreads();
     }
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 4);
     // ---- transforms, in place: columns first, then rows (src/dct.c:137-142) ----

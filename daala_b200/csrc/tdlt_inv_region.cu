@@ -11,8 +11,9 @@
 // X0-2..X0+125, a whole number of lapping cells -- and needs the two bottom
 // rows / right columns of raw iDCT output of its upper / left / upper-left
 // neighbours.  Every region publishes those strips to global memory as 8-byte
-// (sample, epoch) pairs -- an aligned 8-byte store is indivisible, so a reader
-// that sees the epoch of this launch has the sample too: no flag, no fence --
+// (sample, epoch) pairs -- one aligned 64-bit scalar store each, which is single-copy
+// atomic, so a reader that sees the epoch of this launch has the sample too: no flag,
+// no fence --
 // and consumers take the pairs of regions that precede them in a TICKET order
 // (CTAs draw tickets in the order they start running, so a region only ever
 // waits on work that is already resident: no deadlock).  The tickets walk the
@@ -22,7 +23,7 @@
 //
 // Phases: ticket, TMA box + plan record, ring fetch | DC pyramid top-down |
 // inverse transforms in place (class-sorted warp tasks) | publish | un-lapping of
-// the levels 8 .. superblock fused with the store (unlap_block_store).
+// the levels 8 .. superblock in one pass (region_lap_pass) | store of the owned rectangle.
 #include "tdlt_tasks.cuh"
 #include "tdlt_region.cuh"
 #include "tdlt_kernels.h"
@@ -31,13 +32,16 @@ namespace tdlt {
 
 constexpr int kStripInts = 2*kRegW + 2*kRegH;   // bottom rows 62, 63; right columns 126, 127
 
+// One (sample, epoch) pair travels as ONE 64-bit scalar access: a naturally aligned
+// b64 access is single-copy atomic in the PTX memory model (a v2.b32 access is formally two).
 __device__ __forceinline__ int2 ld_pair(const int2 *p) {
-  int2 v;
-  asm volatile("ld.volatile.global.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
-  return v;
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return make_int2((int)(unsigned)v, (int)(unsigned)(v >> 32));
 }
 __device__ __forceinline__ void st_pair(int2 *p, int sample, int epoch) {
-  asm volatile("st.volatile.global.v2.s32 [%0], {%1, %2};" :: "l"(p), "r"(sample), "r"(epoch) : "memory");
+  const unsigned long long v = (unsigned long long)(unsigned)sample | ((unsigned long long)(unsigned)epoch << 32);
+  asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
 // The two samples of the ring this thread is responsible for (threads 0..193):
@@ -158,8 +162,12 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
     if (tile_on) {
       region_haar_tile<true>(At, lane, sb);
       int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + 32*ty)*pd.w + X0 + 32*tx;
-#pragma unroll 1
-      for (int r = 0; r < 32; r++) g[(size_t)r*pd.w + lane] = At[r*kAP + lane];
+      int *gq = g + (size_t)(lane >> 3)*pd.w + 4*(lane & 7);
+      const int *aq = At + (lane >> 3)*kAP + 4*(lane & 7);
+#pragma unroll
+      for (int it = 0; it < 8; it++) {      // 4 rows of 128 bytes per warp instruction
+        *reinterpret_cast<int4 *>(gq + (size_t)(4*it)*pd.w) = *reinterpret_cast<const int4 *>(aq + 4*it*kAP);
+      }
     }
     return;
   }
@@ -292,12 +300,10 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   __syncthreads();      // the ring is in A, and the strips were read before anyone laps them
   TDLT_MARK(t, 6);
 
-  // ---- un-lap (levels 8 .. superblock) and store the owned rectangle, one phase ----
-  // buffer row b <-> plane row Y0 - 2 + b.  Owned: buffer rows b0 .. b1-1 and region
-  // columns cs .. ce-1 (cs = -2, or 0 in the first region column; ce = 126, or where the
-  // plane ends).  One warp task = one row of 4x4 blocks of the offset grid
-  // (unlap_block_store, tdlt_region.cuh); where the plane ends in this region the
-  // blocks holding columns 126, 127 make one more task.
+  // ---- un-lap (levels 8 .. superblock) in one pass, in place (region_lap_pass), then the
+  // owned rectangle goes out row by row (region_store_owned).  buffer row b <-> plane row
+  // Y0 - 2 + b.  Owned: buffer rows b0 .. b1-1 and region columns cs .. ce-1 (cs = -2, or 0
+  // in the first region column; ce = 126, or where the plane ends).
   const bool last_r = Y0 + kRegH >= pd.h, last_c = X0 + kRegW >= pd.w;
   TDLT_MARK(t, 7);
   {
@@ -305,18 +311,10 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
     const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
     const int cs = (id.rx > 0) ? -2 : 0;
     const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
-    const int nbi = (b1 + 3) >> 2;
     int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
-    // even block rows carry filters of both directions, odd ones of one: warp w takes
-    // the rows w and 15 - w (one of each), then 16 + w
-#pragma unroll 1
-    for (int k = 0; k < 3; k++) {
-      const int bi = k == 0 ? warp : (k == 1 ? 15 - warp : 16 + warp);
-      if (bi < nbi) unlap_block_store<true>(s.A, s.ub, sb, bi, lane, true, g, (size_t)pd.w, b0, b1, cs, ce);
-    }
-    if (ce > kRegW - 2 && warp == kRegWarps - 1) {
-      unlap_block_store<false>(s.A, s.ub, sb, lane, 32, lane < nbi, g, (size_t)pd.w, b0, b1, cs, ce);
-    }
+    if (!(TDLT_ABLATE & 1)) region_lap_pass<true>(s.A, s.ub, s.msk, last_r ? kCellsFwd : kCellsInv, warp, lane);
+    __syncthreads();
+    if (!(TDLT_ABLATE & 128)) region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
   }
   TDLT_MARK(t, 8);
 }

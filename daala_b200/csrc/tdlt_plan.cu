@@ -84,7 +84,6 @@ tdlt_plan_kernel(const __grid_constant__ RegionBatch bd, const unsigned char *__
       unsigned char *ub = rec[k] + (kOffUb - kOffLs);
       unsigned char *tasks = rec[k] + (kOffTasks - kOffLs);
       int *cnt = reinterpret_cast<int *>(rec[k] + (kOffCnt - kOffLs));
-      unsigned *msk = reinterpret_cast<unsigned *>(rec[k] + (kOffMsk - kOffLs));
       int L = 0xFF, bits = 0, which = -1;
       if (inside[k]) {
         L = haar ? 3 : max(raw[k], dec) - dec;
@@ -117,11 +116,18 @@ tdlt_plan_kernel(const __grid_constant__ RegionBatch bd, const unsigned char *__
       if (active) {
         ls[r*kUS + c] = (unsigned char)L;
         ub[r*kUS + c] = (unsigned char)bits;
-        if (bits & kUbTop) atomicOr(msk + r, 1u << c);
-        if (bits & kUbLeft) atomicOr(msk + 10 + r, 1u << c);
       }
       list_push4(tasks, kTaskListStride, cnt + 4, which, (unsigned char)((UR << 4) | UC), lane);
     }
+  }
+  // the order of the two filter directions at the crossing of row line 8*iu and column line
+  // 8*ju (region_lap_pass): bit ju of word iu = the row line is at least as coarse
+  if (tid < kRegUY + 1) {
+    const int li = lap_level8(tid, sb);
+    unsigned m = 0;
+#pragma unroll
+    for (int ju = 0; ju <= kRegUX; ju++) m |= (unsigned)(li >= lap_level8(ju, sb)) << ju;
+    for (int k = 0; k < nreg; k++) reinterpret_cast<unsigned *>(rec[k] + (kOffMsk - kOffLs))[tid] = m;
   }
   __syncthreads();
   int4 *dst = reinterpret_cast<int4 *>(

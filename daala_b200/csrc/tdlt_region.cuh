@@ -6,11 +6,11 @@
 // first sorted into lists of equal-shaped tasks, so that every warp instruction
 // runs the same code on 32 busy lanes whatever the block-size map looks like:
 //
-//   lapping    block-wide phases, one per (level, direction), levels = the edge
-//              alignments superblock / 16 / 8; a lane filters four columns of
-//              one edge line (int4 per row) or one row of two edge lines; which
-//              edges are filtered is a bit test against per-unit-row masks.
-//              Level 4 (mid-edges of a unit split into 4x4) is filtered in
+//   lapping    the levels superblock / 16 / 8 in ONE barrier-free pass over the 4x4 blocks
+//              of the grid offset by (2, 2) (region_lap_pass below): cell tasks (lane =
+//              a crossing of two 8-lines, its block and the half blocks either side on
+//              the row line) and edge tasks (lane = one row of a column line between
+//              crossings).  Level 4 (mid-edges of a unit split into 4x4) is filtered in
 //              registers by the transform task of that unit.
 //   transforms class 0: an 8x8 unit split into four 4x4 blocks  (2 lanes)
 //              class 1: an 8x8 block                            (2 lanes)
@@ -25,7 +25,7 @@
 //       odd number, so that 8 consecutive rows of one chunk column fall in 8
 //       different bank groups -- for 16-byte accesses along a row AND down a
 //       column, so the two passes of every transform run in place in A)
-//   unit tables (leaf size, edge bits), edge masks, task lists, counters.
+//   unit tables (leaf size, edge bits), crossing-order masks, task lists, counters.
 #pragma once
 #include "tdlt_device.cuh"
 #include "tdlt_tasks.cuh"
@@ -77,7 +77,7 @@ constexpr int kOffUb = kOffLs + kUTab;                   // unit edge bits
 constexpr int kOffTasks = kOffUb + kUTab;
 constexpr int kTaskListStride = 128;                     // bytes per class list
 constexpr int kOffCnt = kOffTasks + 4*kTaskListStride;   // 8 ints, [4..7] = class counts
-constexpr int kOffMsk = kOffCnt + 32;                    // 2 x 10 edge masks, right after cnt
+constexpr int kOffMsk = kOffCnt + 32;                    // 9 crossing-order masks (20 words reserved)
 constexpr int kOffBar = kOffMsk + 80;
 constexpr int kPlanBytes = kOffBar - kOffLs;
 #ifndef TDLT_PLAN_PER_CTA
@@ -140,7 +140,7 @@ struct RegionSmem {
   unsigned char *ub;      // edge bits per unit (kUb*)
   unsigned char *tasks;   // 4 lists
   int *cnt;               // [4..7] task classes
-  unsigned *msk;          // [r]: bit c = unit (r-1, c-1) has kUbTop; [10 + r]: kUbLeft
+  unsigned *msk;          // [iu]: bit ju = row line 8*iu is at least as coarse as column line 8*ju
   unsigned long long *bar;
   int *dyn;               // [0] ticket (inverse), [1] task draw counter
 };
@@ -209,128 +209,14 @@ __device__ __forceinline__ void list_push4(T *lists, int stride, int *cnt, int w
 // Level 4 (the mid-edges of units split into 4x4 blocks) never leaves its unit
 // and is filtered in registers by the transform task of that unit (lap4_unit
 // below), so the phases here run over the levels 8 .. superblock only.
-template <bool kInverse>
-__device__ __forceinline__ void lap_chunk(int *A, int yl, int m) {
-  int4 *p = reinterpret_cast<int4 *>(A + yl*kAP + 4*m);   // buffer row yl = region row yl - 2
-  constexpr int S = kAP/4;
-  int4 r0 = p[0], r1 = p[S], r2 = p[2*S], r3 = p[3*S];
-  if (kInverse) {
-    post4(r0.x, r1.x, r2.x, r3.x); post4(r0.y, r1.y, r2.y, r3.y);
-    post4(r0.z, r1.z, r2.z, r3.z); post4(r0.w, r1.w, r2.w, r3.w);
-  }
-  else {
-    pre4(r0.x, r1.x, r2.x, r3.x); pre4(r0.y, r1.y, r2.y, r3.y);
-    pre4(r0.z, r1.z, r2.z, r3.z); pre4(r0.w, r1.w, r2.w, r3.w);
-  }
-  p[0] = r0; p[S] = r1; p[2*S] = r2; p[3*S] = r3;
-}
-
-// Block-wide phases: one (level, direction) at a time, a barrier between phases.
-// Which edges are filtered comes from the per-unit-row bit masks s.msk.
-// Columns: a warp takes one line, lane = chunk 1 + lane (region columns 4*lane
-// ..).  The chunks outside 1..32 (0: the two columns left of the region; 33:
-// forward, superblock level, the two right of it) go to one extra partial warp
-// task.
-template <bool kInverse>
-__device__ __forceinline__ void region_lap_cols(int *A, const unsigned *msk, int lv, int sb,
-                                                int warp, int lane) {
-  const bool top = lv == sb;
-  const int lg = 31 - __clz(lv);                            // lv and sb are powers of two
-  const int nlines = top ? (kRegH >> lg) + (kInverse ? 0 : 1) : (kRegH/2) >> lg;
-  const int first = top ? 0 : lv, step = top ? sb : 2*lv;
-  const int nextra = kInverse ? 1 : (top ? 2 : 0);         // extra chunks per line
-  // one call site for both kinds of task (the filter code is inlined once)
-  int yl = 0, m = 0;
-  bool on = false;
-  if (warp < nlines) {
-    yl = first + warp*step;
-    m = lane + 1;
-    // chunk m = lane + 1 lies in unit column lane >> 1, mask bit (lane >> 1) + 1
-    on = (msk[(yl >> 3) + 1] >> ((lane >> 1) + 1)) & 1;
-  }
-  else if (warp == nlines && nextra) {
-    const int line = lane >> 1;
-    m = (lane & 1) ? 33 : 0;
-    yl = first + line*step;
-    on = lane < 2*nlines && (lane & 1) < nextra &&
-         ((msk[(yl >> 3) + 1] >> ((lane & 1) ? 17 : 0)) & 1);
-  }
-  if (on) lap_chunk<kInverse>(A, yl, m);
-}
-
-// Rows: warp w takes the rows 32*(w & 1) .. +31 and the line pairs w >> 1, +4,
-// .. (two independent filter chains per lane).  Forward: region rows 0..63.
-// Inverse: region rows -2..61, and where the plane ends 62..63 as well (warp 0,
-// lanes 0 and 1, in a second sweep).
-template <bool kInverse>
-__device__ __forceinline__ void lap_row_pair(int *arow, unsigned m, int ja, int jb, bool hasb) {
-  bool ona = (m >> (ja + 1)) & 1;
-  bool onb = hasb && ((m >> (jb + 1)) & 1);
-  int2 *pa = reinterpret_cast<int2 *>(arow + 8*ja + 2);   // region columns 8j-2 .. 8j+1
-  int2 *pb = reinterpret_cast<int2 *>(arow + 8*jb + 2);
-  int2 la, ha, lb, hb;
-  if (ona) { la = pa[0]; ha = pa[1]; }
-  if (onb) { lb = pb[0]; hb = pb[1]; }
-  if (ona) {
-    if (kInverse) post4(la.x, la.y, ha.x, ha.y); else pre4(la.x, la.y, ha.x, ha.y);
-  }
-  if (onb) {
-    if (kInverse) post4(lb.x, lb.y, hb.x, hb.y); else pre4(lb.x, lb.y, hb.x, hb.y);
-  }
-  if (ona) { pa[0] = la; pa[1] = ha; }
-  if (onb) { pb[0] = lb; pb[1] = hb; }
-}
-template <bool kInverse>
-__device__ __forceinline__ void region_lap_rows(int *A, const unsigned *msk, int lv, int sb,
-                                                int warp, int lane, bool last_row,
-                                                int nw = kRegWarps) {
-  const bool top = lv == sb;
-  const int lg = 31 - __clz(lv);
-  const int nlines = top ? (kRegW >> lg) + (kInverse ? 0 : 1) : (kRegW/2) >> lg;
-  const int jfirst = top ? 0 : lv >> 3, jstep = top ? sb >> 3 : lv >> 2;
-  // work item i = (line pair i >> 1, upper / lower 32 rows i & 1), dealt to nw warps
-#pragma unroll 1
-  for (int i = warp; i < ((nlines + 1) & ~1); i += nw) {
-    const int row = 32*(i & 1) + lane + (kInverse ? 0 : 2);     // buffer row = region row + 2
-    const unsigned m = msk[10 + ((row - 2) >> 3) + 1];
-    int ja = jfirst + (i & ~1)*jstep;
-    lap_row_pair<kInverse>(A + row*kAP, m, ja, ja + jstep, (i | 1) < nlines);
-  }
-  if (kInverse && last_row && warp == 0 && lane < 2) {
-    int *arow2 = A + (64 + lane)*kAP;
-    const unsigned m2 = msk[10 + 8];
-#pragma unroll 1
-    for (int pr = 0; 2*pr < nlines; pr++) {
-      int ja = jfirst + 2*pr*jstep;
-      lap_row_pair<kInverse>(arow2, m2, ja, ja + jstep, 2*pr + 1 < nlines);
-    }
-  }
-}
-
 // Level of the line at coordinate 8k: the largest power of two dividing it, capped at
 // the superblock size.
 __device__ __forceinline__ int lap_level8(int k, int sb) {
   int c = 8*k;
   return (c & (sb - 1)) == 0 ? sb : (c & -c);
 }
-// ---------------------------------------------------------------------------
-// Inverse tail: the un-lapping of the levels 8 .. superblock AND the store of the
-// region's owned rectangle as one barrier-free phase.  The owned rectangle (region rows
-// -2 .. 61, columns -2 .. 125) is tiled exactly by the 4x4 blocks of the grid offset by
-// (2, 2) -- block (bi, bj) = buffer rows 4bi .. 4bi+3, region columns 4bj-2 .. 4bj+1 --
-// and every filter lies inside one block, so a lane takes one block from shared memory
-// into registers, undoes the filters that cross it (a CELL up to four along its rows
-// and four down its columns, HF / VF blocks four of one direction, the inside of a unit
-// none) and stores the 16 samples straight to global memory: the buffer is only read,
-// nothing is written back, no barrier separates the levels.
-// A warp task is one block row (bi uniform, lane = bj): the lanes' 8-byte pieces of one
-// row form one contiguous run of 512 bytes.
-// The inverse undoes the forward order backwards: at a crossing the filters of the
-// finer line first, and on a tie those along the rows (across the vertical edge)
-// first.  The code below always runs "down the columns, then along the rows"; a lane
-// that needs the other order works on the transposed block (12 selects each way, much
-// cheaper than a second copy of the four filters).
-// ---------------------------------------------------------------------------
+// Transposes a 4x4 register block when t (12 selects): used where a lane needs the two
+// filter directions in the other order than the code runs them.
 __device__ __forceinline__ void transpose4_if(int (&x)[4][4], bool t) {
 #pragma unroll
   for (int r = 0; r < 4; r++) {
@@ -342,98 +228,141 @@ __device__ __forceinline__ void transpose4_if(int (&x)[4][4], bool t) {
     }
   }
 }
-// g -> plane sample (Y0 - 2, X0 - 2), i.e. buffer row 0 / region column -2 (may lie
-// before the plane: such pieces are never stored).  Stored: buffer rows b0 .. b1-1,
-// region columns cs .. ce-1.
-// kRow: called by a whole warp for one block row (bi uniform, bj = lane).  The block of
-// lane j holds region columns 4j-2 .. 4j+1, which is 8 bytes off the 16-byte grid, so
-// every lane fetches the left half of its right neighbour's block by shuffle and the
-// row goes out as ONE run of 16-byte vectors (columns 4j .. 4j+3: whole 32-byte
-// sectors) plus one 8-byte piece at either end (lane 0: columns -2, -1; lane 31: 124,
-// 125).  !kRow: any lane, any block, only the left half (columns 4bj-2, 4bj-1) is
-// stored -- the blocks holding columns 126, 127 where the plane ends.
-template <bool kRow>
-__device__ __forceinline__ void unlap_block_store(const int *A, const unsigned char *ub, int sb,
-                                                  int bi, int bj, bool on, int *g, size_t pitch,
-                                                  int b0, int b1, int cs, int ce) {
-  const bool ei = !(bi & 1), ej = !(bj & 1);
-  const int iu = bi >> 1, ju = bj >> 1;
-  int x[4][4];
-  // which filters cross the block: bit 0 down its left two columns, 1 its right two,
-  // 2 along its upper two rows, 3 its lower two
-  unsigned f = 0;
-  bool tr = false;
-  if (on) {
-    const int2 *p = reinterpret_cast<const int2 *>(A + 4*bi*kAP + 4*bj + 2);
-    constexpr int S = kAP/2;
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-      int2 l = p[r*S];
-      x[r][0] = l.x; x[r][1] = l.y;
-      if (kRow) {
-        int2 h = p[r*S + 1];
-        x[r][2] = h.x; x[r][3] = h.y;
-      }
-    }
-    if (!(TDLT_ABLATE & 1)) {
-      const unsigned char *u = ub + ut(iu, ju);
-      const unsigned u0 = u[0];
-      const unsigned uc = ej ? u[-1] : u0;        // cell: the unit left of the crossing
-      static_assert(kUbTop == 1 && kUbLeft == 2, "bit positions used below");
-      if (ei) f = uc & 1;
-      if (kRow) {
-        const unsigned ur = ei ? u[-kUS] : u0;    // cell: the unit above it
-        if (ei) f |= (u0 & 1) << 1;
-        if (ej) f |= ((ur & 2) << 1) | ((u0 & 2) << 2);
-        // forward: the coarser line first, the horizontal edge on a tie; so the inverse
-        // starts along the rows iff the row line is at least as coarse as the column line
-        tr = ei && ej && lap_level8(iu, sb) >= lap_level8(ju, sb);
-      }
+// ---------------------------------------------------------------------------
+// One-pass lapping of the levels 8 .. superblock: every 4-tap
+// filter of those levels lies inside ONE 4x4 block of the grid offset by (2, 2), so all
+// of them can run in a single barrier-free pass, each block taken into registers, its
+// filters applied in the reference's order, and written back.  Two kinds of warp task,
+// both with whole-warp conflict-poor shared-memory access:
+//   cell task  lane = the crossing (iu, ju) of row line 8*iu and column line 8*ju (iu in
+//              0..8, ju in 0..16, 17 per row line).  The lane takes the two 16-byte chunks
+//              around the crossing, buffer rows 8*iu .. +3 (region rows 8*iu-2 .. +1),
+//              region columns 8*ju-4 .. 8*ju+3: the crossing's own 4x4 block in the middle
+//              (filters of both directions, order by level) and, either side, half of the
+//              blocks that only the horizontal edge crosses (filters down the columns).
+//   edge task  lane = one row of one column line between two crossings (region rows
+//              8*iu+2 .. +5, columns 8*ju-2 .. +1): one filter along the row; two column
+//              lines and two units per lane pair up so that a half warp spreads over all
+//              the 8-byte bank pairs its rows can reach.
+// The forward pass needs the crossings 0..8 x 0..16 (its far sides are recomputed from the
+// halo); the inverse owns 0..7 x 0..15, plus column-line 16's left half (columns 124, 125
+// belong to it) and row line 8 where the plane ends.
+// Order inside a crossing (src/filter.c:1493-1508, 1567-1584; src/encode.c:1311-1327):
+// forward, the coarser line first and on a tie the filters down the columns (across the
+// horizontal edge); the inverse backwards.  trm[iu] bit ju = level(row line iu) >=
+// level(column line ju) (tdlt_plan.cu).  The code always runs "down the columns, then
+// along the rows"; a lane that needs the other order works on the transposed block.
+// ---------------------------------------------------------------------------
+template <bool kInverse>
+__device__ __forceinline__ void filt4(int &a, int &b, int &c, int &d) {
+  if (kInverse) post4(a, b, c, d); else pre4(a, b, c, d);
+}
+constexpr int kCellsPerLine = kRegUX + 1;              // 17
+constexpr int kCellsFwd = (kRegUY + 1)*kCellsPerLine;  // 153
+constexpr int kCellsInv = kRegUY*kCellsPerLine;        // 136 (153 where the plane ends below)
+constexpr int kCellTasks = (kCellsFwd + 31)/32;        // 5
+constexpr int kEdgeTasksFwd = 9, kEdgeTasksInv = 8;
+
+template <bool kInverse>
+__device__ __forceinline__ void lap_cell_task(int *A, const unsigned char *ub, const unsigned *trm,
+                                              int idx, int ncells) {
+  if (idx >= ncells) return;
+  const int iu = (idx*241) >> 12, ju = idx - kCellsPerLine*iu;     // idx / 17, exact below 2^11
+  const unsigned char *u = ub + ut(iu, ju);
+  const unsigned u0 = u[0], ul = u[-1], ua = u[-kUS];
+  static_assert(kUbTop == 1 && kUbLeft == 2, "bit positions used below");
+  // bit 0: filters down the columns 0..3 of the eight (the unit left of the crossing has its
+  // top edge filtered), 1: columns 4..7, 2: along the rows 0, 1 of the crossing's block (the
+  // unit above has its left edge filtered), 3: rows 2, 3
+  unsigned f = (ul & 1) | ((u0 & 1) << 1) | ((ua & 2) << 1) | ((u0 & 2) << 2);
+  if (kInverse && ju == kRegUX) f &= 1;     // column line 16 is the next region's: only 124, 125
+  if (!f) return;
+  const bool both = (f & 3) && (f & 12);
+  const bool tr = both && ((((trm[iu] >> ju) & 1) != 0) == kInverse);
+#ifdef TDLT_FAKE_CELLS
+  int4 *p = reinterpret_cast<int4 *>(A + 8*iu*kAP + 4*(idx & 31));   // timing experiment: conflict-free, wrong
+#else
+  int4 *p = reinterpret_cast<int4 *>(A + 8*iu*kAP + 8*ju);
+#endif
+  constexpr int S = kAP/4;
+  int4 L0 = p[0], R0 = p[1], L1 = p[S], R1 = p[S + 1];
+  int4 L2 = p[2*S], R2 = p[2*S + 1], L3 = p[3*S], R3 = p[3*S + 1];
+  if (f & 1) { filt4<kInverse>(L0.x, L1.x, L2.x, L3.x); filt4<kInverse>(L0.y, L1.y, L2.y, L3.y); }
+  if (f & 2) { filt4<kInverse>(R0.z, R1.z, R2.z, R3.z); filt4<kInverse>(R0.w, R1.w, R2.w, R3.w); }
+  int x[4][4] = {{L0.z, L0.w, R0.x, R0.y}, {L1.z, L1.w, R1.x, R1.y},
+                 {L2.z, L2.w, R2.x, R2.y}, {L3.z, L3.w, R3.x, R3.y}};
+  const unsigned g = tr ? ((f & 3) << 2) | (f >> 2) : f;   // on the transposed block rows and columns swap
+  transpose4_if(x, tr);
+  if (g & 1) { filt4<kInverse>(x[0][0], x[1][0], x[2][0], x[3][0]); filt4<kInverse>(x[0][1], x[1][1], x[2][1], x[3][1]); }
+  if (g & 2) { filt4<kInverse>(x[0][2], x[1][2], x[2][2], x[3][2]); filt4<kInverse>(x[0][3], x[1][3], x[2][3], x[3][3]); }
+  if (g & 4) { filt4<kInverse>(x[0][0], x[0][1], x[0][2], x[0][3]); filt4<kInverse>(x[1][0], x[1][1], x[1][2], x[1][3]); }
+  if (g & 8) { filt4<kInverse>(x[2][0], x[2][1], x[2][2], x[2][3]); filt4<kInverse>(x[3][0], x[3][1], x[3][2], x[3][3]); }
+  transpose4_if(x, tr);
+  p[0] = make_int4(L0.x, L0.y, x[0][0], x[0][1]);       p[1] = make_int4(x[0][2], x[0][3], R0.z, R0.w);
+  p[S] = make_int4(L1.x, L1.y, x[1][0], x[1][1]);       p[S + 1] = make_int4(x[1][2], x[1][3], R1.z, R1.w);
+  p[2*S] = make_int4(L2.x, L2.y, x[2][0], x[2][1]);     p[2*S + 1] = make_int4(x[2][2], x[2][3], R2.z, R2.w);
+  p[3*S] = make_int4(L3.x, L3.y, x[3][0], x[3][1]);     p[3*S + 1] = make_int4(x[3][2], x[3][3], R3.z, R3.w);
+}
+
+// Edge task v: v < 8 -> column lines j0 and j0 + 2, j0 = 4*(v >> 1) + (v & 1), lane = (row k of
+// the four, which line, unit iu in 0..3) and the same for unit iu + 4; v == 8 (forward only)
+// -> column line 16, lane = (k, iu in 0..7).
+template <bool kInverse>
+__device__ __forceinline__ void lap_edge_task(int *A, const unsigned char *ub, int v, int lane) {
+  const int k = lane & 3;
+  const bool two = v < 8;
+  const int ju = two ? ((v >> 1) << 2) + (v & 1) + ((lane >> 1) & 2) : kRegUX;
+  const int iua = two ? lane >> 3 : lane >> 2;
+  const bool ona = (ub[ut(iua, ju)] & kUbLeft) != 0;
+  const bool onb = two && (ub[ut(iua + 4, ju)] & kUbLeft) != 0;
+  int2 *pa = reinterpret_cast<int2 *>(A + (8*iua + 4 + k)*kAP + 8*ju + 2);   // region columns 8ju-2 .. +1
+  int2 *pb = pa + 32*kAP/2;                                                  // the unit four rows of units below
+  int2 la, ha, lb, hb;
+  if (ona) { la = pa[0]; ha = pa[1]; }
+  if (onb) { lb = pb[0]; hb = pb[1]; }
+  if (ona) filt4<kInverse>(la.x, la.y, ha.x, ha.y);
+  if (onb) filt4<kInverse>(lb.x, lb.y, hb.x, hb.y);
+  if (ona) { pa[0] = la; pa[1] = ha; }
+  if (onb) { pb[0] = lb; pb[1] = hb; }
+}
+
+// The whole pass, called by all warps of the CTA; the caller puts a block barrier either
+// side.  ncells: kCellsFwd, or kCellsInv (inverse; kCellsFwd where the plane ends below).
+template <bool kInverse>
+__device__ __forceinline__ void region_lap_pass(int *A, const unsigned char *ub, const unsigned *trm,
+                                                int ncells, int warp, int lane) {
+  if (warp < kCellTasks) {
+    lap_cell_task<kInverse>(A, ub, trm, 32*warp + lane, ncells);
+  }
+  else {
+    constexpr int nv = kInverse ? kEdgeTasksInv : kEdgeTasksFwd;
+#pragma unroll 1
+    for (int v = warp - kCellTasks; v < nv; v += kRegWarps - kCellTasks) {
+      lap_edge_task<kInverse>(A, ub, v, lane);
     }
   }
-  const bool colL0 = f & 1;
-  if (!kRow) {
-    // beyond the plane's last unit column nothing crosses the block along its rows
-    if (colL0) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
-    if (on && !(TDLT_ABLATE & 128) && 4*bj - 2 < ce) {
-      int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
-#pragma unroll
-      for (int r = 0; r < 4; r++) {
-        const int b = 4*bi + r;
-        if (b >= b0 && b < b1) *reinterpret_cast<int2 *>(gp + r*pitch) = make_int2(x[r][0], x[r][1]);
-      }
-    }
-    return;
-  }
-  if (tr) f = ((f & 3) << 2) | (f >> 2);       // on the transposed block rows and columns swap
-  if (ei) transpose4_if(x, tr);                // (bi is warp-uniform here: odd rows skip it)
-  const bool colL = f & 1, colR = f & 2, rowT = f & 4, rowB = f & 8;
-  if (colL) { post4(x[0][0], x[1][0], x[2][0], x[3][0]); post4(x[0][1], x[1][1], x[2][1], x[3][1]); }
-  if (colR) { post4(x[0][2], x[1][2], x[2][2], x[3][2]); post4(x[0][3], x[1][3], x[2][3], x[3][3]); }
-  if (rowT) { post4(x[0][0], x[0][1], x[0][2], x[0][3]); post4(x[1][0], x[1][1], x[1][2], x[1][3]); }
-  if (rowB) { post4(x[2][0], x[2][1], x[2][2], x[2][3]); post4(x[3][0], x[3][1], x[3][2], x[3][3]); }
-  if (ei) transpose4_if(x, tr);
-  {
-    // columns 4bj .. 4bj+3 are all mine and the right half is in the warp (lane 31's is
-    // not: where the plane ends there, columns 126, 127 are the extra task's)
-    const bool full = 4*bj + 3 < ce && bj < 31;
-    // the 8-byte pieces: lane 0 its left half (if the region owns columns -2, -1), the
-    // lane whose right neighbour is beyond ce its right half
-    const bool pl = bj == 0 && cs < 0, ph = !full && 4*bj + 1 < ce;
-    int *gp = g + (size_t)(4*bi)*pitch + 4*bj;
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-      const int n0 = __shfl_down_sync(0xffffffffu, x[r][0], 1);
-      const int n1 = __shfl_down_sync(0xffffffffu, x[r][1], 1);
-      const int b = 4*bi + r;
-      if (b >= b0 && b < b1 && !(TDLT_ABLATE & 128)) {
-        if (full) *reinterpret_cast<int4 *>(gp + r*pitch + 2) = make_int4(x[r][2], x[r][3], n0, n1);
-        if (pl | ph) {
-          *reinterpret_cast<int2 *>(gp + r*pitch + (pl ? 0 : 2)) =
-              pl ? make_int2(x[r][0], x[r][1]) : make_int2(x[r][2], x[r][3]);
-        }
-      }
-    }
+}
+
+// Inverse: the owned rectangle goes out after the pass, buffer rows b0 .. b1-1, region
+// columns cs .. ce-1 (cs = -2 or 0; ce = 126, or a multiple of 32 where the plane ends);
+// g -> the plane sample at buffer row 0, region column -2.  A warp takes a row at a time:
+// 16-byte vectors for the columns 0 .. 123 (whole sectors), 8-byte pieces at either end.
+__device__ __forceinline__ void region_store_owned(const int *A, int *g, size_t pitch, int b0, int b1,
+                                                   int cs, int ce, int warp, int lane) {
+  const int c = 4*lane;
+  const bool full = c + 3 < ce, half = !full && c + 1 < ce, left = lane == 0 && cs < 0;
+  const int *arow = A + (b0 + warp)*kAP + 4 + c;       // -> region column c
+  int *grow = g + (size_t)(b0 + warp)*pitch + 2 + c;
+#pragma unroll 2
+  for (int b = b0 + warp; b < b1; b += kRegWarps, arow += kRegWarps*kAP, grow += kRegWarps*pitch) {
+    // (one 16-byte load: left to itself the compiler splits it in two because of the 8-byte
+    // store below, and 8-byte loads at a 16-byte lane stride conflict two ways)
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(arow)));
+    if (full) *reinterpret_cast<int4 *>(grow) = v;
+    if (half) *reinterpret_cast<int2 *>(grow) = make_int2(v.x, v.y);
+    if (left) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
   }
 }
 

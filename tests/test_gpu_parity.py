@@ -653,4 +653,12 @@ def test_device_batches_plan_reuse_and_stress():
         d_ref = chk.fwd_frames([a[:1] for a in c_np], bsize[:1], DECS, 1)
         for p in range(3):
             assert np.array_equal(d[p][0].cpu().numpy(), d_ref[p][0])
+        # the stage is out of place (the reference's callers pass ctmp and dtmp): an in-place
+        # or overlapping call is refused in both directions instead of corrupting silently
+        with pytest.raises(daala_b200.TdltError):
+            ctx.fwd_batch(cp, cp, maps.data_ptr(), nframes, KEY, st)
+        with pytest.raises(daala_b200.TdltError):
+            ctx.inv_batch([x + 64 for x in dp], dp, maps.data_ptr(), nframes, KEY, st)
+        # a context call leaves the caller's current device as it found it
+        assert torch.cuda.current_device() == 0
     chk.close()
