@@ -57,6 +57,8 @@ def lib():
         L.od_tdlt_fwd_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_inv_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_fwd_batch_static.argtypes = [C.POINTER(Geometry), arr, arr, vp, ci, ci, vp]
+        L.od_tdlt_fwd_batch_pix.argtypes = [vp, arr, arr, vp, ci, ci, ci, ci, ci, vp]
+        L.od_tdlt_inv_batch_pix.argtypes = [vp, arr, arr, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_pix_to_coeff_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_coeff_to_pix_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_cfl_pred_batch.argtypes = [vp, vp, vp, vp, ci, vp]
@@ -70,6 +72,8 @@ def lib():
         L.od_tdlt_set_scan_tables.argtypes = [vp, arr, C.POINTER(ci)]
         L.od_tdlt_coding_order_batch.argtypes = [vp, arr, arr, vp, ci, ci, vp]
         L.od_tdlt_coding_order_frames.argtypes = [vp, arr, arr, vp, ci, ci]
+        L.od_tdlt_host_register.argtypes = [vp, C.c_size_t]
+        L.od_tdlt_host_unregister.argtypes = [vp]
         L.od_tdlt_fwd_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         L.od_tdlt_inv_frames.argtypes = [vp, arr, arr, vp, ci, ci]
         iarr, larr = C.POINTER(ci), C.POINTER(ll)
@@ -166,6 +170,22 @@ class TdltContext:
     def inv_batch(self, c_ptrs, d_ptrs, bsize_ptr, nframes, flags=0, stream=0):
         self._check(self.L.od_tdlt_inv_batch(self._h, _ptr_array(c_ptrs), _ptr_array(d_ptrs),
                                              bsize_ptr, nframes, flags, stream), "od_tdlt_inv_batch")
+
+    def fwd_batch_pix(self, d_ptrs, pix_ptrs, bsize_ptr, nframes, flags=0, xstride=1, bitdepth_mode=1,
+                      lossless=0, stream=0):
+        """Device pointers: the forward stage straight from planes of 8/16-bit reference-buffer
+        samples (od_ref_buf_to_coeff fused into the load)."""
+        self._check(self.L.od_tdlt_fwd_batch_pix(self._h, _ptr_array(d_ptrs), _ptr_array(pix_ptrs),
+                                                 bsize_ptr, nframes, flags, xstride, bitdepth_mode,
+                                                 lossless, stream), "od_tdlt_fwd_batch_pix")
+
+    def inv_batch_pix(self, pix_ptrs, d_ptrs, bsize_ptr, nframes, flags=0, xstride=1, bitdepth_mode=1,
+                      lossless=0, stream=0):
+        """Device pointers: the inverse stage straight to planes of 8/16-bit reference-buffer
+        samples (od_coeff_to_ref_buf fused into the store)."""
+        self._check(self.L.od_tdlt_inv_batch_pix(self._h, _ptr_array(pix_ptrs), _ptr_array(d_ptrs),
+                                                 bsize_ptr, nframes, flags, xstride, bitdepth_mode,
+                                                 lossless, stream), "od_tdlt_inv_batch_pix")
 
     def cfl_pred_batch(self, l_ptr, d_luma_ptr, bsize_ptr, nframes, stream=0):
         """Device pointers: chroma-from-luma predictor planes (od_tdlt_cfl_pred_batch)."""
@@ -308,6 +328,19 @@ def fwd_batch_static(pic_width, pic_height, decs, d_ptrs, c_ptrs, bsize_ptr, nfr
         g.ydec[i] = d
     return lib().od_tdlt_fwd_batch_static(C.byref(g), _ptr_array(d_ptrs), _ptr_array(c_ptrs),
                                           bsize_ptr, nframes, flags, stream)
+
+
+def host_register(array):
+    """Page-locks a numpy array's memory (od_tdlt_host_register)."""
+    rc = lib().od_tdlt_host_register(array.ctypes.data, array.nbytes)
+    if rc != 0:
+        raise TdltError("od_tdlt_host_register failed: %d" % rc)
+
+
+def host_unregister(array):
+    rc = lib().od_tdlt_host_unregister(array.ctypes.data)
+    if rc != 0:
+        raise TdltError("od_tdlt_host_unregister failed: %d" % rc)
 
 
 def launch_count():

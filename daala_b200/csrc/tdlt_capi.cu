@@ -114,23 +114,25 @@ static encode_tiled_fn get_encode_tiled() {
   return fn;
 }
 
-static bool ranges_overlap(const void *a, const void *b, size_t bytes) {
+static bool ranges_overlap(const void *a, size_t na, const void *b, size_t nb) {
   const uintptr_t x = (uintptr_t)a, y = (uintptr_t)b;
-  return x < y + bytes && y < x + bytes;
+  return x < y + nb && y < x + na;
 }
 
 // 3-D map (x, y, frame) over nframes planes of w x h int32; box bx x by x 1.
 static int make_tmap(od_tdlt_ctx *ctx, CUtensorMap *m, const void *base, int w, int h,
-                     int nframes, int boxw, int boxh, bool swizzle) {
+                     int nframes, int boxw, int boxh, int elem_bytes = 4) {
   encode_tiled_fn enc = get_encode_tiled();
   if (!enc) return fail(ctx, OD_TDLT_EFAULT, "cuTensorMapEncodeTiled unavailable");
   cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
-  cuuint64_t strides[2] = {(cuuint64_t)w*4, (cuuint64_t)w*h*4};
+  cuuint64_t strides[2] = {(cuuint64_t)w*elem_bytes, (cuuint64_t)w*h*elem_bytes};
   cuuint32_t boxd[3] = {(cuuint32_t)boxw, (cuuint32_t)boxh, 1};
   cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, const_cast<void *>(base), dims, strides,
-                   boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+  const CUtensorMapDataType dt = elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                 : (elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16
+                                                    : CU_TENSOR_MAP_DATA_TYPE_INT32);
+  CUresult r = enc(m, dt, 3, const_cast<void *>(base), dims, strides,
+                   boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(ctx, OD_TDLT_EFAULT, "cuTensorMapEncodeTiled failed: %d", (int)r);
   return OD_TDLT_SUCCESS;
@@ -276,6 +278,14 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+    {
+      const void *pixk[4] = {(const void *)tdlt_fwd_region_pix8_kernel, (const void *)tdlt_fwd_region_pix16_kernel,
+                             (const void *)tdlt_inv_region_pix8_kernel, (const void *)tdlt_inv_region_pix16_kernel};
+      for (int k = 0; k < 4; k++) {
+        cudaFuncSetAttribute(pixk[k], cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
+        cudaFuncSetAttribute(pixk[k], cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      }
+    }
     cudaFuncSetAttribute(tdlt_fwd_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     cudaFuncSetAttribute(tdlt_inv_region_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
@@ -376,9 +386,18 @@ static int launch_plan(od_tdlt_ctx *ctx, const RegionBatch &rb, const unsigned c
 }
 
 // ---------------------------------------------------------------- batches --
-int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
-                      const unsigned char *bsize, int nframes, int flags, void *stream) {
-  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+static int conv_shift(int xstride, int bitdepth_mode, int lossless_p) {
+  // reference src/state.c:1221-1223, 1236-1238 (OD_COEFF_SHIFT == 4)
+  if (xstride == 1) return lossless_p ? (bitdepth_mode - 1)*2 : 4;
+  return lossless_p ? 4 - (bitdepth_mode - 1)*2 : 0;
+}
+
+// The forward batch: in[] are od_coeff planes (pix_bytes 0) or planes of pix_bytes-byte
+// reference-buffer samples converted on the fly (od_ref_buf_to_coeff fused into the load).
+static int fwd_batch_any(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const in[],
+                         const unsigned char *bsize, int nframes, int flags, int pix_bytes,
+                         int pix_shift, void *stream) {
+  if (!ctx || !d || !in || !bsize) return OD_TDLT_EFAULT;
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
   DeviceGuard dev_guard(ctx->device);
   if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
@@ -388,16 +407,23 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   rb.nframes = nframes;
   rb.inv_nframes = 1.0f/(float)nframes;
   rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
+  rb.pix_shift = pix_shift;
+  if (pix_bytes && (rb.flags & OD_TDLT_HAAR)) {
+    return fail(ctx, OD_TDLT_EINVAL, "the fused pixel path has no lossless (OD_TDLT_HAAR) form");
+  }
   PlanePtrs out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
-    if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
+    if (((uintptr_t)in[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
     }
-    if (ranges_overlap(c[p], d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff))) {
-      return fail(ctx, OD_TDLT_EINVAL, "plane %d: c and d overlap (the stage is out of place)", p);
+    const size_t nsamp = (size_t)ctx->plane_size[p]*nframes;
+    if (ranges_overlap(in[p], nsamp*(pix_bytes ? pix_bytes : sizeof(od_coeff)), d[p], nsamp*sizeof(od_coeff))) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane %d: input and output overlap (the stage is out of place)", p);
     }
-    int rc = make_tmap(ctx, &maps.in[p], c[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
+    int rc = pix_bytes ? make_tmap(ctx, &maps.in[p], in[p], rb.pl[p].w, rb.pl[p].h, nframes,
+                                   pix_bytes == 1 ? PixBox<1>::kW : PixBox<2>::kW, kARegRows, pix_bytes)
+                       : make_tmap(ctx, &maps.in[p], in[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows);
     if (rc) return rc;
     out.p[p] = d[p];
   }
@@ -405,17 +431,37 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
   int prc = launch_plan(ctx, rb, bsize, nframes, flags, (cudaStream_t)stream);
   if (prc) return prc;
   dim3 grid((unsigned)rb.regs_per_frame, (unsigned)nframes);
-  if (rb.flags & OD_TDLT_HAAR) {
-    tdlt_fwd_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
-        maps, rb, ctx->plan, out);
-  }
-  else {
-    tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, (cudaStream_t)stream>>>(
-        maps, rb, ctx->plan, out);
-  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (rb.flags & OD_TDLT_HAAR) tdlt_fwd_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(maps, rb, ctx->plan, out);
+  else if (pix_bytes == 1) tdlt_fwd_region_pix8_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(maps, rb, ctx->plan, out);
+  else if (pix_bytes == 2) tdlt_fwd_region_pix16_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(maps, rb, ctx->plan, out);
+  else tdlt_fwd_region_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(maps, rb, ctx->plan, out);
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
+                      const unsigned char *bsize, int nframes, int flags, void *stream) {
+  return fwd_batch_any(ctx, d, reinterpret_cast<const void *const *>(c), bsize, nframes, flags, 0, 0,
+                       stream);
+}
+
+static int check_pix_args(od_tdlt_ctx *ctx, int xstride, int bitdepth_mode) {
+  if ((xstride != 1 && xstride != 2) || bitdepth_mode < 1 || bitdepth_mode > 3) {
+    return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");
+  }
+  return OD_TDLT_SUCCESS;
+}
+
+int od_tdlt_fwd_batch_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
+                          const unsigned char *bsize, int nframes, int flags, int xstride,
+                          int bitdepth_mode, int lossless_p, void *stream) {
+  if (!ctx || !pix) return OD_TDLT_EFAULT;
+  int rc = check_pix_args(ctx, xstride, bitdepth_mode);
+  if (rc) return rc;
+  return fwd_batch_any(ctx, d, pix, bsize, nframes, flags, xstride,
+                       conv_shift(xstride, bitdepth_mode, lossless_p), stream);
 }
 
 static int ensure_scratch(od_tdlt_ctx *ctx, long long tiles) {
@@ -432,9 +478,12 @@ static int ensure_scratch(od_tdlt_ctx *ctx, long long tiles) {
   return OD_TDLT_SUCCESS;
 }
 
-int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
-                      const unsigned char *bsize, int nframes, int flags, void *stream) {
-  if (!ctx || !d || !c || !bsize) return OD_TDLT_EFAULT;
+// The inverse batch: out[] are od_coeff planes (pix_bytes 0) or planes of pix_bytes-byte
+// reference-buffer samples (od_coeff_to_ref_buf fused into the store).
+static int inv_batch_any(od_tdlt_ctx *ctx, void *const outp[], const od_coeff *const d[],
+                         const unsigned char *bsize, int nframes, int flags, int pix_bytes,
+                         int pix_shift, void *stream) {
+  if (!ctx || !d || !outp || !bsize) return OD_TDLT_EFAULT;
   if (nframes < 1) return fail(ctx, OD_TDLT_EINVAL, "nframes < 1");
   DeviceGuard dev_guard(ctx->device);
   if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
@@ -442,20 +491,25 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   rb.nframes = nframes;
   rb.inv_nframes = 1.0f/(float)nframes;
   rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
+  rb.pix_shift = pix_shift;
+  if (pix_bytes && (rb.flags & OD_TDLT_HAAR)) {
+    return fail(ctx, OD_TDLT_EINVAL, "the fused pixel path has no lossless (OD_TDLT_HAAR) form");
+  }
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
   PlanePtrs out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
-    if (((uintptr_t)c[p] | (uintptr_t)d[p]) & 15) {
+    if (((uintptr_t)outp[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
     }
-    if (ranges_overlap(c[p], d[p], (size_t)ctx->plane_size[p]*nframes*sizeof(od_coeff))) {
-      return fail(ctx, OD_TDLT_EINVAL, "plane %d: c and d overlap (the stage is out of place)", p);
+    const size_t nsamp = (size_t)ctx->plane_size[p]*nframes;
+    if (ranges_overlap(outp[p], nsamp*(pix_bytes ? pix_bytes : sizeof(od_coeff)), d[p], nsamp*sizeof(od_coeff))) {
+      return fail(ctx, OD_TDLT_EINVAL, "plane %d: input and output overlap (the stage is out of place)", p);
     }
-    int trc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows, false);
+    int trc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows);
     if (trc) return trc;
-    out.p[p] = c[p];
+    out.p[p] = reinterpret_cast<int *>(outp[p]);
   }
   long long total = (long long)rb.regs_per_frame*nframes;
   int rc = ensure_scratch(ctx, total);
@@ -468,12 +522,21 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   ctx->epoch++;
   const unsigned short *order =
       ctx->order + (size_t)(nframes >= 48 ? 0 : (nframes >= 16 ? 1 : 2))*rb.regs_per_frame;
+  const unsigned grid = (unsigned)total;
   if (rb.flags & OD_TDLT_HAAR) {
-    tdlt_inv_haar_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
+    tdlt_inv_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+  }
+  else if (pix_bytes == 1) {
+    tdlt_inv_region_pix8_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+  }
+  else if (pix_bytes == 2) {
+    tdlt_inv_region_pix16_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
         maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
   }
   else {
-    tdlt_inv_region_kernel<<<(unsigned)total, kRegThreads, kRegSmemBytes, st>>>(
+    tdlt_inv_region_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
         maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
   }
   g_launches++;
@@ -481,10 +544,19 @@ int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *con
   return OD_TDLT_SUCCESS;
 }
 
-static int conv_shift(int xstride, int bitdepth_mode, int lossless_p) {
-  // reference src/state.c:1221-1223, 1236-1238 (OD_COEFF_SHIFT == 4)
-  if (xstride == 1) return lossless_p ? (bitdepth_mode - 1)*2 : 4;
-  return lossless_p ? 4 - (bitdepth_mode - 1)*2 : 0;
+int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
+                      const unsigned char *bsize, int nframes, int flags, void *stream) {
+  return inv_batch_any(ctx, reinterpret_cast<void *const *>(c), d, bsize, nframes, flags, 0, 0, stream);
+}
+
+int od_tdlt_inv_batch_pix(od_tdlt_ctx *ctx, void *const pix[], const od_coeff *const d[],
+                          const unsigned char *bsize, int nframes, int flags, int xstride,
+                          int bitdepth_mode, int lossless_p, void *stream) {
+  if (!ctx || !pix) return OD_TDLT_EFAULT;
+  int rc = check_pix_args(ctx, xstride, bitdepth_mode);
+  if (rc) return rc;
+  return inv_batch_any(ctx, pix, d, bsize, nframes, flags, xstride,
+                       conv_shift(xstride, bitdepth_mode, lossless_p), stream);
 }
 
 int od_tdlt_pix_to_coeff_batch(od_tdlt_ctx *ctx, od_coeff *c, const void *pix, int pli,
@@ -755,7 +827,19 @@ static int run_frames_queue(od_tdlt_ctx *ctx, const FramesJob &j) {
     CK(ctx, cudaEventRecord(ctx->ev_in[k], s_in));
     // ---- kernels ------------------------------------------------------------
     CK(ctx, cudaStreamWaitEvent(s_run, ctx->ev_in[k], 0));
-    if (!j.inverse) {
+    // the pixel conversion is fused into the transform kernels' load / store; lossless mode
+    // (another kernel pair) keeps the separate conversion passes
+    const bool fused = j.pix && !(j.flags & OD_TDLT_HAAR);
+    void *dpix[kMaxPlanes];
+    for (int p = 0; p < np; p++) dpix[p] = (char *)ctx->dev_pix[p] + (size_t)f0*ctx->plane_size[p]*j.xstride;
+    if (fused) {
+      rc = j.inverse ? od_tdlt_inv_batch_pix(ctx, dpix, dd, db, n, j.flags, j.xstride, j.bitdepth_mode,
+                                             j.lossless_p, s_run)
+                     : od_tdlt_fwd_batch_pix(ctx, dd, dpix, db, n, j.flags, j.xstride, j.bitdepth_mode,
+                                             j.lossless_p, s_run);
+      if (rc) return rc;
+    }
+    else if (!j.inverse) {
       if (j.pix) {
         for (int p = 0; p < np; p++) {
           rc = od_tdlt_pix_to_coeff_batch(ctx, dc[p],
@@ -823,6 +907,24 @@ static int run_frames(od_tdlt_ctx *ctx, const FramesJob &j) {
 }
 
 extern "C" {
+
+// Page-locks caller memory so that the host-pointer calls can overlap their copies with the
+// kernels (the reference's planes come from plain malloc, src/state.c:409-428: from pageable
+// memory every cudaMemcpyAsync is staged by the driver and the three-stream pipeline of
+// run_frames degenerates to one copy at a time).
+int od_tdlt_host_register(void *ptr, size_t bytes) {
+  if (!ptr || !bytes) return OD_TDLT_EFAULT;
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return OD_TDLT_SUCCESS; }
+  if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorInvalidValue ? OD_TDLT_EINVAL : OD_TDLT_EFAULT; }
+  return OD_TDLT_SUCCESS;
+}
+int od_tdlt_host_unregister(void *ptr) {
+  if (!ptr) return OD_TDLT_EFAULT;
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e != cudaSuccess) { cudaGetLastError(); return OD_TDLT_EINVAL; }
+  return OD_TDLT_SUCCESS;
+}
 
 int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
                        const unsigned char *bsize, int nframes, int flags) {

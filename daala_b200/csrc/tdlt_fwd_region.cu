@@ -18,7 +18,7 @@ namespace tdlt {
 __device__ long long *g_tdlt_trace = nullptr;
 #endif
 
-template <bool kHaar>
+template <bool kHaar, int kPix>
 __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
                        const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out) {
@@ -36,8 +36,16 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
   if (tid == 0) {
     mbar_init(s.bar, 1);
     fence_mbar_init();
-    mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
-    tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    if (kPix == 0) {
+      mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
+      tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    }
+    else {
+      // the region as 8- / 16-bit reference-buffer samples, into the tail of A's storage
+      constexpr int kP = kPix ? kPix : 1;
+      mbar_expect_tx(s.bar, PixBox<kP>::kBytes + kPlanBytes);
+      tma_load_3d(smem + kOffA + PixBox<kP>::kOff, &maps.in[id.pli], s.bar, X0 - 4 - PixBox<kP>::kSkip, Y0 - 2, id.frame);
+    }
     bulk_g2s(s.ls, plan + ((size_t)blockIdx.y*bd.regs_per_frame + blockIdx.x)*kPlanBytes,
              kPlanBytes, s.bar);
     s.dyn[1] = 0;                             // task draw counter
@@ -45,6 +53,10 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
   __syncthreads();
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 1);
   mbar_wait(s.bar, 0);
+  if (kPix) {
+    region_widen_box<(kPix ? kPix : 1)>(smem, bd.pix_shift, tid);
+    __syncthreads();
+  }
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 2);
 
   if (!haar) {
@@ -170,7 +182,22 @@ __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out) {
-  tdlt_fwd_region_body<false>(maps, bd, plan, out);
+  tdlt_fwd_region_body<false, 0>(maps, bd, plan, out);
+}
+
+// The same with od_ref_buf_to_coeff fused into the load: maps describe planes of 8-bit
+// (pix8) or 16-bit (pix16) reference-buffer samples.
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_fwd_region_pix8_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out) {
+  tdlt_fwd_region_body<false, 1>(maps, bd, plan, out);
+}
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_fwd_region_pix16_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out) {
+  tdlt_fwd_region_body<false, 2>(maps, bd, plan, out);
 }
 
 // Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
@@ -178,7 +205,7 @@ __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_fwd_haar_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out) {
-  tdlt_fwd_region_body<true>(maps, bd, plan, out);
+  tdlt_fwd_region_body<true, 0>(maps, bd, plan, out);
 }
 
 

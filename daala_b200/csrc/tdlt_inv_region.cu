@@ -83,7 +83,7 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
-template <bool kHaar>
+template <bool kHaar, int kPix>
 __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
                        const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
@@ -314,7 +314,13 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
     int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
     if (!(TDLT_ABLATE & 1)) region_lap_pass<true>(s.A, s.ub, s.msk, last_r ? kCellsFwd : kCellsInv, warp, lane);
     __syncthreads();
-    if (!(TDLT_ABLATE & 128)) region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
+    if (kPix) {
+      // od_coeff_to_ref_buf fused into the store: out.p[] are planes of kPix-byte samples
+      unsigned char *gp = reinterpret_cast<unsigned char *>(out.p[id.pli]) +
+                          (((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2))*kPix;
+      region_store_owned_pix<(kPix ? kPix : 1)>(s.A, gp, (size_t)pd.w*kPix, b0, b1, cs, ce, bd.pix_shift, warp, lane);
+    }
+    else if (!(TDLT_ABLATE & 128)) region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
   }
   TDLT_MARK(t, 8);
 }
@@ -325,7 +331,26 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<false>(maps, bd, plan, out, strips, ticket, epoch, order);
+  tdlt_inv_region_body<false, 0>(maps, bd, plan, out, strips, ticket, epoch, order);
+}
+
+// The same with od_coeff_to_ref_buf fused into the store: out.p[] are planes of 8-bit (pix8)
+// or 16-bit (pix16) reference-buffer samples.
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_inv_region_pix8_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out,
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
+                       const unsigned short *__restrict__ order) {
+  tdlt_inv_region_body<false, 1>(maps, bd, plan, out, strips, ticket, epoch, order);
+}
+__global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
+tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
+                       const __grid_constant__ RegionBatch bd,
+                       const unsigned char *__restrict__ plan, PlanePtrs out,
+                       int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
+                       const unsigned short *__restrict__ order) {
+  tdlt_inv_region_body<false, 2>(maps, bd, plan, out, strips, ticket, epoch, order);
 }
 
 // Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
@@ -335,7 +360,7 @@ tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<true>(maps, bd, plan, out, strips, ticket, epoch, order);
+  tdlt_inv_region_body<true, 0>(maps, bd, plan, out, strips, ticket, epoch, order);
 }
 
 

@@ -24,6 +24,12 @@ __global__ void tdlt_plan_kernel(const __grid_constant__ RegionBatch bd,
 __global__ void tdlt_fwd_region_kernel(const __grid_constant__ TmapSet maps,
                                        const __grid_constant__ RegionBatch bd,
                                        const unsigned char *__restrict__ plan, PlanePtrs out);
+__global__ void tdlt_fwd_region_pix8_kernel(const __grid_constant__ TmapSet maps,
+                                            const __grid_constant__ RegionBatch bd,
+                                            const unsigned char *__restrict__ plan, PlanePtrs out);
+__global__ void tdlt_fwd_region_pix16_kernel(const __grid_constant__ TmapSet maps,
+                                             const __grid_constant__ RegionBatch bd,
+                                             const unsigned char *__restrict__ plan, PlanePtrs out);
 __global__ void tdlt_fwd_haar_kernel(const __grid_constant__ TmapSet maps,
                                      const __grid_constant__ RegionBatch bd,
                                      const unsigned char *__restrict__ plan, PlanePtrs out);
@@ -33,6 +39,18 @@ __global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                                        PlanePtrs out, int2 *__restrict__ strips,
                                        int *__restrict__ ticket, int epoch,
                                        const unsigned short *__restrict__ order);
+__global__ void tdlt_inv_region_pix8_kernel(const __grid_constant__ TmapSet maps,
+                                            const __grid_constant__ RegionBatch bd,
+                                            const unsigned char *__restrict__ plan,
+                                            PlanePtrs out, int2 *__restrict__ strips,
+                                            int *__restrict__ ticket, int epoch,
+                                            const unsigned short *__restrict__ order);
+__global__ void tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
+                                             const __grid_constant__ RegionBatch bd,
+                                             const unsigned char *__restrict__ plan,
+                                             PlanePtrs out, int2 *__restrict__ strips,
+                                             int *__restrict__ ticket, int epoch,
+                                             const unsigned short *__restrict__ order);
 __global__ void tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                                      const __grid_constant__ RegionBatch bd,
                                      const unsigned char *__restrict__ plan,

@@ -110,6 +110,7 @@ struct RegionBatch {
   int pic_w, pic_h;      // LUMA picture size (gates the split filters)
   int bw, bh;            // block-size map: entries across / down (8x8 luma units)
   int flags;             // OD_TDLT_KEYFRAME | OD_TDLT_HAAR
+  int pix_shift;         // fused pixel conversion: the shift of src/state.c:1221-1223 / 1236-1238
 };
 
 struct RegionId {
@@ -156,6 +157,74 @@ __device__ __forceinline__ RegionSmem carve_region(unsigned char *base) {
   s.bar = reinterpret_cast<unsigned long long *>(base + kOffBar);
   s.dyn = reinterpret_cast<int *>(base + kOffDyn);
   return s;
+}
+
+// ---------------------------------------------------------------------------
+// Fused pixel <-> coefficient conversion (reference od_ref_buf_to_coeff /
+// od_coeff_to_ref_buf, src/state.c:1209-1316; clamps src/odintrin.h:104-113): the
+// forward kernel takes its region as a TMA box of 8- or 16-bit reference-buffer samples
+// and widens it into A; the inverse kernel narrows its owned rectangle on the way out.
+//   kPix 1 (xstride 1):  c = (p - 128) << shift           p = clamp255(((c + rnd) >> shift) + 128)
+//   kPix 2 (xstride 2):  c = (p - 2048 + rnd) >> shift    p = clamp(c << shift + 2048, 0, 4095)
+// The sample box (PixBox below) lands in the tail of A's own storage, at a 128-byte aligned offset; all threads take
+// their part of it into registers, a barrier, then they write the widened rows.
+// ---------------------------------------------------------------------------
+// The box starts kSkip samples left of A's first column because the innermost TMA coordinate
+// must be a multiple of 16 BYTES (16 samples of one byte, 8 of two), as must the box row.
+template <int kPix> struct PixBox {
+  static constexpr int kSkip = 16/kPix - 4;                       // box column of A's column 0: 12 / 4
+  static constexpr int kW = kPix == 1 ? 160 : 144;                // samples per box row (>= kSkip + kAP)
+  static constexpr int kBytes = kW*kARegRows*kPix;
+  static constexpr int kOff = ((kARegBytes - kBytes)/128)*128;
+  static_assert(kW >= kSkip + kAP && (kW*kPix) % 16 == 0, "box row");
+  static_assert(kOff >= 0 && kOff + kBytes <= kARegBytes, "the sample box fits in A");
+};
+template <int kPix>
+__device__ __forceinline__ int pix_to_coeff1(int p, int shift) {
+  return kPix == 1 ? (p - 128)*(1 << shift) : (p - 2048 + ((1 << shift) >> 1)) >> shift;
+}
+template <int kPix>
+__device__ __forceinline__ int coeff_to_pix1(int c, int shift) {
+  return kPix == 1 ? min(max(((c + ((1 << shift) >> 1)) >> shift) + 128, 0), 255)
+                   : min(max(c*(1 << shift) + 2048, 0), 4095);
+}
+// Called by all threads after the box has landed; ends with the widened region in A (the
+// caller's next barrier orders it).  Work item = 4 samples = one 16-byte chunk of A.
+template <int kPix>
+__device__ __forceinline__ void region_widen_box(unsigned char *smem, int shift, int tid) {
+  constexpr int kItems = kARegRows*(kAP/4);                       // 2380
+  constexpr int kIter = (kItems + kRegThreads - 1)/kRegThreads;   // 10
+  const unsigned char *box = smem + kOffA + PixBox<kPix>::kOff;
+  int4 *A4 = reinterpret_cast<int4 *>(smem + kOffA);
+  unsigned lo[kIter], hi[kIter];
+#pragma unroll
+  for (int it = 0; it < kIter; it++) {
+    const int j = tid + kRegThreads*it;
+    lo[it] = hi[it] = 0;
+    if (j < kItems) {
+      const int row = (j*1873) >> 16, q = j - row*(kAP/4);        // j / 35, exact below 2^15
+      const unsigned char *src = box + (row*PixBox<kPix>::kW + PixBox<kPix>::kSkip + 4*q)*kPix;
+      if (kPix == 1) lo[it] = *reinterpret_cast<const unsigned *>(src);
+      else { uint2 t = *reinterpret_cast<const uint2 *>(src); lo[it] = t.x; hi[it] = t.y; }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < kIter; it++) {
+    const int j = tid + kRegThreads*it;
+    if (j < kItems) {
+      int4 o;
+      if (kPix == 1) {
+        o.x = pix_to_coeff1<1>(lo[it] & 255, shift);         o.y = pix_to_coeff1<1>((lo[it] >> 8) & 255, shift);
+        o.z = pix_to_coeff1<1>((lo[it] >> 16) & 255, shift); o.w = pix_to_coeff1<1>(lo[it] >> 24, shift);
+      }
+      else {
+        o.x = pix_to_coeff1<2>((short)(lo[it] & 0xffff), shift); o.y = pix_to_coeff1<2>((short)(lo[it] >> 16), shift);
+        o.z = pix_to_coeff1<2>((short)(hi[it] & 0xffff), shift); o.w = pix_to_coeff1<2>((short)(hi[it] >> 16), shift);
+      }
+      A4[j] = o;
+    }
+  }
 }
 
 // Unit-table index of region unit (uy, ux), uy in [-1, 8], ux in [-1, 16].
@@ -363,6 +432,40 @@ __device__ __forceinline__ void region_store_owned(const int *A, int *g, size_t 
     if (full) *reinterpret_cast<int4 *>(grow) = v;
     if (half) *reinterpret_cast<int2 *>(grow) = make_int2(v.x, v.y);
     if (left) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
+  }
+}
+
+// The same with the samples narrowed to kPix-byte reference-buffer pixels on the way out
+// (od_coeff_to_ref_buf): g -> the pixel at buffer row 0, region column -2; pitch in bytes.
+template <int kPix>
+__device__ __forceinline__ void region_store_owned_pix(const int *A, unsigned char *g, size_t pitch,
+                                                       int b0, int b1, int cs, int ce, int shift,
+                                                       int warp, int lane) {
+  const int c = 4*lane;
+  const bool full = c + 3 < ce, half = !full && c + 1 < ce, left = lane == 0 && cs < 0;
+  const int *arow = A + (b0 + warp)*kAP + 4 + c;
+  unsigned char *grow = g + (size_t)(b0 + warp)*pitch + (2 + c)*kPix;     // -> region column c
+#pragma unroll 2
+  for (int b = b0 + warp; b < b1; b += kRegWarps, arow += kRegWarps*kAP, grow += kRegWarps*pitch) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(arow)));
+    const unsigned p0 = coeff_to_pix1<kPix>(v.x, shift), p1 = coeff_to_pix1<kPix>(v.y, shift);
+    const unsigned p2 = coeff_to_pix1<kPix>(v.z, shift), p3 = coeff_to_pix1<kPix>(v.w, shift);
+    if (kPix == 1) {
+      if (full) *reinterpret_cast<unsigned *>(grow) = p0 | (p1 << 8) | (p2 << 16) | (p3 << 24);
+      if (half) *reinterpret_cast<unsigned short *>(grow) = (unsigned short)(p0 | (p1 << 8));
+    }
+    else {
+      if (full) *reinterpret_cast<uint2 *>(grow) = make_uint2(p0 | (p1 << 16), p2 | (p3 << 16));
+      if (half) *reinterpret_cast<unsigned *>(grow) = p0 | (p1 << 16);
+    }
+    if (left) {
+      const int2 l = *reinterpret_cast<const int2 *>(arow - 2);
+      const unsigned q0 = coeff_to_pix1<kPix>(l.x, shift), q1 = coeff_to_pix1<kPix>(l.y, shift);
+      if (kPix == 1) *reinterpret_cast<unsigned short *>(grow - 2) = (unsigned short)(q0 | (q1 << 8));
+      else *reinterpret_cast<unsigned *>(grow - 4) = q0 | (q1 << 16);
+    }
   }
 }
 

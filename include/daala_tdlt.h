@@ -30,6 +30,7 @@
 #ifndef DAALA_TDLT_H
 #define DAALA_TDLT_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -111,6 +112,24 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
  const unsigned char *bsize, int nframes, int flags, void *stream);
 int od_tdlt_inv_batch(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],
  const unsigned char *bsize, int nframes, int flags, void *stream);
+/* The same two stages with the pixel conversion fused into the kernels' load / store, so
+   that the od_coeff copy of the spatial side never exists in memory:
+     forward = od_ref_plane_to_coeff (src/state.c:1252-1272, od_ref_buf_to_coeff :1209-1250)
+               + the forward stage, pix -> d;
+     inverse = the inverse stage + od_coeff_to_ref_plane (src/state.c:1320-1338,
+               od_coeff_to_ref_buf :1274-1316), d -> pix.
+   pix[pli]: DEVICE pointers to nframes contiguous planes of (fw>>xdec) x (fh>>ydec)
+   reference-buffer samples, xstride bytes each (1: 8-bit, 2: 16-bit), no padding, 16-byte
+   aligned; xstride / bitdepth_mode / lossless_p as in the conversion calls below.  Not
+   available with OD_TDLT_HAAR (OD_TDLT_EINVAL): lossless mode uses the separate conversion
+   calls.  Per sample and direction these calls move 4 + xstride bytes instead of 12 + xstride
+   (conversion pass + transform pass). */
+int od_tdlt_fwd_batch_pix(od_tdlt_ctx *ctx, od_coeff *const d[], const void *const pix[],
+ const unsigned char *bsize, int nframes, int flags, int xstride, int bitdepth_mode,
+ int lossless_p, void *stream);
+int od_tdlt_inv_batch_pix(od_tdlt_ctx *ctx, void *const pix[], const od_coeff *const d[],
+ const unsigned char *bsize, int nframes, int flags, int xstride, int bitdepth_mode,
+ int lossless_p, void *stream);
 
 /* The forward batch call for callers that must not allocate (code under CUDA graph
    capture, serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in
@@ -203,9 +222,19 @@ int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *
 
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
-   out as above but in host memory (pinned or pageable).
+   out as above but in host memory.  Pageable memory works, but every copy is then staged
+   by the driver and nothing overlaps (measured: bench.py's e2e.pageable); the reference's
+   planes are plain malloc (src/state.c:409-428), so page-lock them once after
+   od_state_init with
+     od_tdlt_host_register(state->ctmp[pli], plane_bytes);   ... dtmp, the od_img planes
+   and release them before od_state_clear frees them (od_tdlt_host_unregister).  Both wrap
+   cudaHostRegister / cudaHostUnregister (portable across devices); registering a range
+   twice is not an error.  Returns OD_TDLT_SUCCESS, OD_TDLT_EINVAL (bad range) or
+   OD_TDLT_EFAULT.
    These replace, in od_encode_coefficients / od_decode_coefficients, the loops
    at src/encode.c:2425-2437 + :2492 and src/decode.c:632-638, 854-866, 1032-1041. */
+int od_tdlt_host_register(void *ptr, size_t bytes);
+int od_tdlt_host_unregister(void *ptr);
 int od_tdlt_fwd_frames(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *const c[],
  const unsigned char *bsize, int nframes, int flags);
 int od_tdlt_inv_frames(od_tdlt_ctx *ctx, od_coeff *const c[], const od_coeff *const d[],

@@ -356,3 +356,161 @@ void ref_dct1d_vectors(int bs, int inverse, od_coeff *out, const od_coeff *in, i
     else (*OD_FDCT_1D[bs])(out + (size_t)k*n, in + (size_t)k*n, 1);
   }
 }
+
+/* ---- frame-level drivers of the neighbouring stages ---------------------------------
+   The same loops tests/oracle_libs.py runs from Python (one reference call per superblock
+   or block), in C, so that bench.py and tools/bench_*.py can TIME the reference on these
+   stages without the interpreter in the way.  Every sample still goes through the
+   reference's own functions; tests/test_oracle_vs_ref.py holds them to the Python loops. */
+
+/* od_dering over a frame in the decoder's loop order (src/decode.c:1055-1122): in plays the
+   unfiltered copy etmp (narrowed to int16 as that copy is), out the reconstruction ctmp. */
+void ref_dering_frame(void *h, od_coeff *const out[], od_coeff *const in[], int nplanes,
+ const int dec[], const unsigned char *flags, unsigned char *const bskip[], int skip_stride,
+ const int q[], int impl) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *s = &r->enc->state;
+  int16_t *e[OD_NPLANES_MAX];
+  int16_t buf[32*32];
+  int W;
+  int H;
+  int pli;
+  int sbx;
+  int sby;
+  W = s->frame_width;
+  H = s->frame_height;
+  for (pli = 0; pli < nplanes; pli++) {
+    size_t n;
+    size_t i;
+    n = (size_t)(W >> dec[pli])*(H >> dec[pli]);
+    e[pli] = (int16_t *)malloc(n*sizeof(int16_t));
+    for (i = 0; i < n; i++) {
+      e[pli][i] = (int16_t)in[pli][i];
+      out[pli][i] = in[pli][i];
+    }
+  }
+  for (sby = 0; sby < s->nvsb; sby++) {
+    for (sbx = 0; sbx < s->nhsb; sbx++) {
+      int dir[OD_DERING_NBLOCKS][OD_DERING_NBLOCKS];
+      if (!flags[sby*s->nhsb + sbx]) continue;
+      memset(dir, 0, sizeof(dir));
+      for (pli = 0; pli < nplanes; pli++) {
+        int ln;
+        int n;
+        int w;
+        int y;
+        int x;
+        ln = 5 - dec[pli];
+        n = 1 << ln;
+        w = W >> dec[pli];
+        ref_dering(h, buf, n, e[pli] + (size_t)(sby << ln)*w + (sbx << ln), w, ln, sbx, sby,
+         s->nhsb, s->nvsb, q[pli], dec[pli], &dir[0][0], pli,
+         bskip[pli] + (sby << (3 - dec[pli]))*skip_stride + (sbx << (3 - dec[pli])),
+         skip_stride, impl);
+        for (y = 0; y < n; y++) {
+          for (x = 0; x < n; x++) {
+            out[pli][(size_t)((sby << ln) + y)*w + (sbx << ln) + x] = buf[y*n + x];
+          }
+        }
+      }
+    }
+  }
+  for (pli = 0; pli < nplanes; pli++) free(e[pli]);
+}
+
+/* od_smooth_recursive per superblock and plane with the decoder's arguments
+   (src/decode.c:1139-1143), in place. */
+void ref_smooth_frame(void *h, od_coeff *const c[], int nplanes, const int dec[],
+ unsigned char *bsize, int bstride, const int q[]) {
+  ref_ctx *r = (ref_ctx *)h;
+  od_state *s = &r->enc->state;
+  int pli;
+  int sbx;
+  int sby;
+  for (pli = 0; pli < nplanes; pli++) {
+    for (sby = 0; sby < s->nvsb; sby++) {
+      for (sbx = 0; sbx < s->nhsb; sbx++) {
+        od_smooth_recursive(c[pli], bsize, bstride, sbx, sby, 3, s->frame_width >> dec[pli],
+         dec[pli], dec[pli], 3, q[pli], pli);
+      }
+    }
+  }
+}
+
+/* od_resample_luma_coeffs once per chroma leaf block of a 4:2:0 frame, with the arguments
+   of its call sites (src/encode.c:1512-1517): l is the half-resolution predictor plane. */
+void ref_cfl_pred_frame(od_coeff *l, const od_coeff *d_luma, int W, int H,
+ const unsigned char *bsize, int bstride) {
+  int uy;
+  int ux;
+  int cw;
+  cw = W >> 1;
+  for (uy = 0; uy < H >> 3; uy++) {
+    for (ux = 0; ux < W >> 3; ux++) {
+      int obs;
+      int bsi;
+      int m;
+      obs = bsize[uy*bstride + ux];
+      bsi = obs > 1 ? obs : 1;
+      m = 1 << (bsi - 1);
+      if ((ux & (m - 1)) || (uy & (m - 1))) continue;
+      od_resample_luma_coeffs(l + (size_t)(uy*4)*cw + ux*4, cw,
+       d_luma + (size_t)(uy*8)*W + ux*8, W, 1, 1, bsi - 1, obs);
+    }
+  }
+}
+
+/* od_raster_to_coding_order / od_coding_order_to_raster (src/partition.c:144-200) block by
+   block over the map, vectors placed in the product's block-linear plane
+   (include/daala_tdlt.h: superblocks in raster order, 4x4 units in Z order inside). */
+static size_t ref_block_linear_offset(int x0, int y0, int w, int S) {
+  int ux;
+  int uy;
+  int z;
+  int b;
+  ux = (x0 % S) >> 2;
+  uy = (y0 % S) >> 2;
+  z = 0;
+  for (b = 0; b < 3; b++) z |= (((ux >> b) & 1) << (2*b)) | (((uy >> b) & 1) << (2*b + 1));
+  return ((size_t)(y0/S)*(w/S) + x0/S)*S*S + 16*(size_t)z;
+}
+
+void ref_coding_order_plane(od_coeff *v, od_coeff *d, int W, int H, int dec,
+ const unsigned char *bsize, int bstride, int to_coding) {
+  od_coeff tmp[32*32];
+  int uy;
+  int ux;
+  for (uy = 0; uy < (H << dec) >> 3; uy++) {
+    for (ux = 0; ux < (W << dec) >> 3; ux++) {
+      int obs;
+      int lu;
+      int n;
+      int nsub;
+      int k;
+      obs = bsize[uy*bstride + ux];
+      lu = obs > 1 ? obs - 1 : 0;
+      if ((ux & ((1 << lu) - 1)) || (uy & ((1 << lu) - 1))) continue;
+      n = (4 << obs) >> dec;
+      if (n < 4) n = 4;
+      nsub = (obs == 0 && dec == 0) ? 4 : 1;
+      for (k = 0; k < nsub; k++) {
+        int x0;
+        int y0;
+        int ncoded;
+        od_coeff *vec;
+        x0 = ((ux*8) >> dec) + 4*(k & 1);
+        y0 = ((uy*8) >> dec) + 4*(k >> 1);
+        vec = v + ref_block_linear_offset(x0, y0, W, 32 >> dec);
+        ncoded = n*n < 512 ? n*n : 512;
+        if (to_coding) {
+          od_raster_to_coding_order(tmp, n, d + (size_t)y0*W + x0, W);
+          memcpy(vec, tmp, ncoded*sizeof(od_coeff));
+        }
+        else {
+          memcpy(tmp, vec, n*n*sizeof(od_coeff));
+          od_coding_order_to_raster(d + (size_t)y0*W + x0, W, tmp, n);
+        }
+      }
+    }
+  }
+}

@@ -17,7 +17,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 PORT_SO = os.path.join(ORACLE_DIR, "libtdlt_oracle.so")
-REF_SO = os.path.join(ORACLE_DIR, "_ref", "libdaala_ref.so")
+# DAALA_REF_LIB: another build of the same reference sources (bench.py's cpu_baseline times the
+# -O3 -march=native one in a subprocess); the tests never set it.
+REF_SO = os.environ.get("DAALA_REF_LIB") or os.path.join(ORACLE_DIR, "_ref", "libdaala_ref.so")
 
 I32P = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 U8P = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
@@ -489,3 +491,45 @@ def ar1_plane(h, w, rng, rho=0.95, sigma=40.0, mean=0.0, scale=16, lo=-2048, hi=
         a[:, j] = rho * a[:, j - 1] + a[:, j]
     v = np.clip(np.rint(a + mean) * scale, lo, hi)
     return v.astype(np.int32)
+
+
+# ---- the same reference loops in C (oracle/ref_glue.c), for the TIMED CPU baselines ----------
+def ref_dering_frame_c(rc, planes, decs, flags, bskip, q, impl=1):
+    """ref_dering_frame with the superblock loop in C (what bench.py / tools/bench_dering.py time)."""
+    planes = [np.ascontiguousarray(p, dtype=np.int32) for p in planes]
+    out = [np.zeros_like(p) for p in planes]
+    flags = np.ascontiguousarray(flags, dtype=np.uint8)
+    bskip = [np.ascontiguousarray(b, dtype=np.uint8) for b in bskip]
+    n, pa, da, ba = dering_args(planes, decs, bskip)
+    oa = (C.c_void_p * 4)(*[o.ctypes.data for o in out])
+    rc.lib.ref_dering_frame(C.c_void_p(rc.h), oa, pa, n, da, ptr(flags), ba, bskip[0].shape[1],
+                            (C.c_int * 4)(*q), impl)
+    return out
+
+
+def ref_smooth_frame_c(rc, planes, decs, bsize, q):
+    out = [np.ascontiguousarray(p, dtype=np.int32).copy() for p in planes]
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    pa = (C.c_void_p * 4)(*[o.ctypes.data for o in out])
+    rc.lib.ref_smooth_frame(C.c_void_p(rc.h), pa, len(out), (C.c_int * 4)(*decs), ptr(bsize),
+                            bsize.shape[1], (C.c_int * 4)(*q))
+    return out
+
+
+def ref_cfl_pred_plane_c(d_luma, bsize):
+    d_luma = np.ascontiguousarray(d_luma, dtype=np.int32)
+    H, W = d_luma.shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    l = np.zeros((H // 2, W // 2), np.int32)
+    ref().ref_cfl_pred_frame(ptr(l), ptr(d_luma), W, H, ptr(bsize), bsize.shape[1])
+    return l
+
+
+def ref_coding_order_plane_c(src, bsize, dec, to_coding=True, out=None):
+    src = np.ascontiguousarray(src, dtype=np.int32).copy()
+    out = np.zeros_like(src) if out is None else out
+    H, W = src.shape
+    bsize = np.ascontiguousarray(bsize, dtype=np.uint8)
+    v, d = (out, src) if to_coding else (src, out)
+    ref().ref_coding_order_plane(ptr(v), ptr(d), W, H, dec, ptr(bsize), bsize.shape[1], 1 if to_coding else 0)
+    return out

@@ -192,6 +192,55 @@ def test_pixel_paths_match_checker(xstride, mode, lossless):
     chk.close()
 
 
+@pytest.mark.parametrize("xstride,mode,lossless", [(1, 1, 0), (2, 2, 0), (2, 3, 1)])
+def test_fused_pixel_batches_equal_the_two_pass_path(xstride, mode, lossless):
+    """od_tdlt_fwd_batch_pix / od_tdlt_inv_batch_pix (conversion fused into the transform
+    kernels' load / store) against the conversion kernel + transform kernel pair, bit for
+    bit, on an 8-frame 1080p batch (partial regions at the bottom of every plane); the
+    lossless kernels refuse the fused form."""
+    import torch
+    import daala_b200
+    pic_w, pic_h, nframes = 1920, 1080, 8
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(4100 + xstride)
+    with _ctx(pic_w, pic_h, 0) as ctx:
+        bsize = make_maps("quad", nframes, ctx.nhsb, ctx.nvsb, rng)
+        maps = torch.from_numpy(bsize).to(dev)
+        if xstride == 1:
+            pix_np = [rng.integers(0, 256, size=(nframes,) + s).astype(np.uint8) for s in ctx.plane_shapes]
+        else:
+            pix_np = [rng.integers(0, 4096, size=(nframes,) + s).astype(np.int16) for s in ctx.plane_shapes]
+        pix = [torch.from_numpy(a).to(dev) for a in pix_np]
+        c = [torch.empty(a.shape, dtype=torch.int32, device=dev) for a in pix_np]
+        d1 = [torch.empty_like(t) for t in c]
+        d2 = [torch.zeros_like(t) for t in c]
+        st = torch.cuda.current_stream().cuda_stream
+        KEY = daala_b200.OD_TDLT_KEYFRAME
+        for p in range(3):
+            ctx.pix_to_coeff_batch(c[p].data_ptr(), pix[p].data_ptr(), p, nframes, xstride, mode, lossless, st)
+        ctx.fwd_batch([t.data_ptr() for t in d1], [t.data_ptr() for t in c], maps.data_ptr(), nframes, KEY, st)
+        ctx.fwd_batch_pix([t.data_ptr() for t in d2], [t.data_ptr() for t in pix], maps.data_ptr(), nframes,
+                          KEY, xstride, mode, lossless, st)
+        torch.cuda.synchronize()
+        for p in range(3):
+            assert torch.equal(d1[p], d2[p]), "forward plane %d" % p
+        dq = [(t // 5) * 5 for t in d1]          # a crude quantiser: the inverse must clamp
+        c2 = [torch.empty_like(t) for t in c]
+        o1 = [torch.full_like(t, 9) for t in pix]
+        o2 = [torch.full_like(t, 9) for t in pix]
+        ctx.inv_batch([t.data_ptr() for t in c2], [t.data_ptr() for t in dq], maps.data_ptr(), nframes, KEY, st)
+        for p in range(3):
+            ctx.coeff_to_pix_batch(o1[p].data_ptr(), c2[p].data_ptr(), p, nframes, xstride, mode, lossless, st)
+        ctx.inv_batch_pix([t.data_ptr() for t in o2], [t.data_ptr() for t in dq], maps.data_ptr(), nframes,
+                          KEY, xstride, mode, lossless, st)
+        torch.cuda.synchronize()
+        for p in range(3):
+            assert torch.equal(o1[p], o2[p]), "inverse plane %d" % p
+        with pytest.raises(daala_b200.TdltError):
+            ctx.fwd_batch_pix([t.data_ptr() for t in d2], [t.data_ptr() for t in pix], maps.data_ptr(),
+                              nframes, KEY | daala_b200.OD_TDLT_HAAR, xstride, mode, lossless, st)
+
+
 # ---- reference-signature entry points (include/daala_tdlt.h section 3) --------
 def _selftest_vectors(n, rng, count):
     """The ranges of the reference's self-test (src/dct.c:3322-3391) plus impulses

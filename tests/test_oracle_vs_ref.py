@@ -460,3 +460,36 @@ def test_coding_order_plane_round_trip_and_layout(reflib, dec):
             reflib.od_raster_to_coding_order(ptr(want), n, ptr(blk), n)
             off = port.oc_block_linear_offset(x0, y0, W, 32 >> dec)
             assert np.array_equal(flat[off:off + n * n], want)
+
+
+def test_c_frame_drivers_equal_the_python_loops(reflib):
+    """The C frame drivers of oracle/ref_glue.c that the benches TIME (ref_dering_frame,
+    ref_smooth_frame, ref_cfl_pred_frame, ref_coding_order_plane) make the same reference
+    calls as the Python loops above: identical planes."""
+    rng = np.random.default_rng(2100)
+    decs = (0, 1, 1)
+    with ol.RefCtx(96, 64) as rc:
+        nhsb, nvsb = rc.nhsb, rc.nvsb
+        planes, flags, bskip = ol.dering_test_frame(rng, nhsb, nvsb, decs, skip_prob=0.4)
+        q = (60, 45, 30)
+        for impl in (0, 1):
+            a = ol.ref_dering_frame(rc, planes, decs, flags, bskip, q, impl=impl)
+            b = ol.ref_dering_frame_c(rc, planes, decs, flags, bskip, q, impl=impl)
+            for p in range(3):
+                assert np.array_equal(a[p], b[p]), "deringing plane %d impl %d" % (p, impl)
+        bsize = ol.random_quadtree_bsize(nhsb, nvsb, rng, 0.4, 0.6, 0.5)
+        a = ol.ref_smooth_frame(planes, decs, bsize, (200, 150, 100))
+        b = ol.ref_smooth_frame_c(rc, planes, decs, bsize, (200, 150, 100))
+        for p in range(3):
+            assert np.array_equal(a[p], b[p]), "smoothing plane %d" % p
+        d_luma = rng.integers(-30000, 30000, size=planes[0].shape).astype(np.int32)
+        bsize = ol.random_quadtree_bsize(nhsb, nvsb, rng)
+        assert np.array_equal(ol.ref_cfl_pred_plane(d_luma, bsize), ol.ref_cfl_pred_plane_c(d_luma, bsize))
+        for dec in (0, 1):
+            d = rng.integers(-30000, 30000, size=planes[dec].shape).astype(np.int32)
+            v1 = ol.ref_coding_order_plane(d, bsize, dec, True)
+            v2 = ol.ref_coding_order_plane_c(d, bsize, dec, True)
+            assert np.array_equal(v1, v2), "to coding order, dec %d" % dec
+            b1 = ol.ref_coding_order_plane(v1, bsize, dec, False, out=np.full_like(d, 77))
+            b2 = ol.ref_coding_order_plane_c(v1, bsize, dec, False, out=np.full_like(d, 77))
+            assert np.array_equal(b1, b2), "to raster, dec %d" % dec

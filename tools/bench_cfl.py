@@ -88,16 +88,22 @@ def main():
     if not args.no_cpu:
         # CPU baseline: the restatement, one thread, on a few frames of the same workload
         dn = d_luma[:4].cpu().numpy()
+        use_ref = ol.have_ref()
+        fn = ol.ref_cfl_pred_plane_c if use_ref else ol.port_cfl_pred_plane
+        if use_ref:      # od_resample_luma_coeffs itself, leaf by leaf, against the GPU's plane
+            assert np.array_equal(l[0].cpu().numpy(), fn(dn[0], maps_np[0])), "frame 0 differs from the reference"
+            line["parity"] += " and (frame 0) to the compiled reference"
         t0 = time.perf_counter()
         reps = 0
         while time.perf_counter() - t0 < 5.0:
             for f in range(dn.shape[0]):
-                ol.port_cfl_pred_plane(dn[f], maps_np[f])
+                fn(dn[f], maps_np[f])
             reps += 1
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": round(pic_w * pic_h * dn.shape[0] * reps / dt / 1e6, 1),
-                                "unit": "Mpixel/s", "cores": 1, "kind": "port",
-                                "sample": "%d frames x %d passes" % (dn.shape[0], reps)}
+                                "unit": "Mpixel/s", "cores": 1, "kind": "reference" if use_ref else "port",
+                                "sample": "%d frames x %d passes%s" % (dn.shape[0], reps,
+                                          " (od_resample_luma_coeffs per chroma leaf)" if use_ref else "")}
     print(json.dumps(line))
     ctx.close()
 

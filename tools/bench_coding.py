@@ -95,16 +95,27 @@ def main():
     line["parity"] = "frame 0 equal to the oracle, round trip exact on the ordered coefficients"
     if not args.no_cpu:
         a = [t[0].cpu().numpy() for t in d]
+        use_ref = ol.have_ref()
+        if use_ref:      # od_raster_to_coding_order itself, block by block, against the GPU's planes
+            for p, dec in enumerate(bench.DECS):
+                want = ol.ref_coding_order_plane_c(a[p], maps_np[0], dec, True)
+                assert np.array_equal(v[p][0].cpu().numpy(), want), "plane %d differs from the reference" % p
+            line["parity"] += "; frame 0 equal to the compiled reference"
         t0 = time.perf_counter()
         reps = 0
         while time.perf_counter() - t0 < 5.0:
             for p, dec in enumerate(bench.DECS):
-                w = ol.port_coding_order_plane(a[p], maps_np[0], dec, tables, True)
-                ol.port_coding_order_plane(w, maps_np[0], dec, tables, False)
+                if use_ref:
+                    w = ol.ref_coding_order_plane_c(a[p], maps_np[0], dec, True)
+                    ol.ref_coding_order_plane_c(w, maps_np[0], dec, False)
+                else:
+                    w = ol.port_coding_order_plane(a[p], maps_np[0], dec, tables, True)
+                    ol.port_coding_order_plane(w, maps_np[0], dec, tables, False)
             reps += 1
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": round(pic_w * pic_h * reps / dt / 1e6, 1), "unit": "Mpixel/s",
-                                "cores": 1, "kind": "port", "sample": "1 frame x %d passes, both directions" % reps}
+                                "cores": 1, "kind": "reference" if use_ref else "port",
+                                "sample": "1 frame x %d passes, both directions" % reps}
     print(json.dumps(line))
     ctx.close()
 

@@ -108,6 +108,7 @@ def main():
     for p in range(3):
         assert np.array_equal(out[p][0].cpu().numpy(), want[p]), "plane %d differs from the oracle" % p
     line["parity"] = "frame 0 equal to the oracle"
+    dering_out0 = [o[0].cpu().numpy().copy() for o in out]
     # ---- keyframe bilinear smoothing of the 32x32-coded superblocks, in place on the output ----
     maps_np = bench.make_maps_np("quad", nframes, nhsb, nvsb, 78)
     maps = torch.from_numpy(maps_np).to(dev)
@@ -133,14 +134,38 @@ def main():
     if not args.no_cpu:
         a = ([p[0].cpu().numpy() for p in planes], bench.DECS, flags[0].cpu().numpy(),
              [b[0].cpu().numpy() for b in bskip], q)
+        use_ref = ol.have_ref()
+        rc = ol.RefCtx(pic_w, pic_h) if use_ref else None
+        if use_ref:      # the reference itself (od_dering, SSE2 filters), frame 0, against the GPU's
+            want = ol.ref_dering_frame_c(rc, *a, impl=1)
+            for p in range(3):
+                assert np.array_equal(dering_out0[p], want[p]), "plane %d differs from the reference" % p
+            line["parity"] = "frame 0 equal to the oracle and to the compiled reference"
         t0 = time.perf_counter()
         reps = 0
         while time.perf_counter() - t0 < 5.0:
-            ol.port_dering_frame(*a)
+            if use_ref:
+                ol.ref_dering_frame_c(rc, *a, impl=1)
+            else:
+                ol.port_dering_frame(*a)
             reps += 1
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": round(pic_w * pic_h * reps / dt / 1e6, 1), "unit": "Mpixel/s",
-                                "cores": 1, "kind": "port", "sample": "1 frame x %d passes" % reps}
+                                "cores": 1, "kind": "reference" if use_ref else "port",
+                                "sample": "1 frame x %d passes (od_dering per superblock and plane, "
+                                          "dispatched SSE2 filters)" % reps}
+        if use_ref:
+            sm_in = [o[0].cpu().numpy() for o in planes]
+            t0 = time.perf_counter()
+            reps = 0
+            while time.perf_counter() - t0 < 3.0:
+                ol.ref_smooth_frame_c(rc, sm_in, bench.DECS, maps_np[0], q)
+                reps += 1
+            dt = time.perf_counter() - t0
+            line["smoothing"]["cpu_baseline"] = {"value": round(pic_w * pic_h * reps / dt / 1e6, 1),
+                                                 "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                                                 "sample": "1 frame x %d passes (od_smooth_recursive)" % reps}
+            rc.close()
     print(json.dumps(line))
     ctx.close()
 
