@@ -514,3 +514,184 @@ void ref_coding_order_plane(od_coeff *v, od_coeff *d, int W, int H, int dec,
     }
   }
 }
+
+/* ---- the whole codec through the reference's own call sites ------------------------------
+   daala_encode_img_in -> daala_encode_packet_out -> daala_decode_packet_in ->
+   daala_decode_img_out over a sequence of 8-bit 4:2:0 frames (src/encode.c:2876, :3246,
+   src/decode.c:1159), i.e. the loop of examples/encoder_example.c + dump_video.c without the
+   Ogg container.  impl selects what the dispatch tables of BOTH states hold: 0 = the C
+   functions, 1 = the runtime x86 dispatch, 2 = the tables a caller installed with
+   ref_set_external_vtbl (the CUDA library's od_tdlt_opt_vtbl_init_cuda /
+   od_tdlt_dering_vtbl_init_cuda).  In _ref/libdaala_ref_cuda.so (cuda_redirect.h) the direct
+   calls -- split and superblock-edge filters, Haar wavelet -- go to the CUDA library as
+   well, whatever impl says.  Every packet is decoded as it is produced, as
+   OD_ENCODER_CHECK's in-loop decoder does (src/encode.c:3203-3243). */
+#include "decint.h"
+
+typedef void (*ref_dct_vtbl_init)(od_dct_func_2d fdct_2d[], od_dct_func_2d idct_2d[]);
+typedef void (*ref_dering_vtbl_init)(od_filter_dering_direction_func direction[],
+ od_filter_dering_orthogonal_func orthogonal[]);
+static ref_dct_vtbl_init ref_ext_dct_init;
+static ref_dering_vtbl_init ref_ext_dering_init;
+
+void ref_set_external_vtbl(void *dct_init, void *dering_init) {
+  ref_ext_dct_init = (ref_dct_vtbl_init)dct_init;
+  ref_ext_dering_init = (ref_dering_vtbl_init)dering_init;
+}
+
+int ref_direct_calls_redirected(void) {
+#if defined(REF_GLUE_CUDA_REDIRECT)
+  return 1;
+#else
+  return 0;
+#endif
+}
+
+static int ref_state_vtbl(od_state *s, int impl) {
+  od_state_opt_vtbl_init_c(s);
+  if (impl == 1) {
+#if defined(OD_X86ASM)
+    od_state_opt_vtbl_init_x86(s);
+#endif
+  }
+  else if (impl == 2) {
+    if (!ref_ext_dct_init) return -1;
+    (*ref_ext_dct_init)(s->opt_vtbl.fdct_2d, s->opt_vtbl.idct_2d);
+    if (ref_ext_dering_init) {
+      (*ref_ext_dering_init)(s->opt_vtbl.filter_dering_direction,
+       s->opt_vtbl.filter_dering_orthogonal);
+    }
+  }
+  return 0;
+}
+
+/* yuv: nframes x (y: w*h, u: cw*ch, v: cw*ch) bytes, cw = (w+1)/2.  packets: the data packets
+   back to back (capacity packets_cap), packet_bytes[f] = size of frame f's packet.  recon:
+   the decoder's output pictures in the layout of yuv.  Returns the number of frames the
+   decoder put out, or a negative error. */
+int ref_codec_roundtrip(int pic_width, int pic_height, int nframes, const unsigned char *yuv,
+ int quality, int complexity, int keyframe_rate, int impl, unsigned char *packets,
+ long long packets_cap, int *packet_bytes, unsigned char *recon) {
+  daala_info info;
+  daala_info dinfo;
+  daala_comment dc;
+  daala_setup_info *setup;
+  daala_enc_ctx *enc;
+  daala_dec_ctx *dec;
+  daala_packet pkt;
+  od_img img;
+  od_img out;
+  long long used;
+  size_t ysz;
+  size_t csz;
+  int cw;
+  int ch;
+  int f;
+  int nout;
+  int ret;
+  int zero;
+  daala_info_init(&info);
+  info.pic_width = pic_width;
+  info.pic_height = pic_height;
+  info.nplanes = 3;
+  info.plane_info[0].xdec = info.plane_info[0].ydec = 0;
+  info.plane_info[1].xdec = info.plane_info[1].ydec = 1;
+  info.plane_info[2].xdec = info.plane_info[2].ydec = 1;
+  info.timebase_numerator = 30;
+  info.timebase_denominator = 1;
+  info.frame_duration = 1;
+  info.pixel_aspect_numerator = 1;
+  info.pixel_aspect_denominator = 1;
+  info.keyframe_rate = keyframe_rate;
+  enc = daala_encode_create(&info);
+  if (!enc) return -100;
+  zero = 0;
+  daala_encode_ctl(enc, OD_SET_QUANT, &quality, sizeof(quality));
+  daala_encode_ctl(enc, OD_SET_COMPLEXITY, &complexity, sizeof(complexity));
+  daala_encode_ctl(enc, OD_SET_B_FRAMES, &zero, sizeof(zero));
+  if (ref_state_vtbl(&enc->state, impl)) { daala_encode_free(enc); return -101; }
+  /* headers -> decoder */
+  daala_comment_init(&dc);
+  daala_info_init(&dinfo);
+  setup = NULL;
+  {
+    daala_comment ec;
+    daala_comment_init(&ec);
+    while ((ret = daala_encode_flush_header(enc, &ec, &pkt)) > 0) {
+      ret = daala_decode_header_in(&dinfo, &dc, &setup, &pkt);
+      if (ret < 0) { daala_encode_free(enc); return -102; }
+    }
+    daala_comment_clear(&ec);
+  }
+  dec = daala_decode_create(&dinfo, setup);
+  daala_setup_free(setup);
+  if (!dec) { daala_encode_free(enc); return -103; }
+  if (ref_state_vtbl(&dec->state, impl)) { daala_decode_free(dec); daala_encode_free(enc); return -101; }
+  cw = (pic_width + 1) >> 1;
+  ch = (pic_height + 1) >> 1;
+  ysz = (size_t)pic_width*pic_height;
+  csz = (size_t)cw*ch;
+  used = 0;
+  nout = 0;
+  for (f = 0; f < nframes; f++) {
+    const unsigned char *fr;
+    int last;
+    int left;
+    int i;
+    fr = yuv + (size_t)f*(ysz + 2*csz);
+    last = f == nframes - 1;
+    memset(&img, 0, sizeof(img));
+    img.nplanes = 3;
+    img.width = pic_width;
+    img.height = pic_height;
+    img.planes[0].data = (unsigned char *)fr;
+    img.planes[0].xstride = 1;
+    img.planes[0].ystride = pic_width;
+    img.planes[1].data = (unsigned char *)fr + ysz;
+    img.planes[2].data = (unsigned char *)fr + ysz + csz;
+    for (i = 1; i < 3; i++) {
+      img.planes[i].xdec = img.planes[i].ydec = 1;
+      img.planes[i].xstride = 1;
+      img.planes[i].ystride = cw;
+    }
+    for (i = 0; i < 3; i++) img.planes[i].bitdepth = 8;
+    left = 0;
+    /* (end_of_input means "this call brings no frame", src/encode.c:2907-2923) */
+    ret = daala_encode_img_in(enc, &img, 0, 0, &left);
+    if (ret < 0) { daala_decode_free(dec); daala_encode_free(enc); return ret; }
+    packet_bytes[f] = 0;
+    while (daala_encode_packet_out(enc, last, &pkt) > 0) {
+      int pli;
+      if (used + pkt.bytes > packets_cap) { daala_decode_free(dec); daala_encode_free(enc); return -104; }
+      memcpy(packets + used, pkt.packet, pkt.bytes);
+      used += pkt.bytes;
+      packet_bytes[f] += (int)pkt.bytes;
+      ret = daala_decode_packet_in(dec, &pkt);
+      if (ret < 0) { daala_decode_free(dec); daala_encode_free(enc); return -105; }
+      /* one picture per packet at most (examples/dump_video.c:414-436); the pictures the
+         decoder still holds come out after the last packet, when it has seen e_o_s */
+      while (daala_decode_img_out(dec, &out) > 0) {
+        unsigned char *dst;
+        if (nout >= nframes) break;
+        dst = recon + (size_t)nout*(ysz + 2*csz);
+        for (pli = 0; pli < 3; pli++) {
+          int w;
+          int h;
+          int y;
+          w = pli ? cw : pic_width;
+          h = pli ? ch : pic_height;
+          for (y = 0; y < h; y++) {
+            memcpy(dst + (size_t)y*w, out.planes[pli].data + (size_t)y*out.planes[pli].ystride, w);
+          }
+          dst += (size_t)w*h;
+        }
+        nout++;
+        if (!last) break;
+      }
+    }
+  }
+  daala_comment_clear(&dc);
+  daala_decode_free(dec);
+  daala_encode_free(enc);
+  return nout;
+}

@@ -533,3 +533,33 @@ def ref_coding_order_plane_c(src, bsize, dec, to_coding=True, out=None):
     v, d = (out, src) if to_coding else (src, out)
     ref().ref_coding_order_plane(ptr(v), ptr(d), W, H, dec, ptr(bsize), bsize.shape[1], 1 if to_coding else 0)
     return out
+
+
+# ---- the whole codec through the reference's call sites (oracle/ref_glue.c) -------------------
+REF_CUDA_SO = os.path.join(ORACLE_DIR, "_ref", "libdaala_ref_cuda.so")
+
+
+def codec_roundtrip(lib, frames, quality, impl, complexity=7, keyframe_rate=1):
+    """frames: list of (y, u, v) uint8 planes (4:2:0).  Runs daala_encode_img_in ->
+    daala_encode_packet_out -> daala_decode_packet_in -> daala_decode_img_out in `lib` (the
+    compiled reference, or its CUDA-redirected twin).  Returns (packet bytes, per-frame packet
+    sizes, list of decoded (y, u, v))."""
+    h, w = frames[0][0].shape
+    cw, ch = (w + 1) // 2, (h + 1) // 2
+    per = w * h + 2 * cw * ch
+    yuv = np.concatenate([np.concatenate([p.ravel() for p in f]) for f in frames]).astype(np.uint8)
+    cap = per * len(frames) * 2 + (1 << 20)
+    packets = np.zeros(cap, np.uint8)
+    sizes = np.zeros(len(frames), np.int32)
+    recon = np.zeros(per * len(frames), np.uint8)
+    lib.ref_codec_roundtrip.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                        C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
+    n = lib.ref_codec_roundtrip(w, h, len(frames), ptr(yuv), quality, complexity, keyframe_rate, impl,
+                                ptr(packets), cap, ptr(sizes), ptr(recon))
+    assert n == len(frames), "ref_codec_roundtrip returned %d" % n
+    out = []
+    for f in range(len(frames)):
+        b = recon[f * per:(f + 1) * per]
+        out.append((b[:w * h].reshape(h, w).copy(), b[w * h:w * h + cw * ch].reshape(ch, cw).copy(),
+                    b[w * h + cw * ch:].reshape(ch, cw).copy()))
+    return packets[:int(sizes.sum())].copy(), sizes, out

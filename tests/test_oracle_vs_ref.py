@@ -6,6 +6,8 @@ extremes :3759-3830; all sign patterns of +-676 for the filters,
 src/filter.c:2041-2116).  CPU only.
 """
 import ctypes as C
+import os
+import sys
 
 import numpy as np
 import pytest
@@ -493,3 +495,25 @@ def test_c_frame_drivers_equal_the_python_loops(reflib):
             b1 = ol.ref_coding_order_plane(v1, bsize, dec, False, out=np.full_like(d, 77))
             b2 = ol.ref_coding_order_plane_c(v1, bsize, dec, False, out=np.full_like(d, 77))
             assert np.array_equal(b1, b2), "to raster, dec %d" % dec
+
+
+@pytest.mark.parametrize("quality,keyframe_rate", [(20, 1), (0, 1), (30, 4)])
+def test_codec_roundtrip_harness_c_vs_simd(reflib, quality, keyframe_rate):
+    """The whole-codec harness (encoder -> packets -> decoder through the reference's own API)
+    with the C tables and with the runtime x86 dispatch: same packets, same pictures -- the
+    equality the CUDA-routed run is held to on the GPU (tests/test_zy_dropin_codec.py); at
+    quality 0 the decoder returns the input (tools/check_lossless.sh)."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden as mg
+    frames = [mg.cif_frame(t) for t in range(4)]      # (the decoder puts pictures out one packet late)
+    pk0, sz0, out0 = ol.codec_roundtrip(reflib, frames, quality, 0, keyframe_rate=keyframe_rate)
+    pk1, sz1, out1 = ol.codec_roundtrip(reflib, frames, quality, 1, keyframe_rate=keyframe_rate)
+    assert len(pk0) > 100 and np.array_equal(sz0, sz1) and np.array_equal(pk0, pk1)
+    for a, b in zip(out0, out1):
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    if quality == 0:
+        for a, b in zip(out0, frames):
+            assert all(np.array_equal(x, y) for x, y in zip(a, b)), "lossless mode must return the input"
+    else:
+        err = np.abs(out0[0][0].astype(int) - frames[0][0].astype(int)).mean()
+        assert err < 8, "decoded picture is far from the input (%.1f)" % err
