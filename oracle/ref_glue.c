@@ -547,6 +547,10 @@ int ref_direct_calls_redirected(void) {
 #endif
 }
 
+#if defined(REF_GLUE_CUDA_REDIRECT)
+void ref_chk_install_vtbl(od_state *s, void *dct_init, void *dering_init);
+#endif
+
 static int ref_state_vtbl(od_state *s, int impl) {
   od_state_opt_vtbl_init_c(s);
   if (impl == 1) {
@@ -562,6 +566,14 @@ static int ref_state_vtbl(od_state *s, int impl) {
        s->opt_vtbl.filter_dering_orthogonal);
     }
   }
+#if defined(REF_GLUE_CUDA_REDIRECT)
+  else if (impl == 3) {
+    /* OD_CHECKASM style: every table entry runs the C function and the external one and
+       compares (oracle/cuda_check.c); the direct calls do the same while ref_chk_mode is set */
+    if (!ref_ext_dct_init) return -1;
+    ref_chk_install_vtbl(s, (void *)ref_ext_dct_init, (void *)ref_ext_dering_init);
+  }
+#endif
   return 0;
 }
 
@@ -569,6 +581,11 @@ static int ref_state_vtbl(od_state *s, int impl) {
    back to back (capacity packets_cap), packet_bytes[f] = size of frame f's packet.  recon:
    the decoder's output pictures in the layout of yuv.  Returns the number of frames the
    decoder put out, or a negative error. */
+/* Rows in which the decoder's reconstruction differed from the encoder's during the last
+   ref_codec_roundtrip (OD_ENCODER_CHECK's "Pixel mismatch in row" count; 0 = in step). */
+static long long ref_encoder_check_rows;
+long long ref_encoder_check_mismatched_rows(void) { return ref_encoder_check_rows; }
+
 int ref_codec_roundtrip(int pic_width, int pic_height, int nframes, const unsigned char *yuv,
  int quality, int complexity, int keyframe_rate, int impl, unsigned char *packets,
  long long packets_cap, int *packet_bytes, unsigned char *recon) {
@@ -633,6 +650,7 @@ int ref_codec_roundtrip(int pic_width, int pic_height, int nframes, const unsign
   csz = (size_t)cw*ch;
   used = 0;
   nout = 0;
+  ref_encoder_check_rows = 0;
   for (f = 0; f < nframes; f++) {
     const unsigned char *fr;
     int last;
@@ -668,6 +686,27 @@ int ref_codec_roundtrip(int pic_width, int pic_height, int nframes, const unsign
       packet_bytes[f] += (int)pkt.bytes;
       ret = daala_decode_packet_in(dec, &pkt);
       if (ret < 0) { daala_decode_free(dec); daala_encode_free(enc); return -105; }
+      /* OD_ENCODER_CHECK (src/encode.c:3203-3243): the decoder's reconstruction of this
+         packet against the encoder's own, row by row over the padded frame */
+      {
+        od_img *ei;
+        od_img *di;
+        ei = enc->state.ref_imgs + enc->state.ref_imgi[OD_FRAME_SELF];
+        di = dec->state.ref_imgs + dec->state.ref_imgi[OD_FRAME_SELF];
+        for (pli = 0; pli < ei->nplanes; pli++) {
+          int pw;
+          int ph;
+          int y;
+          pw = dec->state.frame_width >> di->planes[pli].xdec;
+          ph = dec->state.frame_height >> di->planes[pli].ydec;
+          for (y = 0; y < ph; y++) {
+            if (memcmp(ei->planes[pli].data + (size_t)ei->planes[pli].ystride*y,
+             di->planes[pli].data + (size_t)di->planes[pli].ystride*y, pw)) {
+              ref_encoder_check_rows++;
+            }
+          }
+        }
+      }
       /* one picture per packet at most (examples/dump_video.c:414-436); the pictures the
          decoder still holds come out after the last packet, when it has seen e_o_s */
       while (daala_decode_img_out(dec, &out) > 0) {
