@@ -60,6 +60,8 @@ def lib():
         L.od_tdlt_fwd_batch_pix.argtypes = [vp, arr, arr, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_inv_batch_pix.argtypes = [vp, arr, arr, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_pix_to_coeff_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
+        L.od_tdlt_img_copy_pad_batch.argtypes = [vp, arr, C.POINTER(ci), C.POINTER(ll), ci, ci, ci,
+                                                 arr, C.POINTER(ci), C.POINTER(ll), ci, ci, ci, vp]
         L.od_tdlt_coeff_to_pix_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, vp]
         L.od_tdlt_cfl_pred_batch.argtypes = [vp, vp, vp, vp, ci, vp]
         L.od_tdlt_cfl_pred_frames.argtypes = [vp, vp, vp, vp, ci]
@@ -186,6 +188,17 @@ class TdltContext:
         self._check(self.L.od_tdlt_inv_batch_pix(self._h, _ptr_array(pix_ptrs), _ptr_array(d_ptrs),
                                                  bsize_ptr, nframes, flags, xstride, bitdepth_mode,
                                                  lossless, stream), "od_tdlt_inv_batch_pix")
+
+    def img_copy_pad_batch(self, dst_ptrs, dst_ystride, dst_frame_stride, dst_xstride, dst_bitdepth, border,
+                           src_ptrs, src_ystride, src_frame_stride, src_xstride, src_bitdepth, nframes,
+                           stream=0):
+        """Device pointers: the encoder's input side (od_img_copy_pad) for a batch of pictures."""
+        I4, L4 = C.c_int * NPLANES_MAX, C.c_longlong * NPLANES_MAX
+        pad = lambda v: list(v) + [0] * (NPLANES_MAX - len(v))  # noqa: E731
+        self._check(self.L.od_tdlt_img_copy_pad_batch(
+            self._h, _ptr_array(dst_ptrs), I4(*pad(dst_ystride)), L4(*pad(dst_frame_stride)), dst_xstride,
+            dst_bitdepth, border, _ptr_array(src_ptrs), I4(*pad(src_ystride)), L4(*pad(src_frame_stride)),
+            src_xstride, src_bitdepth, nframes, stream), "od_tdlt_img_copy_pad_batch")
 
     def cfl_pred_batch(self, l_ptr, d_luma_ptr, bsize_ptr, nframes, stream=0):
         """Device pointers: chroma-from-luma predictor planes (od_tdlt_cfl_pred_batch)."""

@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdaala_tdlt_cuda.so")
-SOURCES = ["tdlt_plan.cu", "tdlt_fwd_region.cu", "tdlt_inv_region.cu", "tdlt_aux_kernels.cu", "tdlt_dering.cu", "tdlt_capi.cu", "tdlt_static.cu"]
+SOURCES = ["tdlt_plan.cu", "tdlt_fwd_region.cu", "tdlt_inv_region.cu", "tdlt_aux_kernels.cu", "tdlt_dering.cu", "tdlt_input.cu", "tdlt_capi.cu", "tdlt_static.cu"]
 HEADERS = ["tdlt_device.cuh", "tdlt_region.cuh", "tdlt_tasks.cuh", "tdlt_lift_gen.cuh", "tdlt_kernels.h",
            "tdlt_aux_kernels.h", os.path.join("..", "..", "include", "daala_tdlt.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

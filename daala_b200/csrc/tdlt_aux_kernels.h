@@ -74,4 +74,22 @@ void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st);
 void launch_dering_block(short *y, const short *in, const short *x, int n, int thr, int dir,
                          bool orthogonal, cudaStream_t st);
 
+// The encoder's input side (tdlt_input.cu): od_img_copy_pad per plane.
+struct ImgPadPlane {
+  const unsigned char *src;        // first picture sample of frame 0
+  unsigned char *dst;              // first visible sample of frame 0's plane buffer
+  long long src_frame_stride, dst_frame_stride;    // bytes
+  int src_ystride, dst_ystride;    // bytes
+  int pic_w, pic_h;                // picture size in this plane
+  int plane_w, plane_h;            // padded frame size in this plane
+  int border;                      // samples of border around the plane in dst (0: none)
+};
+struct ImgPadParams {
+  ImgPadPlane pl[4];
+  int nplanes, nframes;
+  int src_xs, dst_xs;              // bytes per sample (1 or 2)
+  int src_bits, dst_bits;
+};
+void launch_img_copy_pad(const ImgPadParams &P, cudaStream_t st);
+
 }  // namespace tdlt

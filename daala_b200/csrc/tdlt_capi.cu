@@ -447,6 +447,56 @@ int od_tdlt_fwd_batch(od_tdlt_ctx *ctx, od_coeff *const d[], const od_coeff *con
                        stream);
 }
 
+// od_img_copy_pad (reference src/encode.c:1728-1750) for a batch of pictures.
+int od_tdlt_img_copy_pad_batch(od_tdlt_ctx *ctx, void *const dst[], const int dst_ystride[],
+                               const long long dst_frame_stride[], int dst_xstride, int dst_bitdepth,
+                               int border, const void *const src[], const int src_ystride[],
+                               const long long src_frame_stride[], int src_xstride, int src_bitdepth,
+                               int nframes, void *stream) {
+  if (!ctx || !dst || !dst_ystride || !dst_frame_stride || !src || !src_ystride || !src_frame_stride) {
+    return OD_TDLT_EFAULT;
+  }
+  if (nframes < 1 || border < 0 || (dst_xstride != 1 && dst_xstride != 2) ||
+      (src_xstride != 1 && src_xstride != 2) || src_bitdepth < 8 || src_bitdepth > 16 ||
+      dst_bitdepth < 8 || dst_bitdepth > 16 || (src_bitdepth > 8) != (src_xstride == 2) ||
+      (dst_bitdepth > 8) != (dst_xstride == 2)) {
+    return fail(ctx, OD_TDLT_EINVAL, "od_tdlt_img_copy_pad_batch: 8-bit samples are one byte, deeper ones two");
+  }
+  DeviceGuard dev_guard(ctx->device);
+  if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
+  ImgPadParams P;
+  memset(&P, 0, sizeof(P));
+  P.nplanes = ctx->g.nplanes;
+  P.nframes = nframes;
+  P.src_xs = src_xstride; P.dst_xs = dst_xstride;
+  P.src_bits = src_bitdepth; P.dst_bits = dst_bitdepth;
+  for (int p = 0; p < P.nplanes; p++) {
+    if (!dst[p] || !src[p]) return OD_TDLT_EFAULT;
+    const int dec = ctx->g.xdec[p];
+    ImgPadPlane &pl = P.pl[p];
+    pl.src = (const unsigned char *)src[p];
+    pl.dst = (unsigned char *)dst[p];
+    pl.src_ystride = src_ystride[p]; pl.dst_ystride = dst_ystride[p];
+    pl.src_frame_stride = src_frame_stride[p]; pl.dst_frame_stride = dst_frame_stride[p];
+    // src/encode.c:1743-1744, src/state.c:134-139
+    pl.pic_w = (ctx->g.pic_width + (1 << dec) - 1) >> dec;
+    pl.pic_h = (ctx->g.pic_height + (1 << dec) - 1) >> dec;
+    pl.plane_w = ctx->fw >> dec;
+    pl.plane_h = ctx->fh >> dec;
+    pl.border = border >> dec;
+    if (dst_xstride == 2 && ((uintptr_t)dst[p] | (uintptr_t)dst_ystride[p] | (uintptr_t)dst_frame_stride[p]) & 1) {
+      return fail(ctx, OD_TDLT_EINVAL, "16-bit destination must be 2-byte aligned");
+    }
+    if (src_xstride == 2 && ((uintptr_t)src[p] | (uintptr_t)src_ystride[p] | (uintptr_t)src_frame_stride[p]) & 1) {
+      return fail(ctx, OD_TDLT_EINVAL, "16-bit source must be 2-byte aligned");
+    }
+  }
+  launch_img_copy_pad(P, (cudaStream_t)stream);
+  g_launches += border > 0 ? 3 : 2;
+  CK(ctx, cudaGetLastError());
+  return OD_TDLT_SUCCESS;
+}
+
 static int check_pix_args(od_tdlt_ctx *ctx, int xstride, int bitdepth_mode) {
   if ((xstride != 1 && xstride != 2) || bitdepth_mode < 1 || bitdepth_mode > 3) {
     return fail(ctx, OD_TDLT_EINVAL, "bad conversion arguments");

@@ -220,6 +220,24 @@ int od_tdlt_set_scan_tables(od_tdlt_ctx *ctx, const unsigned char *const tables[
 int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *const d[],
  const unsigned char *bsize, int nframes, int to_coding, void *stream);
 
+/* The encoder's input side, the step before od_ref_plane_to_coeff (reference
+   od_img_copy_pad, src/encode.c:1728-1750, called from daala_encode_img_in at :2840): per
+   plane od_img_plane_copy with its bit-depth conversion and clamps (src/state.c:92-217: 8 ->
+   8 copy, deeper -> 8 rounding, 8 -> deeper and deeper -> deeper shifts), the low-pass
+   extension of the picture to the padded frame (od_img_plane_copy_pad, src/encode.c:610-700)
+   and, when border > 0, od_img_plane_edge_ext (src/state.c:1100-1159) into a border of
+   border >> xdec samples all round (OD_BUFFER_PADDING = 64 in the reference's buffers).
+     src[p]: picture samples of plane p, ((pic_width + (1 << xdec) - 1) >> xdec) x (... height),
+             src_xstride bytes per sample (1 for 8 bits, 2 above), rows src_ystride[p] BYTES
+             apart, frames src_frame_stride[p] bytes apart;
+     dst[p]: first visible sample of the (fw >> xdec) x (fh >> ydec) plane, same conventions.
+   With border = 0, dst_ystride[p] = (fw >> xdec)*dst_xstride and frames back to back, dst is
+   exactly what od_tdlt_fwd_batch_pix reads.  DEVICE pointers, asynchronous on `stream`. */
+int od_tdlt_img_copy_pad_batch(od_tdlt_ctx *ctx, void *const dst[], const int dst_ystride[],
+ const long long dst_frame_stride[], int dst_xstride, int dst_bitdepth, int border,
+ const void *const src[], const int src_ystride[], const long long src_frame_stride[],
+ int src_xstride, int src_bitdepth, int nframes, void *stream);
+
 /* ---- 2. whole-frame host calls ----------------------------------------
    HOST pointers, synchronous, nframes <= max_frames.  Planes and maps are laid
    out as above but in host memory.  Pageable memory works, but every copy is then staged

@@ -734,3 +734,35 @@ int ref_codec_roundtrip(int pic_width, int pic_height, int nframes, const unsign
   daala_encode_free(enc);
   return nout;
 }
+
+/* ---- the encoder's input side: od_img_copy_pad (src/encode.c:1728-1750) on one plane ----
+   od_img_plane_copy_pad (static, src/encode.c:610) + od_img_edge_ext (src/state.c:1161) on
+   caller buffers: dst -> first visible sample of a plane buffer with a border of
+   OD_BUFFER_PADDING >> dec samples all round. */
+void ref_img_copy_pad_plane(unsigned char *dst, int dst_xstride, int dst_ystride, int dst_bits,
+ int plane_w, int plane_h, int dec, unsigned char *src, int src_xstride, int src_ystride,
+ int src_bits, int pic_w, int pic_h, int edge_ext) {
+  od_img d;
+  od_img s;
+  memset(&d, 0, sizeof(d));
+  memset(&s, 0, sizeof(s));
+  d.nplanes = 1;
+  d.width = plane_w << dec;
+  d.height = plane_h << dec;
+  d.planes[0].data = dst;
+  d.planes[0].xstride = dst_xstride;
+  d.planes[0].ystride = dst_ystride;
+  d.planes[0].xdec = d.planes[0].ydec = dec;
+  d.planes[0].bitdepth = dst_bits;
+  s.nplanes = 1;
+  s.width = pic_w << dec;
+  s.height = pic_h << dec;
+  s.planes[0].data = src;
+  s.planes[0].xstride = src_xstride;
+  s.planes[0].ystride = src_ystride;
+  s.planes[0].xdec = s.planes[0].ydec = dec;
+  s.planes[0].bitdepth = src_bits;
+  od_img_plane_copy_pad(&d, plane_w, plane_h, &s, pic_w, pic_h, 0);
+  if (edge_ext) od_img_edge_ext(&d);
+}
+int ref_buffer_padding(void) { return OD_BUFFER_PADDING; }

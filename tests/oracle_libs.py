@@ -563,3 +563,39 @@ def codec_roundtrip(lib, frames, quality, impl, complexity=7, keyframe_rate=1):
         out.append((b[:w * h].reshape(h, w).copy(), b[w * h:w * h + cw * ch].reshape(ch, cw).copy(),
                     b[w * h + cw * ch:].reshape(ch, cw).copy()))
     return packets[:int(sizes.sum())].copy(), sizes, out
+
+
+# ---- the encoder's input side (od_img_copy_pad) ------------------------------------------------
+def _img_pad_buffers(pic, plane_w, plane_h, border, dst_bits):
+    ddt = np.uint8 if dst_bits == 8 else np.int16
+    buf = np.full((plane_h + 2 * border, plane_w + 2 * border), 77, ddt)
+    return buf, buf[border:, border:]
+
+
+def port_img_copy_pad_plane(pic, src_bits, plane_w, plane_h, border, dst_bits):
+    """pic: (pic_h, pic_w) uint8 / int16 picture plane.  Returns the bordered plane buffer
+    (plane_h + 2 border, plane_w + 2 border) of the restatement."""
+    lib = port()
+    pic = np.ascontiguousarray(pic)
+    buf, vis = _img_pad_buffers(pic, plane_w, plane_h, border, dst_bits)
+    lib.oc_img_copy_pad_plane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.oc_img_copy_pad_plane(C.c_void_p(vis.ctypes.data), buf.itemsize, buf.strides[0], dst_bits, plane_w,
+                              plane_h, border, ptr(pic), pic.itemsize, pic.strides[0], src_bits,
+                              pic.shape[1], pic.shape[0])
+    return buf
+
+
+def ref_img_copy_pad_plane(pic, src_bits, plane_w, plane_h, dec, dst_bits, edge_ext=True):
+    """The same through the REFERENCE's od_img_plane_copy_pad + od_img_edge_ext; the border is
+    the reference's OD_BUFFER_PADDING >> dec."""
+    lib = ref()
+    pic = np.ascontiguousarray(pic)
+    border = lib.ref_buffer_padding() >> dec
+    buf, vis = _img_pad_buffers(pic, plane_w, plane_h, border, dst_bits)
+    lib.ref_img_copy_pad_plane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.ref_img_copy_pad_plane(C.c_void_p(vis.ctypes.data), buf.itemsize, buf.strides[0], dst_bits, plane_w,
+                               plane_h, dec, ptr(pic), pic.itemsize, pic.strides[0], src_bits,
+                               pic.shape[1], pic.shape[0], 1 if edge_ext else 0)
+    return buf

@@ -241,6 +241,98 @@ def test_fused_pixel_batches_equal_the_two_pass_path(xstride, mode, lossless):
                               nframes, KEY | daala_b200.OD_TDLT_HAAR, xstride, mode, lossless, st)
 
 
+@pytest.mark.parametrize("pic_w,pic_h,src_bits,dst_bits", [(352, 288, 8, 8), (352, 288, 10, 8), (200, 136, 10, 12),
+                                                            (33, 17, 8, 10), (1920, 1080, 8, 8), (130, 70, 16, 8)])
+def test_img_copy_pad_matches_checker(pic_w, pic_h, src_bits, dst_bits):
+    """The encoder's input side on the device (od_tdlt_img_copy_pad_batch = od_img_copy_pad):
+    three pictures per call, all planes, into bordered buffers (OD_BUFFER_PADDING = 64) --
+    against the compiled reference's od_img_plane_copy_pad + od_img_edge_ext when it is here,
+    else the restatement; nothing outside the bordered planes may change."""
+    import torch
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(4300 + pic_w + src_bits)
+    nframes, border, guard = 3, 64, 5
+    with _ctx(pic_w, pic_h, 0) as ctx:
+        fw, fh = ctx.frame_width, ctx.frame_height
+        sdt = np.uint8 if src_bits == 8 else np.int16
+        ddt = np.uint8 if dst_bits == 8 else np.int16
+        srcs, dsts, want = [], [], []
+        for dec in DECS:
+            pw, ph = (pic_w + (1 << dec) - 1) >> dec, (pic_h + (1 << dec) - 1) >> dec
+            if src_bits == 8:
+                pic = rng.integers(0, 256, size=(nframes, ph, pw + 3)).astype(np.uint8)     # padded rows
+            else:
+                pic = rng.integers(-40, (1 << src_bits) + 40, size=(nframes, ph, pw + 3)).clip(-32768, 32767).astype(np.int16)
+            srcs.append(pic)
+            b = border >> dec
+            dsts.append(np.full((nframes, (fh >> dec) + 2 * b + 2 * guard, (fw >> dec) + 2 * b + 2 * guard), 55, ddt))
+            per = []
+            for f in range(nframes):
+                p = np.ascontiguousarray(pic[f, :, :pw])
+                if ol.have_ref():
+                    per.append(ol.ref_img_copy_pad_plane(p, src_bits, fw >> dec, fh >> dec, dec, dst_bits))
+                else:
+                    per.append(ol.port_img_copy_pad_plane(p, src_bits, fw >> dec, fh >> dec, b, dst_bits))
+            want.append(per)
+        ts = [torch.from_numpy(a).to(dev) for a in srcs]
+        td = [torch.from_numpy(a).to(dev) for a in dsts]
+        isz = np.dtype(ddt).itemsize
+        dptr = [t.data_ptr() + ((guard + (border >> dec)) * t.shape[2] + guard + (border >> dec)) * isz
+                for t, dec in zip(td, DECS)]
+        ctx.img_copy_pad_batch(dptr, [t.shape[2] * isz for t in td], [t.shape[1] * t.shape[2] * isz for t in td],
+                               isz, dst_bits, border,
+                               [t.data_ptr() for t in ts], [a.strides[1] for a in srcs], [a.strides[0] for a in srcs],
+                               np.dtype(sdt).itemsize, src_bits, nframes, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        for p, dec in enumerate(DECS):
+            got = td[p].cpu().numpy()
+            for f in range(nframes):
+                inner = got[f, guard:-guard, guard:-guard]
+                assert np.array_equal(inner, want[p][f]), "plane %d frame %d" % (p, f)
+                outer = got[f].copy()
+                outer[guard:-guard, guard:-guard] = 55
+                assert (outer == 55).all(), "wrote outside the bordered plane"
+
+
+def test_picture_to_coefficients_on_the_device():
+    """od_tdlt_img_copy_pad_batch (border 0, packed planes) feeding od_tdlt_fwd_batch_pix: an
+    8-bit 200x136 picture goes from the caller's samples to coefficients without a host pass
+    and equals the checker's forward stage of the padded picture."""
+    import torch
+    import daala_b200
+    dev = torch.device("cuda", 0)
+    pic_w, pic_h, nframes = 200, 136, 2
+    rng = np.random.default_rng(4400)
+    chk = Checker(pic_w, pic_h)
+    with _ctx(pic_w, pic_h, 0) as ctx:
+        fw, fh = ctx.frame_width, ctx.frame_height
+        bsize = make_maps("quad", nframes, ctx.nhsb, ctx.nvsb, rng)
+        pics = [rng.integers(0, 256, size=(nframes, (pic_h + d) >> d, (pic_w + d) >> d)).astype(np.uint8) for d in DECS]
+        tp = [torch.from_numpy(a).to(dev) for a in pics]
+        planes = [torch.zeros((nframes,) + s, dtype=torch.uint8, device=dev) for s in ctx.plane_shapes]
+        d = [torch.zeros((nframes,) + s, dtype=torch.int32, device=dev) for s in ctx.plane_shapes]
+        st = torch.cuda.current_stream().cuda_stream
+        ctx.img_copy_pad_batch([t.data_ptr() for t in planes], [s[1] for s in ctx.plane_shapes],
+                               [s[0] * s[1] for s in ctx.plane_shapes], 1, 8, 0,
+                               [t.data_ptr() for t in tp], [a.strides[1] for a in pics], [a.strides[0] for a in pics],
+                               1, 8, nframes, st)
+        maps = torch.from_numpy(bsize).to(dev)
+        ctx.fwd_batch_pix([t.data_ptr() for t in d], [t.data_ptr() for t in planes], maps.data_ptr(), nframes,
+                          daala_b200.OD_TDLT_KEYFRAME, 1, 1, 0, st)
+        torch.cuda.synchronize()
+        c = []
+        for p, dec in enumerate(DECS):
+            cc = np.zeros((nframes,) + ctx.plane_shapes[p], np.int32)
+            for f in range(nframes):
+                padded = ol.port_img_copy_pad_plane(np.ascontiguousarray(pics[p][f]), 8, fw >> dec, fh >> dec, 0, 8)
+                cc[f] = (padded.astype(np.int32) - 128) << 4
+            c.append(cc)
+        d_ref = chk.fwd_frames(c, bsize, DECS, 1)
+        for p in range(3):
+            assert np.array_equal(d[p].cpu().numpy(), d_ref[p]), "plane %d" % p
+    chk.close()
+
+
 # ---- reference-signature entry points (include/daala_tdlt.h section 3) --------
 def _selftest_vectors(n, rng, count):
     """The ranges of the reference's self-test (src/dct.c:3322-3391) plus impulses

@@ -517,3 +517,26 @@ def test_codec_roundtrip_harness_c_vs_simd(reflib, quality, keyframe_rate):
     else:
         err = np.abs(out0[0][0].astype(int) - frames[0][0].astype(int)).mean()
         assert err < 8, "decoded picture is far from the input (%.1f)" % err
+
+
+IMG_PAD_CASES = [(352, 288, 8, 8), (352, 288, 10, 8), (200, 136, 10, 12), (33, 17, 8, 10),
+                 (64, 64, 12, 10), (130, 70, 16, 8), (1, 1, 8, 8)]
+
+
+@pytest.mark.parametrize("pic_w,pic_h,src_bits,dst_bits", IMG_PAD_CASES)
+def test_img_copy_pad_matches_reference(reflib, pic_w, pic_h, src_bits, dst_bits):
+    """The encoder's input side: od_img_plane_copy's bit-depth conversions
+    with their clamps, the low-pass extension to the padded frame and od_img_edge_ext, luma
+    and 4:2:0 chroma planes, pictures that are no multiple of 64 (or of 2)."""
+    rng = np.random.default_rng(2300 + pic_w + src_bits)
+    fw, fh = ol.padded_dims(pic_w, pic_h)
+    for dec in (0, 1):
+        pw, ph = (pic_w + (1 << dec) - 1) >> dec, (pic_h + (1 << dec) - 1) >> dec
+        if src_bits == 8:
+            pic = rng.integers(0, 256, size=(ph, pw)).astype(np.uint8)
+        else:      # out-of-range samples too: the copy clamps
+            pic = rng.integers(-40, (1 << src_bits) + 40, size=(ph, pw)).clip(-32768, 32767).astype(np.int16)
+        a = ol.ref_img_copy_pad_plane(pic, src_bits, fw >> dec, fh >> dec, dec, dst_bits)
+        b = ol.port_img_copy_pad_plane(pic, src_bits, fw >> dec, fh >> dec, 64 >> dec, dst_bits)
+        assert a.shape == b.shape and np.array_equal(a, b), "dec %d" % dec
+        assert not (a == 77).all()
