@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("DAALA_TDLT_LIB", os.path.join(_HERE, "libdaala_tdlt_c
 OD_TDLT_KEYFRAME = 1
 OD_TDLT_HAAR = 2
 OD_TDLT_SAME_MAPS = 4
+OD_TDLT_CODING_ORDER = 8
 NPLANES_MAX = 4
 
 
@@ -101,6 +102,8 @@ def lib():
             getattr(L, f).argtypes = [vp, ci, vp, ci] + [ci] * na
             getattr(L, f).restype = None
         L.od_tdlt_opt_vtbl_init_cuda.argtypes = [vp, vp]
+        L.od_init_skipped_coeffs_cuda.argtypes = [vp, vp, ci, ci, ci, ci]
+        L.od_init_skipped_coeffs_cuda.restype = None
         L.od_tdlt_opt_vtbl_init_cuda.restype = None
         L.od_prefilter_split_cuda.argtypes = [vp, ci, ci, ci, ci, ci]
         L.od_prefilter_split_cuda.restype = None

@@ -509,6 +509,19 @@ void launch_tf_op(int op, int *dst, int dstride, const int *src, int sstride, in
   tf_ops_kernel<<<1, 256, 0, st>>>(op, dst, dstride, src, sstride, n, p0, p1, p2);
 }
 
+// od_init_skipped_coeffs (reference src/state.c:1340-1357), one block: d is n x n with row
+// stride w; keyframe: everything but the DC cleared; else d = pred (dense n x n).
+__global__ void init_skipped_kernel(int *d, const int *pred, int is_keyframe, int n, int w) {
+  for (int e = threadIdx.x; e < n*n; e += blockDim.x) {
+    const int i = e/n, j = e - i*n;
+    if (is_keyframe) { if (e) d[i*w + j] = 0; }
+    else d[i*w + j] = pred[e];
+  }
+}
+void launch_init_skipped(int *d, const int *pred, int is_keyframe, int n, int w, cudaStream_t st) {
+  init_skipped_kernel<<<1, 256, 0, st>>>(d, pred, is_keyframe, n, w);
+}
+
 void launch_pix_to_coeff(int *c, const void *pix, long long nsamples, int xstride, int shift,
                          cudaStream_t st) {
   long long n4 = nsamples/4;

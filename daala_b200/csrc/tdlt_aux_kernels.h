@@ -68,11 +68,16 @@ struct CodingParams {
   unsigned recip_nhsb;             // ceil(2^32 / nhsb): row of a superblock by multiply-high
 };
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st);
+// tab: 4*1024 + 3*256 positions (tdlt_region.cuh: kCoTabEntries), see cotab_build_kernel
+void launch_cotab_build(unsigned short *tab, const unsigned char *scan, const int lens[4],
+                        cudaStream_t st);
 
 // One block (n = 4 or 8) through one of the two deringing filters; `in` dense with its
 // 3-sample ring (pitch n + 6), x: the unfiltered block (orthogonal filter only).
 void launch_dering_block(short *y, const short *in, const short *x, int n, int thr, int dir,
                          bool orthogonal, cudaStream_t st);
+
+void launch_init_skipped(int *d, const int *pred, int is_keyframe, int n, int w, cudaStream_t st);
 
 // The encoder's input side (tdlt_input.cu): od_img_copy_pad per plane.
 struct ImgPadPlane {

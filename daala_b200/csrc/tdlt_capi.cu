@@ -51,6 +51,7 @@ struct od_tdlt_ctx {
   unsigned char *dev_bsize;
   unsigned char *dev_aux;       // od_tdlt_dering_frames: superblock flags + skip maps
   unsigned char *dev_scan;      // the caller's scan tables (od_tdlt_set_scan_tables)
+  unsigned short *dev_cotab;    // source positions for the fused coding-order store / load
   int scan_len[4];
   size_t dev_aux_bytes;
   cudaStream_t stream;          // kernels
@@ -323,6 +324,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   cudaFree(ctx->dev_bsize);
   cudaFree(ctx->dev_aux);
   cudaFree(ctx->dev_scan);
+  cudaFree(ctx->dev_cotab);
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
   cudaFree(ctx->order);
@@ -358,8 +360,9 @@ int od_tdlt_debug_set_trace(long long *dev_buf) {
 static int launch_plan(od_tdlt_ctx *ctx, const RegionBatch &rb, const unsigned char *bsize,
                        int nframes, int flags, cudaStream_t st) {
   if (flags & OD_TDLT_SAME_MAPS) {
+    // (the plan depends on the maps and on lossless mode only, not on the coding-order flag)
     if (!ctx->plan || ctx->plan_maps != bsize || ctx->plan_nframes != nframes ||
-        ctx->plan_flags != rb.flags || ctx->plan_stream != st) {
+        ctx->plan_flags != (rb.flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR)) || ctx->plan_stream != st) {
       return fail(ctx, OD_TDLT_EINVAL, "OD_TDLT_SAME_MAPS without a matching previous call");
     }
     return OD_TDLT_SUCCESS;
@@ -380,7 +383,7 @@ static int launch_plan(od_tdlt_ctx *ctx, const RegionBatch &rb, const unsigned c
   CK(ctx, cudaGetLastError());
   ctx->plan_maps = bsize;
   ctx->plan_nframes = nframes;
-  ctx->plan_flags = rb.flags;
+  ctx->plan_flags = rb.flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
   ctx->plan_stream = st;
   return OD_TDLT_SUCCESS;
 }
@@ -390,6 +393,19 @@ static int conv_shift(int xstride, int bitdepth_mode, int lossless_p) {
   // reference src/state.c:1221-1223, 1236-1238 (OD_COEFF_SHIFT == 4)
   if (xstride == 1) return lossless_p ? (bitdepth_mode - 1)*2 : 4;
   return lossless_p ? 4 - (bitdepth_mode - 1)*2 : 0;
+}
+
+// OD_TDLT_CODING_ORDER: the coefficient side is the block-linear plane of coding-order vectors.
+static int check_coding_order(od_tdlt_ctx *ctx, RegionBatch &rb) {
+  rb.cotab = nullptr;
+  if (!(rb.flags & OD_TDLT_CODING_ORDER)) return OD_TDLT_SUCCESS;
+  if (rb.flags & OD_TDLT_HAAR) {
+    return fail(ctx, OD_TDLT_EINVAL, "OD_TDLT_CODING_ORDER does not apply to lossless mode (the "
+                "reference codes the wavelet's coefficients in raster order, src/encode.c:1150-1157)");
+  }
+  if (!ctx->dev_cotab) return fail(ctx, OD_TDLT_EINVAL, "od_tdlt_set_scan_tables has not been called");
+  rb.cotab = ctx->dev_cotab;
+  return OD_TDLT_SUCCESS;
 }
 
 // The forward batch: in[] are od_coeff planes (pix_bytes 0) or planes of pix_bytes-byte
@@ -406,11 +422,12 @@ static int fwd_batch_any(od_tdlt_ctx *ctx, od_coeff *const d[], const void *cons
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.inv_nframes = 1.0f/(float)nframes;
-  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
+  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR | OD_TDLT_CODING_ORDER);
   rb.pix_shift = pix_shift;
   if (pix_bytes && (rb.flags & OD_TDLT_HAAR)) {
     return fail(ctx, OD_TDLT_EINVAL, "the fused pixel path has no lossless (OD_TDLT_HAAR) form");
   }
+  if (int crc = check_coding_order(ctx, rb)) return crc;
   PlanePtrs out;
   memset(&out, 0, sizeof(out));
   for (int p = 0; p < rb.nplanes; p++) {
@@ -540,15 +557,17 @@ static int inv_batch_any(od_tdlt_ctx *ctx, void *const outp[], const od_coeff *c
   RegionBatch rb = ctx->rb;
   rb.nframes = nframes;
   rb.inv_nframes = 1.0f/(float)nframes;
-  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR);
+  rb.flags = flags & (OD_TDLT_KEYFRAME | OD_TDLT_HAAR | OD_TDLT_CODING_ORDER);
   rb.pix_shift = pix_shift;
   if (pix_bytes && (rb.flags & OD_TDLT_HAAR)) {
     return fail(ctx, OD_TDLT_EINVAL, "the fused pixel path has no lossless (OD_TDLT_HAAR) form");
   }
+  if (int crc = check_coding_order(ctx, rb)) return crc;
   TmapSet maps;
   memset(&maps, 0, sizeof(maps));
-  PlanePtrs out;
+  PlanePtrs out, inp;
   memset(&out, 0, sizeof(out));
+  memset(&inp, 0, sizeof(inp));
   for (int p = 0; p < rb.nplanes; p++) {
     if (((uintptr_t)outp[p] | (uintptr_t)d[p]) & 15) {
       return fail(ctx, OD_TDLT_EINVAL, "plane pointers must be 16-byte aligned");
@@ -560,6 +579,7 @@ static int inv_batch_any(od_tdlt_ctx *ctx, void *const outp[], const od_coeff *c
     int trc = make_tmap(ctx, &maps.in[p], d[p], rb.pl[p].w, rb.pl[p].h, nframes, kAP, kARegRows);
     if (trc) return trc;
     out.p[p] = reinterpret_cast<int *>(outp[p]);
+    inp.p[p] = const_cast<int *>(d[p]);
   }
   long long total = (long long)rb.regs_per_frame*nframes;
   int rc = ensure_scratch(ctx, total);
@@ -575,19 +595,19 @@ static int inv_batch_any(od_tdlt_ctx *ctx, void *const outp[], const od_coeff *c
   const unsigned grid = (unsigned)total;
   if (rb.flags & OD_TDLT_HAAR) {
     tdlt_inv_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
-        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order, inp);
   }
   else if (pix_bytes == 1) {
     tdlt_inv_region_pix8_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
-        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order, inp);
   }
   else if (pix_bytes == 2) {
     tdlt_inv_region_pix16_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
-        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order, inp);
   }
   else {
     tdlt_inv_region_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
-        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order);
+        maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order, inp);
   }
   g_launches++;
   CK(ctx, cudaGetLastError());
@@ -762,6 +782,13 @@ int od_tdlt_set_scan_tables(od_tdlt_ctx *ctx, const unsigned char *const tables[
   if (!ctx->dev_scan) CK(ctx, cudaMalloc(&ctx->dev_scan, sizeof(host)));
   CK(ctx, cudaMemcpy(ctx->dev_scan, host, sizeof(host), cudaMemcpyHostToDevice));
   for (int k = 0; k < 4; k++) ctx->scan_len[k] = lens[k];
+  // where every entry of a superblock's block-linear range comes from, per block size: what
+  // the transform kernels' fused coding-order store / load read (OD_TDLT_CODING_ORDER)
+  if (!ctx->dev_cotab) CK(ctx, cudaMalloc(&ctx->dev_cotab, kCoTabEntries*sizeof(unsigned short)));
+  launch_cotab_build(ctx->dev_cotab, ctx->dev_scan, ctx->scan_len, 0);
+  g_launches++;
+  CK(ctx, cudaGetLastError());
+  CK(ctx, cudaDeviceSynchronize());
   return OD_TDLT_SUCCESS;
 }
 
@@ -1203,6 +1230,17 @@ void dct_one(int bs, bool inverse, od_coeff *out, int ostride, const od_coeff *i
 }  // namespace
 
 extern "C" {
+
+void od_init_skipped_coeffs_cuda(od_coeff *d, od_coeff *pred, int is_keyframe, int bo, int n, int w) {
+  if (n < 1 || n > 64 || w < n) die("od_init_skipped_coeffs: bad block", cudaErrorInvalidValue);
+  int *dd = g_scratch.A((size_t)n*n), *dp = g_scratch.B((size_t)n*n);
+  h2d_rect(dd, d + bo, w, n, n);
+  if (!is_keyframe) CKF(cudaMemcpy(dp, pred, sizeof(int)*n*n, cudaMemcpyHostToDevice));
+  launch_init_skipped(dd, dp, is_keyframe, n, n, 0);
+  g_launches++;
+  CKF(cudaGetLastError());
+  d2h_rect(d + bo, w, dd, n, n);
+}
 
 void od_bin_fdct4x4_cuda(od_coeff *y, int ys, const od_coeff *x, int xs) { dct_one(0, false, y, ys, x, xs); }
 void od_bin_idct4x4_cuda(od_coeff *x, int xs, const od_coeff *y, int ys) { dct_one(0, true, x, xs, y, ys); }

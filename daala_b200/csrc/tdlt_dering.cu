@@ -675,6 +675,30 @@ __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P
   }
 }
 
+// The same tabulation in global memory, once per od_tdlt_set_scan_tables, for the transform
+// kernels' fused coding-order store / load (OD_TDLT_CODING_ORDER): 4 x 1024 entries for
+// planes at full size, then 3 x 256 for 4:2:0 chroma (kCoTabEntries in tdlt_region.cuh).
+__global__ void cotab_build_kernel(unsigned short *tab, const unsigned char *scan, int l0, int l1,
+                                   int l2, int l3) {
+  __shared__ unsigned short s_scan[kScanEntries];
+  __shared__ int s_len[4];
+  for (int i = threadIdx.x; i < kScanEntries; i += blockDim.x) {
+    s_scan[i] = reinterpret_cast<const unsigned short *>(scan)[i];
+  }
+  if (threadIdx.x == 0) { s_len[0] = l0; s_len[1] = l1; s_len[2] = l2; s_len[3] = l3; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4*kSB*kSB; i += blockDim.x) {
+    tab[i] = coding_source_pos<0>(i & (kSB*kSB - 1), i >> 10, s_scan, s_len);
+  }
+  for (int i = threadIdx.x; i < 3*(kSB/2)*(kSB/2); i += blockDim.x) {
+    tab[4*kSB*kSB + i] = coding_source_pos<1>(i & 255, i >> 8, s_scan, s_len);
+  }
+}
+void launch_cotab_build(unsigned short *tab, const unsigned char *scan, const int lens[4],
+                        cudaStream_t st) {
+  cotab_build_kernel<<<1, 256, 0, st>>>(tab, scan, lens[0], lens[1], lens[2], lens[3]);
+}
+
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st) {
   const long long nunits = (long long)(P.nhsb/2)*P.nvsb*nframes;   // pairs of superblocks
   const long long cap = 148ll*12;                       // a fixed grid walks the superblocks (6 and 12

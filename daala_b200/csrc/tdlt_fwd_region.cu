@@ -157,14 +157,21 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
     const int TX = X0 + 32*tx, TY = Y0 + 32*ty;
     if (TX < pd.w && TY < pd.h) {
       int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;
+      const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
       if (haar) {
         region_haar_tile<false>(At, lane, 32 >> pd.dec);
       }
       else if ((bd.flags & 1) && !(TDLT_ABLATE & 4)) {
-        const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
         region_dc_merge_tile(At, ls0, lane, pd.dec == 0);
       }
-      if (!(TDLT_ABLATE & 16)) {
+      if (!haar && (bd.flags & kFlagCodingOrder)) {
+        // the tile leaves as the coding-order vectors of its blocks (block-linear plane)
+        const int lS = 5 - pd.dec, sbw = pd.w >> lS;
+        int *gtile = out.p[id.pli] + (size_t)id.frame*pd.w*pd.h +
+                     ((size_t)(TY >> lS)*sbw + (TX >> lS))*(size_t)(1 << 2*lS);
+        region_store_tile_coding(At, ls0, bd.cotab, pd.dec, gtile, sbw << 2*lS, lane);
+      }
+      else if (!(TDLT_ABLATE & 16)) {
         int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + TY + (lane >> 3))*pd.w + TX + 4*(lane & 7);
         const int *a = At + (lane >> 3)*kAP + 4*(lane & 7);
 #pragma unroll

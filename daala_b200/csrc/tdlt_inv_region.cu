@@ -88,7 +88,7 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
                        const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
-                       const unsigned short *__restrict__ order) {
+                       const unsigned short *__restrict__ order, PlanePtrs in) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const RegionSmem s = carve_region(smem);
@@ -126,9 +126,13 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   // ---- the region's coefficients: the same TMA box as the forward kernel's (the halo
   // part of it is neighbours' coefficients, of no use here: the ring of raw samples
   // replaces it below), and the region's plan record (tdlt_plan.cu), on one mbarrier
+  const bool coding = !kHaar && (bd.flags & kFlagCodingOrder);
   if (tid == 0) {
-    mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
-    tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    if (coding) mbar_expect_tx(s.bar, kPlanBytes);      // the tiles are gathered below
+    else {
+      mbar_expect_tx(s.bar, kARegBytes + kPlanBytes);
+      tma_load_3d(s.A, &maps.in[id.pli], s.bar, X0 - 4, Y0 - 2, id.frame);
+    }
     bulk_g2s(s.ls, plan + (size_t)lin*kPlanBytes, kPlanBytes, s.bar);
   }
   // ---- the ring of raw samples from the regions above / left / above-left: one
@@ -156,6 +160,17 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   const int tx = warp & 3, ty = warp >> 2;
   const bool tile_on = X0 + 32*tx < pd.w && Y0 + 32*ty < pd.h;
   int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;      // warp w <-> tile w
+  if (coding) {
+    // the region's coefficients arrive as coding-order vectors (block-linear plane): every
+    // warp scatters its tile to its raster place in A
+    if (tile_on) {
+      const int lS = 5 - pd.dec, sbw = pd.w >> lS;
+      int *gtile = in.p[id.pli] + (size_t)id.frame*pd.w*pd.h +
+                   ((size_t)((Y0 + 32*ty) >> lS)*sbw + ((X0 + 32*tx) >> lS))*(size_t)(1 << 2*lS);
+      region_load_tile_coding(At, s.ls + ut(4*ty, 4*tx), bd.cotab, pd.dec, gtile, sbw << 2*lS, lane);
+    }
+    __syncthreads();
+  }
 
   if (haar) {
     // No lapping in lossless mode: every tile is stored where it lies.
@@ -330,8 +345,8 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
-                       const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<false, 0>(maps, bd, plan, out, strips, ticket, epoch, order);
+                       const unsigned short *__restrict__ order, PlanePtrs in) {
+  tdlt_inv_region_body<false, 0>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 
 // The same with od_coeff_to_ref_buf fused into the store: out.p[] are planes of 8-bit (pix8)
@@ -341,16 +356,16 @@ tdlt_inv_region_pix8_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
-                       const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<false, 1>(maps, bd, plan, out, strips, ticket, epoch, order);
+                       const unsigned short *__restrict__ order, PlanePtrs in) {
+  tdlt_inv_region_body<false, 1>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
-                       const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<false, 2>(maps, bd, plan, out, strips, ticket, epoch, order);
+                       const unsigned short *__restrict__ order, PlanePtrs in) {
+  tdlt_inv_region_body<false, 2>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 
 // Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
@@ -359,8 +374,8 @@ tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                        const __grid_constant__ RegionBatch bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
-                       const unsigned short *__restrict__ order) {
-  tdlt_inv_region_body<true, 0>(maps, bd, plan, out, strips, ticket, epoch, order);
+                       const unsigned short *__restrict__ order, PlanePtrs in) {
+  tdlt_inv_region_body<true, 0>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 
 

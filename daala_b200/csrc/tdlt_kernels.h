@@ -38,25 +38,25 @@ __global__ void tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                                        const unsigned char *__restrict__ plan,
                                        PlanePtrs out, int2 *__restrict__ strips,
                                        int *__restrict__ ticket, int epoch,
-                                       const unsigned short *__restrict__ order);
+                                       const unsigned short *__restrict__ order, PlanePtrs in);
 __global__ void tdlt_inv_region_pix8_kernel(const __grid_constant__ TmapSet maps,
                                             const __grid_constant__ RegionBatch bd,
                                             const unsigned char *__restrict__ plan,
                                             PlanePtrs out, int2 *__restrict__ strips,
                                             int *__restrict__ ticket, int epoch,
-                                            const unsigned short *__restrict__ order);
+                                            const unsigned short *__restrict__ order, PlanePtrs in);
 __global__ void tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
                                              const __grid_constant__ RegionBatch bd,
                                              const unsigned char *__restrict__ plan,
                                              PlanePtrs out, int2 *__restrict__ strips,
                                              int *__restrict__ ticket, int epoch,
-                                             const unsigned short *__restrict__ order);
+                                             const unsigned short *__restrict__ order, PlanePtrs in);
 __global__ void tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                                      const __grid_constant__ RegionBatch bd,
                                      const unsigned char *__restrict__ plan,
                                      PlanePtrs out, int2 *__restrict__ strips,
                                      int *__restrict__ ticket, int epoch,
-                                     const unsigned short *__restrict__ order);
+                                     const unsigned short *__restrict__ order, PlanePtrs in);
 constexpr int kRegionStripInts = 2*kRegW + 2*kRegH;
 
 }  // namespace tdlt

@@ -109,8 +109,9 @@ struct RegionBatch {
   float inv_nframes;      // 1 / nframes
   int pic_w, pic_h;      // LUMA picture size (gates the split filters)
   int bw, bh;            // block-size map: entries across / down (8x8 luma units)
-  int flags;             // OD_TDLT_KEYFRAME | OD_TDLT_HAAR
+  int flags;             // OD_TDLT_KEYFRAME | OD_TDLT_HAAR | kFlagCodingOrder
   int pix_shift;         // fused pixel conversion: the shift of src/state.c:1221-1223 / 1236-1238
+  const unsigned short *cotab;   // fused coding order: source positions (kCoTabEntries), or null
 };
 
 struct RegionId {
@@ -465,6 +466,119 @@ __device__ __forceinline__ void region_store_owned_pix(const int *A, unsigned ch
       const unsigned q0 = coeff_to_pix1<kPix>(l.x, shift), q1 = coeff_to_pix1<kPix>(l.y, shift);
       if (kPix == 1) *reinterpret_cast<unsigned short *>(grow - 2) = (unsigned short)(q0 | (q1 << 8));
       else *reinterpret_cast<unsigned *>(grow - 4) = q0 | (q1 << 16);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Fused coding order (OD_TDLT_CODING_ORDER; reference od_raster_to_coding_order /
+// od_coding_order_to_raster, src/partition.c:143-199, as od_block_encode / od_block_decode
+// call them per block, src/encode.c:1160-1161, 1219-1220, src/decode.c:580-581, 630): the
+// forward kernel stores, and the inverse kernel loads, the BLOCK-LINEAR plane of coding-order
+// vectors (layout: include/daala_tdlt.h, od_tdlt_coding_order_batch) instead of the raster
+// plane, so the permutation never costs a pass of its own.  Where entry e of a superblock's
+// range comes from depends on e and the size of the block it lies in only; cotab (built once
+// per od_tdlt_set_scan_tables, tdlt_dering.cu) holds that position, row*S + column inside the
+// superblock or kCoNoPos where the scans order nothing (the second half of a 32x32 block).
+// A warp takes its tile: one 32x32 superblock of a full-size plane, or 2x2 superblocks of 16x16
+// of a 4:2:0 chroma plane -- 1024 entries either way, four consecutive entries per lane and
+// step (they lie in one 4x4 unit, hence in one block), eight steps.
+// ---------------------------------------------------------------------------
+constexpr int kFlagCodingOrder = 8;
+constexpr int kCoTabEntries = 4*1024 + 3*256;
+constexpr unsigned kCoNoPos = 0xffff;
+
+struct CoSite {
+  int4 *vec;            // the four entries in the block-linear plane
+  int a[4];             // word offsets from the tile's origin in A, or -1 (entry not ordered)
+};
+// gtile -> the block-linear plane entry of the tile's first superblock; sbstep = entries from
+// a superblock to the one below it (4:2:0 chroma only).
+__device__ __forceinline__ CoSite co_site(const unsigned short *__restrict__ cotab,
+                                          const unsigned char *ls0, int dec, int it, int lane,
+                                          int *gtile, int sbstep) {
+  CoSite c;
+  const int idx = 128*it + 4*lane;
+  int e, rowoff, coloff, L;
+  uint2 pk;
+  if (dec == 0) {
+    e = idx;
+    const int z = e >> 4;      // Z order of the 4x4 unit: x bit 0, y bit 0, x bit 1, ...
+    const int ux = (z & 1) | ((z >> 1) & 2) | ((z >> 2) & 4), uy = ((z >> 1) & 1) | ((z >> 2) & 2) | ((z >> 3) & 4);
+    L = ls0[(uy >> 1)*kUS + (ux >> 1)];
+    pk = __ldg(reinterpret_cast<const uint2 *>(cotab + (L << 10) + e));
+    rowoff = 0; coloff = 0;
+    c.vec = reinterpret_cast<int4 *>(gtile + e);
+  }
+  else {
+    const int sb = idx >> 8, sx = sb & 1, sy = sb >> 1;
+    e = idx & 255;
+    const int z = e >> 4;
+    const int ux = (z & 1) | ((z >> 1) & 2), uy = ((z >> 1) & 1) | ((z >> 2) & 2);
+    L = ls0[(2*sy + (uy >> 1))*kUS + 2*sx + (ux >> 1)];
+    pk = __ldg(reinterpret_cast<const uint2 *>(cotab + 4*1024 + (L << 8) + e));
+    rowoff = 16*sy; coloff = 16*sx;
+    c.vec = reinterpret_cast<int4 *>(gtile + sy*sbstep + sx*256 + e);
+  }
+  const unsigned p[4] = {pk.x & 0xffff, pk.x >> 16, pk.y & 0xffff, pk.y >> 16};
+  const int sh = 5 - dec, msk = (32 >> dec) - 1;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    c.a[k] = p[k] == kCoNoPos ? -1 : (rowoff + (int)(p[k] >> sh))*kAP + coloff + (int)(p[k] & msk);
+  }
+  return c;
+}
+
+// Forward: the tile leaves as coding-order vectors.  Entries the scans do not order are left
+// as they are in the destination, as the reference leaves them.
+__device__ __forceinline__ void region_store_tile_coding(const int *At, const unsigned char *ls0,
+                                                         const unsigned short *cotab, int dec,
+                                                         int *gtile, int sbstep, int lane) {
+#pragma unroll 2
+  for (int it = 0; it < 8; it++) {
+    const CoSite c = co_site(cotab, ls0, dec, it, lane, gtile, sbstep);
+    int v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = c.a[k] >= 0 ? At[c.a[k]] : 0;
+    if ((c.a[0] | c.a[1] | c.a[2] | c.a[3]) >= 0) *c.vec = make_int4(v[0], v[1], v[2], v[3]);
+    else {
+      int *g = reinterpret_cast<int *>(c.vec);
+#pragma unroll
+      for (int k = 0; k < 4; k++) if (c.a[k] >= 0) g[k] = v[k];
+    }
+  }
+}
+// Inverse: the tile arrives as coding-order vectors and is scattered to its raster place in
+// A; what the scans do not order starts at zero (od_init_skipped_coeffs on a keyframe,
+// src/state.c:1340-1349: everything but the vector's entries is cleared first).
+__device__ __forceinline__ void region_load_tile_coding(int *At, const unsigned char *ls0,
+                                                        const unsigned short *cotab, int dec,
+                                                        int *gtile, int sbstep, int lane) {
+  {
+    int4 *row = reinterpret_cast<int4 *>(At + (lane >> 3)*kAP + 4*(lane & 7));
+#pragma unroll
+    for (int it = 0; it < 8; it++) row[it*kAP] = make_int4(0, 0, 0, 0);    // 4 rows per step
+  }
+  __syncwarp();
+  // four vectors in flight per lane before the first scatter (the loads are plain global
+  // loads here, not a TMA box: their latency is this warp's to hide)
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    int4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int idx = 128*(4*h + k) + 4*lane;
+      const int *src = dec == 0 ? gtile + idx
+                                : gtile + (idx >> 9)*sbstep + ((idx >> 8) & 1)*256 + (idx & 255);
+      v[k] = __ldg(reinterpret_cast<const int4 *>(src));
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const CoSite c = co_site(cotab, ls0, dec, 4*h + k, lane, gtile, sbstep);
+      if (c.a[0] >= 0) At[c.a[0]] = v[k].x;
+      if (c.a[1] >= 0) At[c.a[1]] = v[k].y;
+      if (c.a[2] >= 0) At[c.a[2]] = v[k].z;
+      if (c.a[3] >= 0) At[c.a[3]] = v[k].w;
     }
   }
 }

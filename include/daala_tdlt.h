@@ -60,6 +60,19 @@ typedef int32_t od_coeff;
                                   :2506-2533): the per-region plan built from the maps
                                   by that call is reused instead of rebuilt.
                                   OD_TDLT_EINVAL if there is no such plan. */
+#define OD_TDLT_CODING_ORDER (8) /* the coefficient side of the call is the BLOCK-LINEAR plane
+                                  of coding-order vectors (layout: od_tdlt_coding_order_batch
+                                  below) instead of the raster plane: the forward stage
+                                  stores every block as od_raster_to_coding_order would
+                                  (src/partition.c:143-170; call sites src/encode.c:1160-1161),
+                                  the inverse stage loads it as od_coding_order_to_raster
+                                  does after od_init_skipped_coeffs on a keyframe
+                                  (src/state.c:1340-1349, src/encode.c:1219-1220,
+                                  src/decode.c:580-581, 630): entries the scans do not
+                                  order (half of a 32x32 block) are left alone by the
+                                  forward store and read as zero by the inverse load.
+                                  Needs od_tdlt_set_scan_tables; not with OD_TDLT_HAAR.
+                                  The permutation then costs no pass of its own. */
 
 /* Geometry of a stream; mirrors the fields of daala_info / od_state the path
    reads (reference src/state.c:366-375, 393-394). */
@@ -303,6 +316,11 @@ void od_bin_idct32x32_cuda(od_coeff *x, int xstride, const od_coeff *y, int ystr
 typedef void (*od_tdlt_dct_func_2d)(od_coeff *out, int out_stride, const od_coeff *in,
  int in_stride);
 void od_tdlt_opt_vtbl_init_cuda(od_tdlt_dct_func_2d fdct_2d[], od_tdlt_dct_func_2d idct_2d[]);
+/* od_init_skipped_coeffs, reference src/state.c:1340-1357 (call sites src/encode.c:1219,
+   src/decode.c:580): the block at d + bo (n x n, row stride w) is prepared for
+   od_coding_order_to_raster -- on a keyframe everything but the DC is cleared, else the block
+   takes the prediction pred (n x n, dense). */
+void od_init_skipped_coeffs_cuda(od_coeff *d, od_coeff *pred, int is_keyframe, int bo, int n, int w);
 
 /* The deringing filters of the same table (od_filter_dering_direction_func /
    od_filter_dering_orthogonal_func, src/filter.h:46-65; entries [0] = 4x4, [1] = 8x8,

@@ -678,6 +678,128 @@ def test_coding_order_frames_match_checker(pic_w, pic_h, kind, decs):
             assert np.array_equal(back[p][covered], d[p][covered])
 
 
+@pytest.mark.parametrize("pic_w,pic_h,kind,decs,pix", [
+    (352, 288, "quad", (0, 1, 1), 0), (352, 288, "uniform3", (0, 1, 1), 0), (200, 136, "deep", (0, 1, 1), 1),
+    (352, 288, "quad", (0, 0, 0), 0), (1920, 1080, "quad", (0, 1, 1), 1), (64, 64, "uniform0", (0, 1, 1), 0)])
+def test_fused_coding_order_store_and_load(pic_w, pic_h, kind, decs, pix):
+    """OD_TDLT_CODING_ORDER: the forward kernel's store writes every block's coding-order
+    vector (block-linear plane) and the inverse kernel's load reads it, with no permutation
+    pass.  Forward: equal to the checker's forward stage followed by the REFERENCE's
+    od_raster_to_coding_order block by block (the restatement where the reference is absent),
+    entries the scans do not order untouched.  Inverse: equal to od_init_skipped_coeffs
+    (keyframe: cleared) + od_coding_order_to_raster + the checker's inverse stage.  Also from
+    / to 8-bit pixels (pix)."""
+    import torch
+    import daala_b200
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(4500 + pic_w + len(kind))
+    nframes = 2
+    tables = ol.scan_tables()
+    chk = Checker(pic_w, pic_h) if decs == DECS else None
+    KEY, CO = daala_b200.OD_TDLT_KEYFRAME, daala_b200.OD_TDLT_CODING_ORDER
+    with _ctx(pic_w, pic_h, 0, decs=decs) as ctx:
+        bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+        maps = torch.from_numpy(bsize).to(dev)
+        st = torch.cuda.current_stream().cuda_stream
+        if pix:
+            px_np = [rng.integers(0, 256, size=(nframes,) + s).astype(np.uint8) for s in ctx.plane_shapes]
+            c_np = [(a.astype(np.int32) - 128) << 4 for a in px_np]
+            px = [torch.from_numpy(a).to(dev) for a in px_np]
+        else:
+            c_np = _rand_planes(ctx.plane_shapes, nframes, rng)
+        c = [torch.from_numpy(a).to(dev) for a in c_np]
+        d = [torch.empty_like(t) for t in c]
+        v = [torch.full_like(t, 424242) for t in c]
+        ptrs = lambda ts: [t.data_ptr() for t in ts]  # noqa: E731
+        with pytest.raises(daala_b200.TdltError):       # no scan tables yet
+            ctx.fwd_batch(ptrs(v), ptrs(c), maps.data_ptr(), nframes, KEY | CO, st)
+        ctx.set_scan_tables(tables, ol.SCAN_LEN)
+        ctx.fwd_batch(ptrs(d), ptrs(c), maps.data_ptr(), nframes, KEY, st)
+        if pix:
+            ctx.fwd_batch_pix(ptrs(v), ptrs(px), maps.data_ptr(), nframes, KEY | CO, 1, 1, 0, st)
+        else:
+            ctx.fwd_batch(ptrs(v), ptrs(c), maps.data_ptr(), nframes, KEY | CO, st)
+        torch.cuda.synchronize()
+        d_np = [t.cpu().numpy() for t in d]
+        v_np = [t.cpu().numpy() for t in v]
+        if chk is not None and pic_w < 1000:
+            d_ref = chk.fwd_frames(c_np, bsize, decs, 1)
+            for p in range(3):
+                assert np.array_equal(d_np[p], d_ref[p])
+        d0 = []
+        for p, dec in enumerate(decs):
+            zeroed = np.zeros_like(d_np[p])
+            for f in range(nframes):
+                if ol.have_ref() and pic_w < 1000:
+                    want = ol.ref_coding_order_plane_c(d_np[p][f], bsize[f], dec, True,
+                                                       out=np.full_like(d_np[p][f], 424242))
+                else:
+                    want = ol.port_coding_order_plane(d_np[p][f], bsize[f], dec, tables, True,
+                                                      out=np.full_like(d_np[p][f], 424242))
+                assert np.array_equal(v_np[p][f], want), "fused store, plane %d frame %d" % (p, f)
+                # what the decoder side holds before its inverse transforms: cleared block
+                # (od_init_skipped_coeffs, keyframe) + od_coding_order_to_raster
+                zeroed[f] = ol.port_coding_order_plane(want, bsize[f], dec, tables, False,
+                                                       out=np.zeros_like(d_np[p][f]))
+            d0.append(zeroed)
+        # ---- inverse, straight from the vectors (the sentinel entries must read as zero) ----
+        td0 = [torch.from_numpy(a).to(dev) for a in d0]
+        c_a = [torch.empty_like(t) for t in c]
+        c_b = [torch.empty_like(t) for t in c]
+        ctx.inv_batch(ptrs(c_a), ptrs(td0), maps.data_ptr(), nframes, KEY, st)
+        if pix:
+            o_a = [torch.empty_like(t) for t in px]
+            o_b = [torch.empty_like(t) for t in px]
+            for p in range(len(decs)):
+                ctx.coeff_to_pix_batch(o_a[p].data_ptr(), c_a[p].data_ptr(), p, nframes, 1, 1, 0, st)
+            ctx.inv_batch_pix(ptrs(o_b), ptrs(v), maps.data_ptr(), nframes, KEY | CO, 1, 1, 0, st)
+            torch.cuda.synchronize()
+            for p in range(len(decs)):
+                assert torch.equal(o_a[p], o_b[p]), "fused load to pixels, plane %d" % p
+        else:
+            ctx.inv_batch(ptrs(c_b), ptrs(v), maps.data_ptr(), nframes, KEY | CO, st)
+            torch.cuda.synchronize()
+            for p in range(len(decs)):
+                assert torch.equal(c_a[p], c_b[p]), "fused load, plane %d" % p
+        if chk is not None and pic_w < 1000:
+            c_ref = chk.inv_frames(d0, bsize, decs, 1)
+            for p in range(3):
+                assert np.array_equal(c_a[p].cpu().numpy(), c_ref[p])
+        with pytest.raises(daala_b200.TdltError):       # lossless mode codes in raster order
+            ctx.fwd_batch(ptrs(v), ptrs(c), maps.data_ptr(), nframes, KEY | CO | daala_b200.OD_TDLT_HAAR, st)
+    if chk is not None:
+        chk.close()
+
+
+def test_init_skipped_coeffs_wrapper():
+    """od_init_skipped_coeffs with the reference's signature (src/state.c:1340-1357)."""
+    import daala_b200
+    L = daala_b200.lib()
+    rng = np.random.default_rng(4600)
+    for n in (4, 8, 16, 32):
+        for key in (1, 0):
+            w, bo = n + 11, 3 * (n + 11) + 5
+            d = rng.integers(-30000, 30000, size=(n + 8, w)).astype(np.int32)
+            pred = rng.integers(-30000, 30000, size=(n, n)).astype(np.int32)
+            want = d.copy()
+            blk = want.reshape(-1)[bo:].reshape(-1)
+            if ol.have_ref():
+                R = ol.ref()
+                R.od_init_skipped_coeffs.restype = None
+                R.od_init_skipped_coeffs(ol.ptr(want), ol.ptr(pred), key, bo, n, w)
+            else:
+                for i in range(n):
+                    for j in range(n):
+                        if key:
+                            if i or j:
+                                blk[i * w + j] = 0
+                        else:
+                            blk[i * w + j] = pred[i, j]
+            got = d.copy()
+            L.od_init_skipped_coeffs_cuda(got.ctypes.data, pred.ctypes.data, key, bo, n, w)
+            assert np.array_equal(got, want), "n %d keyframe %d" % (n, key)
+
+
 def test_coding_order_needs_tables():
     import daala_b200
     with _ctx(64, 64, 1) as ctx:

@@ -93,6 +93,32 @@ def main():
                                              out=np.full(want.shape, 1 << 30, np.int32)) != (1 << 30)
         assert np.array_equal(back[p][0].cpu().numpy()[covered], d[p][0].cpu().numpy()[covered])
     line["parity"] = "frame 0 equal to the oracle, round trip exact on the ordered coefficients"
+    # ---- the permutation fused into the transform kernels (OD_TDLT_CODING_ORDER) -------------
+    # forward: coefficients leave as vectors; inverse: they arrive as vectors.  Timed against
+    # the same kernels writing / reading the raster plane (plan kernel included in the forward).
+    KEY, CO = daala_b200.OD_TDLT_KEYFRAME, daala_b200.OD_TDLT_CODING_ORDER
+    SAME = daala_b200.OD_TDLT_SAME_MAPS
+    c = [(t >> 4) for t in d]                      # spatial-domain stand-in, 12-bit range
+    fused = {}
+    for name, fn in (("fwd_raster", lambda: ctx.fwd_batch(bp, [t.data_ptr() for t in c], maps.data_ptr(), nframes, KEY, st)),
+                     ("fwd_coding", lambda: ctx.fwd_batch(vp, [t.data_ptr() for t in c], maps.data_ptr(), nframes, KEY | CO, st)),
+                     ("inv_raster", lambda: ctx.inv_batch(dp, bp, maps.data_ptr(), nframes, KEY | SAME, st)),
+                     ("inv_coding", lambda: ctx.inv_batch(dp, vp, maps.data_ptr(), nframes, KEY | CO | SAME, st))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(args.steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        fused[name + "_ms"] = round(e0.elapsed_time(e1) / args.steps, 4)
+    fused["fwd_ratio"] = round(fused["fwd_coding_ms"] / fused["fwd_raster_ms"], 3)
+    fused["inv_ratio"] = round(fused["inv_coding_ms"] / fused["inv_raster_ms"], 3)
+    fused["note"] = ("OD_TDLT_CODING_ORDER: the forward kernel stores, the inverse kernel loads the "
+                     "block-linear vectors; against the standalone pass above the permutation costs "
+                     "(coding - raster) ms instead of to_coding_ms / to_raster_ms")
+    line["fused"] = fused
     if not args.no_cpu:
         a = [t[0].cpu().numpy() for t in d]
         use_ref = ol.have_ref()
