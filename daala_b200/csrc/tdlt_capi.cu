@@ -280,9 +280,11 @@ int od_tdlt_ctx_create(od_tdlt_ctx **out, const od_tdlt_geometry *g, int device,
     cudaFuncSetAttribute(tdlt_fwd_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     cudaFuncSetAttribute(tdlt_inv_haar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
     {
-      const void *pixk[4] = {(const void *)tdlt_fwd_region_pix8_kernel, (const void *)tdlt_fwd_region_pix16_kernel,
-                             (const void *)tdlt_inv_region_pix8_kernel, (const void *)tdlt_inv_region_pix16_kernel};
-      for (int k = 0; k < 4; k++) {
+      const void *pixk[7] = {(const void *)tdlt_fwd_region_pix8_kernel, (const void *)tdlt_fwd_region_pix16_kernel,
+                             (const void *)tdlt_inv_region_pix8_kernel, (const void *)tdlt_inv_region_pix16_kernel,
+                             (const void *)tdlt_inv_region_co_kernel, (const void *)tdlt_inv_region_co_pix8_kernel,
+                             (const void *)tdlt_inv_region_co_pix16_kernel};
+      for (int k = 0; k < 7; k++) {
         cudaFuncSetAttribute(pixk[k], cudaFuncAttributeMaxDynamicSharedMemorySize, kRegSmemBytes);
         cudaFuncSetAttribute(pixk[k], cudaFuncAttributePreferredSharedMemoryCarveout, 100);
       }
@@ -593,7 +595,13 @@ static int inv_batch_any(od_tdlt_ctx *ctx, void *const outp[], const od_coeff *c
   const unsigned short *order =
       ctx->order + (size_t)(nframes >= 48 ? 0 : (nframes >= 16 ? 1 : 2))*rb.regs_per_frame;
   const unsigned grid = (unsigned)total;
-  if (rb.flags & OD_TDLT_HAAR) {
+  if (rb.flags & OD_TDLT_CODING_ORDER) {
+    auto k = pix_bytes == 1 ? tdlt_inv_region_co_pix8_kernel
+             : (pix_bytes == 2 ? tdlt_inv_region_co_pix16_kernel : tdlt_inv_region_co_kernel);
+    k<<<grid, kRegThreads, kRegSmemBytes, st>>>(maps, rb, ctx->plan, out, ctx->strips, ctx->ticket,
+                                                ctx->epoch, order, inp);
+  }
+  else if (rb.flags & OD_TDLT_HAAR) {
     tdlt_inv_haar_kernel<<<grid, kRegThreads, kRegSmemBytes, st>>>(
         maps, rb, ctx->plan, out, ctx->strips, ctx->ticket, ctx->epoch, order, inp);
   }

@@ -83,7 +83,7 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
-template <bool kHaar, int kPix>
+template <bool kHaar, int kPix, bool kCoding>
 __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
                        const RegionBatch &bd,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
@@ -126,7 +126,7 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   // ---- the region's coefficients: the same TMA box as the forward kernel's (the halo
   // part of it is neighbours' coefficients, of no use here: the ring of raw samples
   // replaces it below), and the region's plan record (tdlt_plan.cu), on one mbarrier
-  const bool coding = !kHaar && (bd.flags & kFlagCodingOrder);
+  constexpr bool coding = kCoding;      // a kernel of its own: the raster kernels carry none of it
   if (tid == 0) {
     if (coding) mbar_expect_tx(s.bar, kPlanBytes);      // the tiles are gathered below
     else {
@@ -346,7 +346,7 @@ tdlt_inv_region_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order, PlanePtrs in) {
-  tdlt_inv_region_body<false, 0>(maps, bd, plan, out, strips, ticket, epoch, order, in);
+  tdlt_inv_region_body<false, 0, false>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 
 // The same with od_coeff_to_ref_buf fused into the store: out.p[] are planes of 8-bit (pix8)
@@ -357,7 +357,7 @@ tdlt_inv_region_pix8_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order, PlanePtrs in) {
-  tdlt_inv_region_body<false, 1>(maps, bd, plan, out, strips, ticket, epoch, order, in);
+  tdlt_inv_region_body<false, 1, false>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
 tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
@@ -365,8 +365,20 @@ tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order, PlanePtrs in) {
-  tdlt_inv_region_body<false, 2>(maps, bd, plan, out, strips, ticket, epoch, order, in);
+  tdlt_inv_region_body<false, 2, false>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
+
+// OD_TDLT_CODING_ORDER: the coefficients arrive as block-linear coding-order vectors (in.p[]).
+#define TDLT_INV_CODING_KERNEL(name, pix) \
+  __global__ void __launch_bounds__(kRegThreads, TDLT_MINB) \
+  name(const __grid_constant__ TmapSet maps, const __grid_constant__ RegionBatch bd, \
+       const unsigned char *__restrict__ plan, PlanePtrs out, int2 *__restrict__ strips, \
+       int *__restrict__ ticket, int epoch, const unsigned short *__restrict__ order, PlanePtrs in) { \
+    tdlt_inv_region_body<false, pix, true>(maps, bd, plan, out, strips, ticket, epoch, order, in); \
+  }
+TDLT_INV_CODING_KERNEL(tdlt_inv_region_co_kernel, 0)
+TDLT_INV_CODING_KERNEL(tdlt_inv_region_co_pix8_kernel, 1)
+TDLT_INV_CODING_KERNEL(tdlt_inv_region_co_pix16_kernel, 2)
 
 // Lossless mode (OD_TDLT_HAAR): the Haar wavelet of every superblock instead of lapping + DCTs.
 __global__ void __launch_bounds__(kRegThreads, TDLT_MINB)
@@ -375,7 +387,7 @@ tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                        const unsigned char *__restrict__ plan, PlanePtrs out,
                        int2 *__restrict__ strips, int *__restrict__ ticket, int epoch,
                        const unsigned short *__restrict__ order, PlanePtrs in) {
-  tdlt_inv_region_body<true, 0>(maps, bd, plan, out, strips, ticket, epoch, order, in);
+  tdlt_inv_region_body<true, 0, false>(maps, bd, plan, out, strips, ticket, epoch, order, in);
 }
 
 

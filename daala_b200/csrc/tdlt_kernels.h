@@ -51,6 +51,14 @@ __global__ void tdlt_inv_region_pix16_kernel(const __grid_constant__ TmapSet map
                                              PlanePtrs out, int2 *__restrict__ strips,
                                              int *__restrict__ ticket, int epoch,
                                              const unsigned short *__restrict__ order, PlanePtrs in);
+#define TDLT_DECL_INV_CO(name) \
+  __global__ void name(const __grid_constant__ TmapSet maps, const __grid_constant__ RegionBatch bd, \
+                       const unsigned char *__restrict__ plan, PlanePtrs out, int2 *__restrict__ strips, \
+                       int *__restrict__ ticket, int epoch, const unsigned short *__restrict__ order, \
+                       PlanePtrs in)
+TDLT_DECL_INV_CO(tdlt_inv_region_co_kernel);
+TDLT_DECL_INV_CO(tdlt_inv_region_co_pix8_kernel);
+TDLT_DECL_INV_CO(tdlt_inv_region_co_pix16_kernel);
 __global__ void tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
                                      const __grid_constant__ RegionBatch bd,
                                      const unsigned char *__restrict__ plan,
