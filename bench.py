@@ -242,7 +242,9 @@ def main():
     ap.add_argument("--frames", type=int, default=0, help="frames per GPU (0 = workload default)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-threads", type=int, default=2)
+    ap.add_argument("--e2e-threads", type=int, default=0,
+                    help="host threads of the e2e figure, one context and one batch each "
+                         "(0 = 4 on one GPU, 2 per rank under torchrun)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary lines (fused pixel kernels, 16-bit / pageable e2e, neighbours)")
@@ -506,11 +508,14 @@ def main():
     if not args.no_e2e:
         import ctypes as C
         link = link_ceiling()
-        # Two host threads, one context each (contexts are
-        # independent), each running whole steps on its own batch, started half a step
-        # apart: the forward call is download-heavy (pixels up, od_coeff down), the inverse
-        # call upload-heavy, so the two directions of the link are busy at the same time.
-        nthr = max(1, args.e2e_threads)
+        # Several host threads, one context each (contexts are
+        # independent), each running whole steps on its own batch, started a fraction of a
+        # step apart: the forward call is download-heavy (pixels up, od_coeff down), the
+        # inverse call upload-heavy, so the two directions of the link are busy at the same
+        # time.  Measured on one GPU (profiles/e2e_threads_r2l.txt): 2 / 3 / 4 threads reach
+        # 0.79 / 0.83 / 0.85 of the link; under torchrun the ranks already share the host's
+        # link, two per rank reach 0.96 at N = 2.
+        nthr = args.e2e_threads if args.e2e_threads > 0 else (4 if world == 1 else 2)
         L = ctx.L
         arr = daala_b200._ptr_array
         ctxs = [ctx] + [daala_b200.TdltContext(pic_w, pic_h, device=local_rank, max_frames=nframes)
@@ -563,7 +568,7 @@ def main():
                 for k in range(nsteps):
                     e2e_fwd(i)
                     if k == 0:
-                        started.set()          # the next thread starts half a step later
+                        started.set()          # the next thread starts now: half a step behind this one
                     e2e_inv(i)
 
             def run_steps(nsteps):
@@ -604,8 +609,8 @@ def main():
         e2e = e2e_variant(1, 1, "pinned")
         e2e["api"] = ("od_tdlt_fwd_frames_pix (8-bit pixels -> od_coeff) + od_tdlt_inv_frames_pix "
                       "(od_coeff -> 8-bit pixels), pixel conversion fused into the transform kernels, "
-                      "synchronous calls; %d host thread(s), one context and one batch each, started "
-                      "half a step apart" % nthr)
+                      "synchronous calls; %d host thread(s), one context and one batch each, each "
+                      "started when the one before it has finished its first forward call" % nthr)
         e2e["link"] = link
         e2e["link_frac_means"] = ("bytes moved both ways per second / what plain cudaMemcpyAsync moves "
                                   "both ways at once on this box (link.both_GBps)")

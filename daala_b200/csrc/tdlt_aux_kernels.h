@@ -1,8 +1,14 @@
 // Launchers of the auxiliary kernels (internal to the library).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 namespace tdlt {
+
+// x / d for x < 2^16 by multiply-high with recip = ceil(2^32 / d) (tdlt_capi.cu recip32; 0 = d is 1).
+__device__ __forceinline__ int div_recip(int x, unsigned recip) {
+  return recip ? (int)__umulhi((unsigned)x, recip) : x;
+}
 
 void launch_pix_to_coeff(int *c, const void *pix, long long nsamples, int xstride, int shift,
                          cudaStream_t st);
@@ -41,8 +47,18 @@ struct DeringParams {
   int dec[4];
   int thr[4];                      // (int)pow(q, 0.84182) per plane, computed on the host
   int nplanes, nhsb, nvsb, skip_stride;
+  unsigned recip_nhsb;             // ceil(2^32 / nhsb): row of a superblock by multiply-high
+  unsigned recip_npair;            // the same for (nhsb + 1) / 2 (pairs of superblocks)
 };
-void launch_dering(const DeringParams &P, int nframes, cudaStream_t st);
+// One 3-D map (x, y, frame) per input plane; box = the superblock's tile with its ring:
+// (32 >> dec) + 8 words by (32 >> dec) + 6 rows.
+struct DeringMaps {
+  CUtensorMap in[4];
+  CUtensorMap dir;                 // luma, box 64 x 32: a pair of superblocks without ring
+};
+// dirthr: 16 ints per superblock and frame (direction | threshold << 3 of every luma 8x8 block)
+void launch_dering(const DeringMaps &maps, const DeringParams &P, int *dirthr, int nframes,
+                   cudaStream_t st);
 
 // Keyframe bilinear smoothing of the superblocks coded as one 32x32 block, in place.
 struct SmoothParams {
@@ -66,6 +82,7 @@ struct CodingParams {
   int dec[4];
   int nplanes, nhsb, nvsb, to_coding;
   unsigned recip_nhsb;             // ceil(2^32 / nhsb): row of a superblock by multiply-high
+  unsigned recip_npair;            // the same for (nhsb + 1) / 2 (pairs of superblocks)
 };
 void launch_coding_order(const CodingParams &P, int nframes, cudaStream_t st);
 // tab: 4*1024 + 3*256 positions (tdlt_region.cuh: kCoTabEntries), see cotab_build_kernel

@@ -24,7 +24,10 @@ constexpr int kMaxChunks = 64;   // pipeline depth of one host-pointer call
 
 // Region orders of the inverse kernel: rows of regions in flight per frame, by batch size.
 constexpr int kOrderTables = 3;
-constexpr int kOrderBands[kOrderTables] = {3, 8, 24};
+#ifndef TDLT_BANDS0
+#define TDLT_BANDS0 3      // (a build flag for tools/ablate.py experiments)
+#endif
+constexpr int kOrderBands[kOrderTables] = {TDLT_BANDS0, 8, 24};
 
 struct od_tdlt_ctx {
   od_tdlt_geometry g;
@@ -52,6 +55,8 @@ struct od_tdlt_ctx {
   unsigned char *dev_aux;       // od_tdlt_dering_frames: superblock flags + skip maps
   unsigned char *dev_scan;      // the caller's scan tables (od_tdlt_set_scan_tables)
   unsigned short *dev_cotab;    // source positions for the fused coding-order store / load
+  int *dering_dirs;             // deringing: 16 ints per superblock and frame (search -> filter kernel)
+  long long dering_sbs;         // ... capacity in superblocks
   int scan_len[4];
   size_t dev_aux_bytes;
   cudaStream_t stream;          // kernels
@@ -119,6 +124,10 @@ static bool ranges_overlap(const void *a, size_t na, const void *b, size_t nb) {
   const uintptr_t x = (uintptr_t)a, y = (uintptr_t)b;
   return x < y + nb && y < x + na;
 }
+
+// ceil(2^32 / d) for the kernels' divisions by multiply-high (tdlt_aux_kernels.h div_recip);
+// 0 stands for d = 1, whose reciprocal does not fit.
+static unsigned recip32(int d) { return d <= 1 ? 0u : (unsigned)(((1ull << 32) + d - 1)/d); }
 
 // 3-D map (x, y, frame) over nframes planes of w x h int32; box bx x by x 1.
 static int make_tmap(od_tdlt_ctx *ctx, CUtensorMap *m, const void *base, int w, int h,
@@ -330,6 +339,7 @@ void od_tdlt_ctx_destroy(od_tdlt_ctx *ctx) {
   cudaFree(ctx->strips);
   cudaFree(ctx->ticket);
   cudaFree(ctx->order);
+  cudaFree(ctx->dering_dirs);
   cudaFree(ctx->plan);
   for (int k = 0; k < kMaxChunks; k++) {
     if (ctx->ev_in[k]) cudaEventDestroy(ctx->ev_in[k]);
@@ -722,9 +732,32 @@ int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff
   P.nvsb = ctx->nvsb;
   P.skip_stride = ctx->nhsb*8;
   P.skip_frame = (long long)ctx->nhsb*8*ctx->nvsb*8;
+  P.recip_nhsb = recip32(ctx->nhsb);
+  if (nframes > 65535) return fail(ctx, OD_TDLT_EINVAL, "nframes %d (at most 65535 per call)", nframes);
+  // the superblock tiles arrive as TMA boxes: (32 >> dec) + 8 words by (32 >> dec) + 6 rows
+  DeringMaps maps;
+  for (int p = 0; p < P.nplanes; p++) {
+    if ((uintptr_t)in[p] & 15) return fail(ctx, OD_TDLT_EINVAL, "plane %d is not 16-byte aligned", p);
+    const int dec = P.dec[p], n = 32 >> dec;
+    if (int rc = make_tmap(ctx, &maps.in[p], in[p], ctx->fw >> dec, ctx->fh >> dec, nframes, n + 8, n + 6)) return rc;
+  }
+  if (int rc = make_tmap(ctx, &maps.dir, in[0], ctx->fw, ctx->fh, nframes, 64, 32)) return rc;
+  const int npair = (ctx->nhsb + 1)/2;
+  P.recip_npair = recip32(npair);
   DeviceGuard dev_guard(ctx->device);
   if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
-  launch_dering(P, nframes, (cudaStream_t)stream);
+  // directions and thresholds of the luma blocks, between the search and the filter kernel
+  const long long nsb = (long long)ctx->nhsb*ctx->nvsb*nframes;
+  if (nsb > ctx->dering_sbs) {
+    CK(ctx, cudaDeviceSynchronize());
+    cudaFree(ctx->dering_dirs);
+    ctx->dering_dirs = nullptr;
+    ctx->dering_sbs = 0;
+    CK(ctx, cudaMalloc(&ctx->dering_dirs, (size_t)nsb*16*sizeof(int)));
+    ctx->dering_sbs = nsb;
+  }
+  launch_dering(maps, P, ctx->dering_dirs, nframes, (cudaStream_t)stream);
+  g_launches++;
   g_launches++;
   CK(ctx, cudaGetLastError());
   return OD_TDLT_SUCCESS;
@@ -826,7 +859,7 @@ int od_tdlt_coding_order_batch(od_tdlt_ctx *ctx, od_coeff *const v[], od_coeff *
   P.nvsb = ctx->nvsb;
   P.to_coding = to_coding != 0;
   if ((long long)ctx->nhsb*ctx->nvsb >= 65536) return fail(ctx, OD_TDLT_EINVAL, "frame too large for the coding-order walk");
-  P.recip_nhsb = (unsigned)(((1ull << 32) + ctx->nhsb - 1)/ctx->nhsb);
+  P.recip_nhsb = recip32(ctx->nhsb);
   DeviceGuard dev_guard(ctx->device);
   if (!dev_guard.ok) return fail(ctx, OD_TDLT_EFAULT, "cudaSetDevice(%d) failed", ctx->device);
   launch_coding_order(P, nframes, (cudaStream_t)stream);

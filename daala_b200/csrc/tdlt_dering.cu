@@ -5,7 +5,9 @@
 // copy), so superblocks are independent: one CTA per superblock and frame, all planes.
 //
 //   per plane (luma first; chroma reuses luma's directions):
-//     load the (n+6)^2 tile -> A (int16 semantics; samples outside the frame = 30000)
+//     the (n+6) x (n+8) tile arrives as ONE TMA box -> A (the next plane's box is asked
+//       for before this plane is worked on); samples outside the frame = 30000; the
+//       reference's int16 etmp copy is the low half of every word, read as such
 //     luma: direction search of the 16 8x8 blocks (thread = block x direction), variances,
 //           per-block thresholds; all planes: skip test of every block
 //     pass 1: 6 taps along the block's direction          A -> B (interior)
@@ -14,7 +16,9 @@
 //
 // HBM-bound by design: 4 bytes read + 4 written per sample; the 3-sample ring around a
 // superblock is re-read from L2 (neighbouring CTAs are resident at the same time).
+#include <cuda.h>
 #include <cuda_runtime.h>
+#include "tdlt_device.cuh"
 #include "tdlt_aux_kernels.h"
 
 namespace tdlt {
@@ -23,12 +27,25 @@ namespace {
 
 constexpr int kSB = 32;               // luma superblock (reference OD_BSIZE_MAX)
 constexpr int kBorder = 3;            // reference OD_FILT_BORDER
-constexpr int kPadL = 4;              // left pad of the tile: interior 16-byte aligned
-constexpr int kPitch = 40;            // words per tile row
-constexpr int kRows = kSB + 2*kBorder;
-constexpr int kTile = kRows*kPitch;
+constexpr int kPadL = 4;              // left / right pad of the tile: interior 16-byte aligned
 constexpr int kFar = 30000;           // reference OD_DERING_VERY_LARGE
 constexpr int kThreads = 128;
+
+// The tile of a plane of one superblock, ring included: n + 6 rows of n + 8 words, dense (it
+// is a TMA box).  With row pitches of 40 / 24 words the 4 x 8 pixels of a warp access (8x8
+// block) and the 2 x (4 x 4) of a chroma warp access fall into 32 different banks.
+template <int DEC> struct Tile {
+  static constexpr int n = kSB >> DEC;
+  static constexpr int pitch = n + 2*kPadL;
+  static constexpr int rows = n + 2*kBorder;
+  static constexpr int words = rows*pitch;
+  static constexpr int origin = kBorder*pitch + kPadL;      // the superblock's first sample
+};
+constexpr int kTileWords = 1536;      // Tile<0>::words = 1520, rounded up to whole 128-byte lines
+static_assert(Tile<0>::words <= kTileWords, "tile buffer");
+
+// The reference filters its int16_t copy of the frame: the low half of the od_coeff word.
+__device__ __forceinline__ int ld16(const int *p) { return *reinterpret_cast<const short *>(p); }
 
 // Line of direction D that pixel (i, j) of an 8x8 block lies on (reference
 // src/filter.c:1666-1673).
@@ -45,22 +62,11 @@ template <int D> struct DirLines {   // pixels on each line, counted at compile 
   }
 };
 
-// Cost of direction D for the 8x8 block at blk (pixels already shifted down to pixel scale,
-// the reference's x >> OD_COEFF_SHIFT; reference src/filter.c:1655-1697): the sum
-// over the direction's lines of (line sum)^2 / (pixels on the line).  Fully unrolled: the
-// line sums live in registers.
-template <int D> __device__ __forceinline__ int dir_cost(const int *blk) {
-  int s[15];
-#pragma unroll
-  for (int k = 0; k < 15; k++) s[k] = 0;
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    int4 a = *reinterpret_cast<const int4 *>(blk + i*kPitch);
-    int4 b = *reinterpret_cast<const int4 *>(blk + i*kPitch + 4);
-    int v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-#pragma unroll
-    for (int j = 0; j < 8; j++) s[dir_line<D>(i, j)] += v[j];
-  }
+// Costs of the directions D0 and D1 for the 8x8 block at blk (pixels already shifted down to
+// pixel scale, the reference's x >> OD_COEFF_SHIFT; reference src/filter.c:1655-1697): the
+// sum over the direction's lines of (line sum)^2 / (pixels on the line).  Fully unrolled: the
+// line sums of both directions live in registers, every row is loaded once for the two.
+template <int D> __device__ __forceinline__ int lines_cost(const int *s) {
   constexpr DirLines<D> lines{};
   int cost = 0;
 #pragma unroll
@@ -71,18 +77,30 @@ template <int D> __device__ __forceinline__ int dir_cost(const int *blk) {
   }
   return cost;
 }
+template <int D0, int D1, int kPitch>
+__device__ __forceinline__ void dir_cost2(const int *blk, int &c0, int &c1) {
+  int s0[15], s1[15];
+#pragma unroll
+  for (int k = 0; k < 15; k++) s0[k] = s1[k] = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    int4 a = *reinterpret_cast<const int4 *>(blk + i*kPitch);
+    int4 b = *reinterpret_cast<const int4 *>(blk + i*kPitch + 4);
+    int v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      s0[dir_line<D0>(i, j)] += v[j];
+      s1[dir_line<D1>(i, j)] += v[j];
+    }
+  }
+  c0 = lines_cost<D0>(s0);
+  c1 = lines_cost<D1>(s1);
+}
 
 __constant__ int kThreshQ8[18] = {  // reference src/filter.c:1803-1807 (formula in its comment)
     128, 134, 150, 168, 188, 210, 234, 262, 292, 327, 365, 408, 455, 509, 569, 635, 710, 768};
-// (dy, dx) of the three taps of each direction as tile offsets (reference
-// direction_offsets_table, src/filter.c:142-151)
-__constant__ int kDirOff[8][3] = {
-    {-1*kPitch + 1, -2*kPitch + 2, -3*kPitch + 3}, {1, -1*kPitch + 2, -1*kPitch + 3},
-    {1, 2, 3}, {1, 1*kPitch + 2, 1*kPitch + 3},
-    {1*kPitch + 1, 2*kPitch + 2, 3*kPitch + 3}, {1*kPitch, 2*kPitch + 1, 3*kPitch + 1},
-    {1*kPitch, 2*kPitch, 3*kPitch}, {1*kPitch, 2*kPitch - 1, 3*kPitch - 1}};
-
-// the same taps as (dy, dx) steps, for the block calls whose buffers have another pitch
+// (dy, dx) of the three taps of each direction (reference direction_offsets_table,
+// src/filter.c:142-151)
 __constant__ signed char kDirStep[8][3][2] = {
     {{-1, 1}, {-2, 2}, {-3, 3}}, {{0, 1}, {-1, 2}, {-1, 3}}, {{0, 1}, {0, 2}, {0, 3}},
     {{0, 1}, {1, 2}, {1, 3}},    {{1, 1}, {2, 2}, {3, 3}},   {{1, 0}, {2, 1}, {3, 1}},
@@ -98,71 +116,82 @@ __device__ __forceinline__ Gate gate(int thr) {
   return g;
 }
 __device__ __forceinline__ int tap(int p, Gate g) { return (unsigned)(p + g.c) < g.lim ? p : 0; }
+// The same shifted by c, so that the subtraction of the centre pixel folds into one constant
+// per pixel: q = the neighbour, cx = c - centre; returns tap(q - centre) + c (a rejected tap
+// counts as c; the caller takes the c's off the weighted sum in one go).
+__device__ __forceinline__ int tapc(int q, int cx, Gate g) {
+  const int t = q + cx;
+  return (unsigned)t < g.lim ? t : g.c;
+}
 
 }  // namespace
 
 // Tile offset of tap K of direction DIR (the table above, as a compile-time value).
-template <int DIR, int K> struct DirOff {
+template <int DIR, int K, int PITCH> struct DirOff {
   static constexpr int dy = DIR == 0 ? -(K + 1) : DIR == 1 ? (K == 0 ? 0 : -1) : DIR == 2 ? 0 :
                             DIR == 3 ? (K == 0 ? 0 : 1) : K + 1;
   static constexpr int dx = DIR <= 3 ? K + 1 : DIR == 4 ? K + 1 : DIR == 5 ? (K == 0 ? 0 : 1) :
                             DIR == 6 ? 0 : (K == 0 ? 0 : -1);
-  static constexpr int value = dy*kPitch + dx;
+  static constexpr int value = dy*PITCH + dx;
 };
 
-// Pass 1 of one 8x8 luma block by one warp: this lane's two pixels (a, a + 4 rows).
+// Pass 1 of one 8x8 block by one warp: this lane's two pixels (a, a + 4 rows).
 template <int DIR>
 __device__ __forceinline__ void pass1_block(const int *a, int *b, int thr) {
-  constexpr int o0 = DirOff<DIR, 0>::value, o1 = DirOff<DIR, 1>::value, o2 = DirOff<DIR, 2>::value;
+  constexpr int kPitch = Tile<0>::pitch;
+  constexpr int o0 = DirOff<DIR, 0, kPitch>::value, o1 = DirOff<DIR, 1, kPitch>::value,
+                o2 = DirOff<DIR, 2, kPitch>::value;
   const Gate g = gate(thr);
+  const int k1 = 8 - 14*g.c;            // rounding offset less the c's of the 3*2 + 2*4 tap weights
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     const int *q = a + h*4*kPitch;
-    const int xx = q[0];
-    int s0 = tap(q[o0] - xx, g) + tap(q[-o0] - xx, g);
-    int s1 = tap(q[o1] - xx, g) + tap(q[-o1] - xx, g) + tap(q[o2] - xx, g) + tap(q[-o2] - xx, g);
-    b[h*4*kPitch] = (short)(xx + ((3*s0 + 2*s1 + 8) >> 4));
+    const int xx = ld16(q);
+    const int cx = g.c - xx;
+    const int s0 = tapc(ld16(q + o0), cx, g) + tapc(ld16(q - o0), cx, g);
+    const int s1 = tapc(ld16(q + o1), cx, g) + tapc(ld16(q - o1), cx, g) +
+                   tapc(ld16(q + o2), cx, g) + tapc(ld16(q - o2), cx, g);
+    b[h*4*kPitch] = (short)(xx + ((3*s0 + 2*s1 + k1) >> 4));
   }
 }
 
-// Pass 2 of one 8x8 luma block by one warp; O = tile offset across the direction.
+// Pass 2 of one 8x8 block by one warp; O = tile offset across the direction.
 template <int O>
 __device__ __forceinline__ void pass2_block(const int *a, const int *b, int *g, int w, int thr) {
+  constexpr int kPitch = Tile<0>::pitch;
   const int third = thr/3;
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     const int *bq = b + h*4*kPitch;
-    const int yy = bq[0];
-    const Gate ga = gate(min(thr, third + abs(yy - a[h*4*kPitch])));
-    int sum = tap(bq[O] - yy, ga) + tap(bq[-O] - yy, ga) + tap(bq[2*O] - yy, ga) +
-              tap(bq[-2*O] - yy, ga);
-    g[h*4*(long long)w] = (short)(yy + ((3*sum + 8) >> 4));
+    const int yy = ld16(bq);
+    const Gate ga = gate(min(thr, third + abs(yy - ld16(a + h*4*kPitch))));
+    const int cy = ga.c - yy;
+    const int sum = tapc(ld16(bq + O), cy, ga) + tapc(ld16(bq - O), cy, ga) +
+                    tapc(ld16(bq + 2*O), cy, ga) + tapc(ld16(bq - 2*O), cy, ga);
+    g[h*4*(long long)w] = (short)(yy + ((3*sum + 8 - 12*ga.c) >> 4));
   }
 }
 
 // One plane of one filtered superblock.  DEC is the plane's decimation: n = 32 >> DEC
-// samples a side, filter blocks of 8 >> DEC.
+// samples a side, filter blocks of 8 >> DEC.  The plane's tile is on its way into A (bar,
+// parity); B is free.  s_dir[], s_lthr[]: directions and thresholds of the 16 luma blocks.
 template <int DEC>
 __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int frame, int sbx,
-                                             int sby, int *A, int *B, int (*s_cost)[8],
-                                             int *s_dir, int *s_thr, int *s_coded) {
-  constexpr int n = kSB >> DEC;
-  constexpr int span = n + 2*kBorder;
-  constexpr int lb = 3 - DEC;
+                                             int sby, int *A, int *B, void *bar, int parity,
+                                             const int *s_dir, const int *s_lthr) {
+  using T = Tile<DEC>;
+  constexpr int n = T::n, kPitch = T::pitch;
   const int t = threadIdx.x;
   const int w = (P.nhsb*kSB) >> DEC;
-  const int *src = P.in[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
   int *dst = P.out[p] + frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
-  int *Ai = A + kBorder*kPitch + kPadL;                 // interior origin
-  int *Bi = B + kBorder*kPitch + kPadL;
-  // ---- load the tile, ring included, as 16-byte vectors: rows -3 .. n+2, columns -4 .. n+3
-  // (the superblock starts on a 16-byte boundary).  What lies outside the frame does so in
-  // whole vectors and rows and becomes "far away" (reference OD_DERING_VERY_LARGE).
-  __syncthreads();                                      // previous plane done with A, B
+  int *Ai = A + T::origin;                              // interior origin
+  int *Bi = B + T::origin;
   // Skip test first, so that its loads are in flight under the tile's: a block whose own
   // 4x4 units and the ring of units around them (lapping reaches there) are all skipped is
   // left alone (reference src/filter.c:1899-1920; the ring is cut at the frame border only).
-  // Eight lanes per block, two flags of the 4x4 window each.
+  // Eight lanes per block, two flags of the 4x4 window each.  Warp w tests the blocks 4w ..
+  // 4w + 3, the blocks it filters below: byte k of its ballot = block 4w + k.
+  unsigned coded_mask;
   {
     constexpr int u = 2 >> DEC;
     const int b = t >> 3;
@@ -178,94 +207,57 @@ __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int f
       const int wj = (t & 1)*2 + e - 1;
       if (wi >= lo_i && wi < hi_i && wj >= lo_j && wj < hi_j) coded |= !__ldg(sk + wi*P.skip_stride + wj);
     }
-    const unsigned m = __ballot_sync(0xffffffffu, coded);
-    if ((t & 7) == 0) s_coded[b] = (m >> (t & 24)) & 0xffu;
+    coded_mask = __ballot_sync(0xffffffffu, coded);
   }
+  mbar_wait(bar, parity);
+  // What lies outside the frame arrives as zeros and becomes "far away" (reference
+  // OD_DERING_VERY_LARGE): whole rows and 4-word column groups of border superblocks only.
   {
-    constexpr int vrow = n/4 + 2;                       // vectors per tile row
     const bool top = sby == 0, bottom = sby == P.nvsb - 1;
     const bool left = sbx == 0, right = sbx == P.nhsb - 1;
-    for (int i = t; i < span*vrow; i += kThreads) {
-      const int r = i/vrow, c = i - r*vrow;
-      const int rr = r - kBorder;
-      const bool ring = rr < 0 || rr >= n || c == 0 || c == vrow - 1;
-      const bool outside = (top && rr < 0) || (bottom && rr >= n) || (left && c == 0) ||
-                           (right && c == vrow - 1);
-      int4 v = make_int4(kFar, kFar, kFar, kFar);
-      if (!outside) {
-        v = __ldg(reinterpret_cast<const int4 *>(src + (long long)rr*w - 4) + c);
-        v.x = (short)v.x; v.y = (short)v.y; v.z = (short)v.z; v.w = (short)v.w;  // the int16_t etmp copy
+    if (top || bottom || left || right) {               // uniform over the CTA
+      for (int i = t; i < T::words; i += kThreads) {
+        const int r = i/kPitch, c = i - r*kPitch;
+        const bool outside = (top && r < kBorder) || (bottom && r >= n + kBorder) ||
+                             (left && c < kPadL) || (right && c >= n + kPadL);
+        if (outside) A[i] = kFar;
       }
-      *reinterpret_cast<int4 *>(A + r*kPitch + 4*c) = v;
-      if (p == 0 && !ring) {  // luma: pixel-scale copy for the direction search (B's interior is free until pass 1)
-        v.x >>= 4; v.y >>= 4; v.z >>= 4; v.w >>= 4;
-      }
-      if (p == 0 || ring) *reinterpret_cast<int4 *>(B + r*kPitch + 4*c) = v;
+      __syncthreads();
     }
+  }
+  // B's ring (pass 2 reaches two samples out of the superblock, straight up / down / left /
+  // right) = the unfiltered samples
+  if (t < n) {                                          // rows -2, -1, n, n + 1
+    const int rs = t/(n/4), cq = t - rs*(n/4);
+    const int rr = rs < 2 ? rs - 2 : n + rs - 2;
+    const int o = (rr + kBorder)*kPitch + kPadL + 4*cq;
+    *reinterpret_cast<int4 *>(B + o) = *reinterpret_cast<const int4 *>(A + o);
+  }
+  else if (t < 3*n) {                                   // columns -2, -1 and n, n + 1
+    const int k = t - n, rr = k >> 1;
+    const int o = (rr + kBorder)*kPitch + ((k & 1) ? n + kPadL : kPadL - 2);
+    *reinterpret_cast<int2 *>(B + o) = *reinterpret_cast<const int2 *>(A + o);
   }
   __syncthreads();
-  // ---- luma: direction search -------------------------------------------------------------
-  if (DEC == 0 && p == 0) {
-    const int blk = t & 15, d = t >> 4;
-    const int *bp = Bi + (blk >> 2)*8*kPitch + (blk & 3)*8;
-    int c;
-    switch (d) {
-      case 0: c = dir_cost<0>(bp); break;
-      case 1: c = dir_cost<1>(bp); break;
-      case 2: c = dir_cost<2>(bp); break;
-      case 3: c = dir_cost<3>(bp); break;
-      case 4: c = dir_cost<4>(bp); break;
-      case 5: c = dir_cost<5>(bp); break;
-      case 6: c = dir_cost<6>(bp); break;
-      default: c = dir_cost<7>(bp); break;
-    }
-    s_cost[blk][d] = c;
-    __syncthreads();
-    if (t < 32) {
-      int var = 0;
-      if (t < 16) {
-        int best = 0, best_cost = 0;
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          int ck = s_cost[t][k];
-          if (ck > best_cost) { best_cost = ck; best = k; }
-        }
-        var = best_cost - s_cost[t][(best + 4) & 7];
-        s_dir[t] = best;
-      }
-      int varsum = var;
-#pragma unroll
-      for (int o = 8; o >= 1; o >>= 1) varsum += __shfl_xor_sync(0xffffffffu, varsum, o);
-      if (t < 16) {
-        // reference od_compute_thresh, src/filter.c:1816-1833
-        int v1 = min(32767, var >> 6);
-        int v2 = min(32767, varsum/(kSB*kSB));
-        unsigned prod = (unsigned)(v1*v2);
-        int e = (32 - __clz(prod)) - 9;
-        e = max(0, min(17, e));
-        s_thr[t] = (P.thr[0]*kThreshQ8[e]) >> 8;
-      }
-    }
-  }
-  else if (t < 16) {
-    s_thr[t] = P.thr[p];
-  }
-  if (t < 16 && !s_coded[t]) s_thr[t] = 0;            // all skipped: pass through
-  __syncthreads();
+  // thresholds: luma's come from the direction search (dering_dir_kernel, s_lthr[]), chroma's
+  // are flat (reference src/filter.c:1877-1897); a block that is all skipped passes through
+  const int flat_thr = P.thr[p];
+  auto blk_thr = [&](int b) {
+    return ((coded_mask >> (8*(b & 3))) & 0xffu) ? (p == 0 ? s_lthr[b] : flat_thr) : 0;
+  };
   // ---- the two passes.  A block with threshold 0 passes through both unchanged.
-  // Luma: one warp per 8x8 block at a time (two pixels per lane, four rows apart), so the
+  // 8x8 blocks: one warp per block at a time (two pixels per lane, four rows apart), so the
   // block's direction and threshold are warp-uniform and the tap offsets compile-time
-  // constants; with a row pitch of 40 words the 4 x 8 pixels of a warp access fall into 32
-  // different banks.  Chroma (4x4 blocks): half a warp per block, offsets from the table.
+  // constants.  Chroma of 4:2:0 (4x4 blocks): half a warp per block, offsets from the table.
   const int warp = t >> 5, lane = t & 31;
   if (DEC == 0) {
     for (int k = 0; k < 4; k++) {
       const int b = warp*4 + k;
-      const int thr = s_thr[b];
+      const int thr = blk_thr(b);
       const int off = ((b >> 2)*8 + (lane >> 3))*kPitch + (b & 3)*8 + (lane & 7);
       if (thr == 0) {
-        Bi[off] = Ai[off];
-        Bi[off + 4*kPitch] = Ai[off + 4*kPitch];
+        Bi[off] = ld16(Ai + off);
+        Bi[off + 4*kPitch] = ld16(Ai + off + 4*kPitch);
         continue;
       }
       switch (s_dir[b]) {
@@ -280,12 +272,13 @@ __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int f
       }
     }
     __syncthreads();
+    // (a warp's four blocks lie side by side: block row `warp`)
+    int *grow = dst + (long long)(warp*8 + (lane >> 3))*w + (lane & 7);
     for (int k = 0; k < 4; k++) {
       const int b = warp*4 + k;
-      const int thr = s_thr[b];
-      const int r = (b >> 2)*8 + (lane >> 3), c = (b & 3)*8 + (lane & 7);
-      const int off = r*kPitch + c;
-      int *g = dst + (long long)r*w + c;
+      const int thr = blk_thr(b);
+      const int off = (warp*8 + (lane >> 3))*kPitch + k*8 + (lane & 7);
+      int *g = grow + k*8;
       if (thr == 0) {
         g[0] = Bi[off];
         g[4*(long long)w] = Bi[off + 4*kPitch];
@@ -298,77 +291,193 @@ __device__ __forceinline__ void dering_plane(const DeringParams &P, int p, int f
     const int half = lane >> 4, l16 = lane & 15;
     for (int k = 0; k < 2; k++) {
       const int b = (warp*2 + k)*2 + half;              // two horizontally adjacent blocks per warp
-      const int thr = s_thr[b];
+      const int thr = blk_thr(b);
       const int off = ((b >> 2)*4 + (l16 >> 2))*kPitch + (b & 3)*4 + (l16 & 3);
-      const int xx = Ai[off];
+      const int xx = ld16(Ai + off);
       int yy = xx;
       if (thr) {
         const int *a = Ai + off;
         const int dir = s_dir[b];
-        const int o0 = kDirOff[dir][0], o1 = kDirOff[dir][1], o2 = kDirOff[dir][2];
+        const int o0 = kDirStep[dir][0][0]*kPitch + kDirStep[dir][0][1];
+        const int o1 = kDirStep[dir][1][0]*kPitch + kDirStep[dir][1][1];
+        const int o2 = kDirStep[dir][2][0]*kPitch + kDirStep[dir][2][1];
         const Gate g = gate(thr);
-        int s0 = tap(a[o0] - xx, g) + tap(a[-o0] - xx, g);
-        int s1 = tap(a[o1] - xx, g) + tap(a[-o1] - xx, g) + tap(a[o2] - xx, g) + tap(a[-o2] - xx, g);
-        yy = (short)(xx + ((3*s0 + 2*s1 + 8) >> 4));
+        const int cx = g.c - xx;
+        const int s0 = tapc(ld16(a + o0), cx, g) + tapc(ld16(a - o0), cx, g);
+        const int s1 = tapc(ld16(a + o1), cx, g) + tapc(ld16(a - o1), cx, g) +
+                       tapc(ld16(a + o2), cx, g) + tapc(ld16(a - o2), cx, g);
+        yy = (short)(xx + ((3*s0 + 2*s1 + 8 - 14*g.c) >> 4));
       }
       Bi[off] = yy;
     }
     __syncthreads();
     for (int k = 0; k < 2; k++) {
       const int b = (warp*2 + k)*2 + half;
-      const int thr = s_thr[b];
+      const int thr = blk_thr(b);
       const int r = (b >> 2)*4 + (l16 >> 2), c = (b & 3)*4 + (l16 & 3);
       const int *bq = Bi + r*kPitch + c;
-      const int yy = bq[0];
+      const int yy = ld16(bq);
       int out = yy;
       if (thr) {
         const int o = s_dir[b] <= 4 ? kPitch : 1;
-        const Gate ga = gate(min(thr, thr/3 + abs(yy - Ai[r*kPitch + c])));
-        int sum = tap(bq[o] - yy, ga) + tap(bq[-o] - yy, ga) + tap(bq[2*o] - yy, ga) +
-                  tap(bq[-2*o] - yy, ga);
-        out = (short)(yy + ((3*sum + 8) >> 4));
+        const Gate ga = gate(min(thr, thr/3 + abs(yy - ld16(Ai + r*kPitch + c))));
+        const int cy = ga.c - yy;
+        const int sum = tapc(ld16(bq + o), cy, ga) + tapc(ld16(bq - o), cy, ga) +
+                        tapc(ld16(bq + 2*o), cy, ga) + tapc(ld16(bq - 2*o), cy, ga);
+        out = (short)(yy + ((3*sum + 8 - 12*ga.c) >> 4));
       }
       dst[(long long)r*w + c] = out;
     }
   }
 }
 
-__global__ void __launch_bounds__(kThreads) dering_kernel(DeringParams P) {
-  __shared__ __align__(16) int A[kTile];
-  __shared__ __align__(16) int B[kTile];
-  __shared__ int s_cost[16][8];
+#ifndef TDLT_DERING_MINB
+#define TDLT_DERING_MINB 10
+#endif
+__global__ void __launch_bounds__(kThreads, TDLT_DERING_MINB)
+dering_kernel(const __grid_constant__ DeringMaps maps, const __grid_constant__ DeringParams P,
+              const int *__restrict__ dirthr) {
+  __shared__ __align__(128) int A[2][kTileWords];
+  __shared__ __align__(16) int B[kTileWords];
+  __shared__ __align__(8) unsigned long long bars[2];
   __shared__ int s_dir[16];
-  __shared__ int s_thr[16];
-  __shared__ int s_coded[16];
+  __shared__ int s_lthr[16];
   const int t = threadIdx.x;
-  // (a 3-D grid that spares these divisions measures 1.5 % slower)
-  const int per = P.nhsb*P.nvsb;
-  const int frame = blockIdx.x/per;
-  const int sb = blockIdx.x - frame*per;
-  const int sby = sb/P.nhsb, sbx = sb - sby*P.nhsb;
-  const bool filtered = P.flags[(long long)frame*per + sb] != 0;
-  for (int p = 0; p < P.nplanes; p++) {
-    const int dec = P.dec[p];
-    if (!filtered) {
+  // grid (superblocks of a frame, frames); the row of a superblock by multiply-high
+  const int sb = blockIdx.x, frame = blockIdx.y;
+  const int sby = div_recip(sb, P.recip_nhsb), sbx = sb - sby*P.nhsb;
+  const bool filtered = P.flags[(long long)frame*gridDim.x + sb] != 0;
+  if (!filtered) {
+    for (int p = 0; p < P.nplanes; p++) {
       // copy through: n rows of n words as 16-byte vectors
-      const int n = kSB >> dec;
-      const int w = (P.nhsb*kSB) >> dec;
+      const int n = kSB >> P.dec[p];
+      const int w = (P.nhsb*kSB) >> P.dec[p];
       const long long o = frame*P.plane_size[p] + (long long)(sby*n)*w + sbx*n;
-      const int vec_per_row = n >> 2;
-      for (int i = t; i < n*vec_per_row; i += kThreads) {
-        int r = i/vec_per_row, c = i - r*vec_per_row;
+      const int lv = 3 - P.dec[p];                      // log2 of the vectors per row
+      for (int i = t; i < n << lv; i += kThreads) {
+        const int r = i >> lv, c = i & ((1 << lv) - 1);
         reinterpret_cast<int4 *>(P.out[p] + o + (long long)r*w)[c] =
             __ldg(reinterpret_cast<const int4 *>(P.in[p] + o + (long long)r*w) + c);
       }
-      continue;
     }
-    if (dec == 0) dering_plane<0>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr, s_coded);
-    else dering_plane<1>(P, p, frame, sbx, sby, A, B, s_cost, s_dir, s_thr, s_coded);
+    return;
+  }
+  // One thread asks for the planes' tiles: plane 0 now, plane p + 1 when plane p - 1 is done
+  // with its buffer.  The box starts 3 rows above and 4 words left of the superblock (a
+  // 16-byte boundary); what it takes from outside the plane reads as zero.
+  auto fetch = [&](int p) {
+    const int dec = P.dec[p], n = kSB >> dec;
+    const int bytes = (dec ? Tile<1>::words : Tile<0>::words)*4;
+    mbar_expect_tx(&bars[p & 1], bytes);
+    tma_load_3d(A[p & 1], &maps.in[p], &bars[p & 1], sbx*n - kPadL, sby*n - kBorder, frame);
+  };
+  if (t == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+    fetch(0);
+  }
+  // the luma blocks' directions and thresholds (dering_dir_kernel): dir | thr << 3
+  if (t < 16) {
+    const int dt = __ldg(dirthr + ((long long)frame*gridDim.x + sb)*16 + t);
+    s_dir[t] = dt & 7;
+    s_lthr[t] = dt >> 3;
+  }
+  __syncthreads();
+  for (int p = 0; p < P.nplanes; p++) {
+    if (p > 0) {
+      // plane p - 1 is done with its A and with B; its border fill wrote A through the
+      // generic proxy, the next box arrives through the async one
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();
+    }
+    if (t == 0 && p + 1 < P.nplanes) fetch(p + 1);
+    const int parity = (p >> 1) & 1;
+    if (P.dec[p] == 0) dering_plane<0>(P, p, frame, sbx, sby, A[p & 1], B, &bars[p & 1], parity, s_dir, s_lthr);
+    else dering_plane<1>(P, p, frame, sbx, sby, A[p & 1], B, &bars[p & 1], parity, s_dir, s_lthr);
   }
 }
 
-void launch_dering(const DeringParams &P, int nframes, cudaStream_t st) {
-  dering_kernel<<<(unsigned)(P.nhsb*P.nvsb*nframes), kThreads, 0, st>>>(P);
+// Direction search of the luma 8x8 blocks (reference od_dir_find8 + od_compute_thresh,
+// src/filter.c:1655-1697, 1816-1833, called from od_dering :1865-1897): one CTA per PAIR of
+// horizontally adjacent superblocks, so that a warp runs one direction for 32 blocks at a
+// time (warp w: directions 2w and 2w + 1) with every lane busy.  Result per block: dir |
+// thr << 3 (threshold before the skip test) -> dirthr[(frame*nsb + sb)*16 + block].
+constexpr int kDirPitch = 2*kSB;
+__global__ void __launch_bounds__(kThreads)
+dering_dir_kernel(const __grid_constant__ DeringMaps maps, const __grid_constant__ DeringParams P,
+                  int *__restrict__ dirthr) {
+  __shared__ __align__(128) int T[kSB*kDirPitch];       // the pair's luma samples, then pixels
+  __shared__ __align__(8) unsigned long long bar;
+  __shared__ int s_cost[32][9];
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int npair = (P.nhsb + 1) >> 1;
+  const int sby = div_recip((int)blockIdx.x, P.recip_npair), px = (int)blockIdx.x - sby*npair;
+  const int frame = blockIdx.y;
+  const int sb0 = sby*P.nhsb + 2*px;
+  const bool two = 2*px + 1 < P.nhsb;
+  const unsigned char *fl = P.flags + (long long)frame*P.nhsb*P.nvsb + sb0;
+  if (!fl[0] && !(two && fl[1])) return;                // uniform
+  if (t == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(&bar, kSB*kDirPitch*4);
+    tma_load_3d(T, &maps.dir, &bar, 2*px*kSB, sby*kSB, frame);
+  }
+  __syncthreads();
+  mbar_wait(&bar, 0);
+  // pixel scale, in place: the reference searches (int16_t)x >> OD_COEFF_SHIFT
+#pragma unroll
+  for (int it = 0; it < kSB*kDirPitch/4/kThreads; it++) {
+    int4 *q = reinterpret_cast<int4 *>(T) + t + it*kThreads;
+    int4 v = *q;
+    v.x = (short)v.x >> 4; v.y = (short)v.y >> 4; v.z = (short)v.z >> 4; v.w = (short)v.w >> 4;
+    *q = v;
+  }
+  __syncthreads();
+  {
+    const int blk = lane & 15;
+    const int *bp = T + (blk >> 2)*8*kDirPitch + (lane >> 4)*kSB + (blk & 3)*8;
+    int c0, c1;
+    switch (warp) {                                     // uniform
+      case 0: dir_cost2<0, 1, kDirPitch>(bp, c0, c1); break;
+      case 1: dir_cost2<2, 3, kDirPitch>(bp, c0, c1); break;
+      case 2: dir_cost2<4, 5, kDirPitch>(bp, c0, c1); break;
+      default: dir_cost2<6, 7, kDirPitch>(bp, c0, c1); break;
+    }
+    s_cost[lane][2*warp] = c0;
+    s_cost[lane][2*warp + 1] = c1;
+  }
+  __syncthreads();
+  if (t < 32) {
+    int best = 0, best_cost = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int ck = s_cost[t][k];
+      if (ck > best_cost) { best_cost = ck; best = k; }
+    }
+    const int var = best_cost - s_cost[t][(best + 4) & 7];
+    int varsum = var;                                   // over the 16 blocks of the lane's superblock
+#pragma unroll
+    for (int o = 8; o >= 1; o >>= 1) varsum += __shfl_xor_sync(0xffffffffu, varsum, o);
+    // reference od_compute_thresh, src/filter.c:1816-1833
+    int v1 = min(32767, var >> 6);
+    int v2 = min(32767, varsum/(kSB*kSB));
+    unsigned prod = (unsigned)(v1*v2);
+    int e = (32 - __clz(prod)) - 9;
+    e = max(0, min(17, e));
+    const int thr = (P.thr[0]*kThreshQ8[e]) >> 8;
+    if (t < 16 || two) {
+      dirthr[((long long)frame*P.nhsb*P.nvsb + sb0 + (t >> 4))*16 + (t & 15)] = best | (thr << 3);
+    }
+  }
+}
+
+void launch_dering(const DeringMaps &maps, const DeringParams &P, int *dirthr, int nframes,
+                   cudaStream_t st) {
+  const int npair = (P.nhsb + 1) >> 1;
+  dering_dir_kernel<<<dim3((unsigned)(npair*P.nvsb), (unsigned)nframes), kThreads, 0, st>>>(maps, P, dirthr);
+  dering_kernel<<<dim3((unsigned)(P.nhsb*P.nvsb), (unsigned)nframes), kThreads, 0, st>>>(maps, P, dirthr);
 }
 
 }  // namespace tdlt
@@ -651,7 +760,7 @@ __global__ void __launch_bounds__(kCoThreads) coding_order_kernel(CodingParams P
   const int step_f = gridDim.x/per2, step_pr = gridDim.x - step_f*per2;
   for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
     const int sb = 2*pr;
-    const int sby = (int)__umulhi((unsigned)sb, P.recip_nhsb), sbx = sb - sby*P.nhsb;
+    const int sby = div_recip(sb, P.recip_nhsb), sbx = sb - sby*P.nhsb;
     const unsigned char *map0 = P.bsize + (long long)frame*per*16 + (long long)(4*sby)*(4*P.nhsb) + 4*sbx;
     const unsigned char *const map[2] = {map0, map0 + 4};
     for (int p = 0; p < P.nplanes; p++) {

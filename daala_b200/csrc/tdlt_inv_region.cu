@@ -83,6 +83,14 @@ __device__ __forceinline__ bool ring_try(const RingSlot &r, int epoch) {
   return ok;
 }
 
+#ifdef TDLT_RINGSTAT
+// measurement build only (tools/ablate.py): how often the ring is not there yet
+__device__ unsigned long long g_ringstat[8];
+#define RINGSTAT(i, n) atomicAdd(&g_ringstat[i], (unsigned long long)(n))
+#else
+#define RINGSTAT(i, n) ((void)0)
+#endif
+
 template <bool kHaar, int kPix, bool kCoding>
 __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
                        const RegionBatch &bd,
@@ -144,12 +152,14 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   RingSlot rs = ring_slot(s.A, strips, lin, pd.nrx, id.rx > 0, id.ry > 0, tid);
   bool ring_early = false;
   {
-    ring_done = !rs.need || (TDLT_ABLATE & 32);
-    if (rs.need) {
+    ring_done = !rs.need || (TDLT_ABLATE & 32) || ((TDLT_ABLATE & 2048) && tid >= 128 && tid < 192);
+    if (!ring_done) {
       int2 p0 = ld_pair(rs.src), p1 = ld_pair(rs.src + 1);
       ring_early = p0.y == epoch && p1.y == epoch;
       ring_val = make_int2(p0.x, p1.x);
       ring_done = ring_early;
+      RINGSTAT(1, 1);
+      if (!ring_early) RINGSTAT(2, 1);
     }
   }
   TDLT_MARK(t, 1);
@@ -310,7 +320,10 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   // ---- the ring: whatever was not there yet when the region started --------------
   if (!ring_done) {
     if (pf0.y == epoch && pf1.y == epoch) *rs.dst = make_int2(pf0.x, pf1.x);
-    else while (!ring_try(rs, epoch)) __nanosleep(20);
+    else if (!(TDLT_ABLATE & 1024)) {
+      RINGSTAT(3, 1);
+      while (!ring_try(rs, epoch)) { RINGSTAT(4, 1); __nanosleep(20); }
+    }
   }
   __syncthreads();      // the ring is in A, and the strips were read before anyone laps them
   TDLT_MARK(t, 6);
@@ -392,3 +405,14 @@ tdlt_inv_haar_kernel(const __grid_constant__ TmapSet maps,
 
 
 }  // namespace tdlt
+
+#ifdef TDLT_RINGSTAT
+extern "C" int od_tdlt_debug_ringstat(unsigned long long *out, int reset) {
+  if (cudaMemcpyFromSymbol(out, tdlt::g_ringstat, sizeof(tdlt::g_ringstat)) != cudaSuccess) return -1;
+  if (reset) {
+    unsigned long long z[8] = {0};
+    cudaMemcpyToSymbol(tdlt::g_ringstat, z, sizeof(z));
+  }
+  return 0;
+}
+#endif

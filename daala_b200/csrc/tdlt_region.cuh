@@ -51,7 +51,7 @@ extern __device__ long long *g_tdlt_trace;
 #define TDLT_MINB 5
 #endif
 #ifndef TDLT_ABLATE
-#define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores
+#define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores, 1024 no polling for the ring (what is not there after the transforms is left out), 2048 the left neighbour's columns are not fetched at all
 #endif
 
 constexpr int kRegW = 128, kRegH = 64;       // region size in samples

@@ -529,7 +529,7 @@ def _dering_batch(rng, nframes, nhsb, nvsb, decs, skip_prob):
 
 @pytest.mark.parametrize("pic_w,pic_h,q,skip_prob", [
     (352, 288, 60, 0.3), (352, 288, 400, 0.7), (200, 136, 12, 0.0), (64, 64, 100, 0.5),
-    (33, 17, 33, 0.2), (1920, 1080, 80, 0.5)])
+    (33, 17, 33, 0.2), (20, 70, 90, 0.3), (90, 20, 50, 0.1), (1920, 1080, 80, 0.5)])
 def test_dering_frames_match_checker(pic_w, pic_h, q, skip_prob):
     """The deringing filter over whole frames (every superblock position, random decisions and
     skip maps, chroma reusing luma's directions) against the reference's od_dering."""
@@ -640,7 +640,8 @@ def test_dering_block_filters(bsi):
 
 @pytest.mark.parametrize("pic_w,pic_h,kind,decs", [
     (352, 288, "quad", (0, 1, 1)), (200, 136, "deep", (0, 1, 1)), (64, 64, "uniform3", (0, 1, 1)),
-    (96, 64, "quad", (0, 0, 0)), (352, 288, "uniform0", (0, 1, 1)), (1920, 1080, "quad", (0, 1, 1))])
+    (96, 64, "quad", (0, 0, 0)), (352, 288, "uniform0", (0, 1, 1)), (20, 70, "quad", (0, 1, 1)),
+    (1920, 1080, "quad", (0, 1, 1))])
 def test_coding_order_frames_match_checker(pic_w, pic_h, kind, decs):
     """Raster <-> coding order of every transform block with the reference's scan tables: the
     block-linear vectors against the restatement (pinned block by block against the reference's

@@ -43,7 +43,16 @@ if len(sys.argv) > 1 and sys.argv[1] == "--one":
         e1.record(); torch.cuda.synchronize()
         res.append(e0.elapsed_time(e1)/10)
     ok = all(torch.equal(a, b) for a, b in zip(c, c2))
-    print("fwd %.3f ms  inv %.3f ms  roundtrip %s" % (res[0], res[1], "ok" if ok else "WRONG"))
+    extra = ""
+    try:      # measurement builds (-DTDLT_RINGSTAT) count how often the inverse waits for its ring
+        import ctypes
+        fn = daala_b200._lib.od_tdlt_debug_ringstat
+        out = (ctypes.c_ulonglong*8)()
+        fn(out, 1); inv(); torch.cuda.synchronize(); fn(out, 0)
+        extra = "  ring: need %d, not there at start %d, not there after the transforms %d, polls %d" % (out[1], out[2], out[3], out[4])
+    except AttributeError:
+        pass
+    print("fwd %.3f ms  inv %.3f ms  roundtrip %s%s" % (res[0], res[1], "ok" if ok else "WRONG", extra))
     sys.exit(0)
 nframes = sys.argv[1] if len(sys.argv) > 1 else "64"
 kind = sys.argv[2] if len(sys.argv) > 2 else "quad"
