@@ -404,10 +404,12 @@ dering_kernel(const __grid_constant__ DeringMaps maps, const __grid_constant__ D
 // time (warp w: directions 2w and 2w + 1) with every lane busy.  Result per block: dir |
 // thr << 3 (threshold before the skip test) -> dirthr[(frame*nsb + sb)*16 + block].
 constexpr int kDirPitch = 2*kSB;
+constexpr int kBlkPitch = 68;          // words between the 8x8 blocks of the regrouped copy
 __global__ void __launch_bounds__(kThreads)
 dering_dir_kernel(const __grid_constant__ DeringMaps maps, const __grid_constant__ DeringParams P,
                   int *__restrict__ dirthr) {
-  __shared__ __align__(128) int T[kSB*kDirPitch];       // the pair's luma samples, then pixels
+  __shared__ __align__(128) int T[kSB*kDirPitch];       // the pair's luma samples, row by row
+  __shared__ __align__(16) int S[32*kBlkPitch];         // the same as pixels, block by block
   __shared__ __align__(8) unsigned long long bar;
   __shared__ int s_cost[32][9];
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -426,24 +428,27 @@ dering_dir_kernel(const __grid_constant__ DeringMaps maps, const __grid_constant
   }
   __syncthreads();
   mbar_wait(&bar, 0);
-  // pixel scale, in place: the reference searches (int16_t)x >> OD_COEFF_SHIFT
+  // pixel scale (the reference searches (int16_t)x >> OD_COEFF_SHIFT), regrouped block by
+  // block: block (superblock s, row by, column bx) = 64 words at S + (16 s + 4 by + bx)*68.
+  // With 17 16-byte chunks between blocks the eight lanes of a quarter warp, each reading
+  // the same chunk of its own block, hit eight different bank groups.
 #pragma unroll
   for (int it = 0; it < kSB*kDirPitch/4/kThreads; it++) {
-    int4 *q = reinterpret_cast<int4 *>(T) + t + it*kThreads;
-    int4 v = *q;
+    const int i = t + it*kThreads, r = i >> 4, c = i & 15;          // row, 16-byte chunk of the row
+    int4 v = reinterpret_cast<const int4 *>(T)[i];
     v.x = (short)v.x >> 4; v.y = (short)v.y >> 4; v.z = (short)v.z >> 4; v.w = (short)v.w >> 4;
-    *q = v;
+    const int blk = ((c >> 3) << 4) + ((r >> 3) << 2) + ((c >> 1) & 3);
+    *reinterpret_cast<int4 *>(S + blk*kBlkPitch + (r & 7)*8 + (c & 1)*4) = v;
   }
   __syncthreads();
   {
-    const int blk = lane & 15;
-    const int *bp = T + (blk >> 2)*8*kDirPitch + (lane >> 4)*kSB + (blk & 3)*8;
+    const int *bp = S + lane*kBlkPitch;                 // lane = block: 16*superblock + 4*by + bx
     int c0, c1;
     switch (warp) {                                     // uniform
-      case 0: dir_cost2<0, 1, kDirPitch>(bp, c0, c1); break;
-      case 1: dir_cost2<2, 3, kDirPitch>(bp, c0, c1); break;
-      case 2: dir_cost2<4, 5, kDirPitch>(bp, c0, c1); break;
-      default: dir_cost2<6, 7, kDirPitch>(bp, c0, c1); break;
+      case 0: dir_cost2<0, 1, 8>(bp, c0, c1); break;
+      case 1: dir_cost2<2, 3, 8>(bp, c0, c1); break;
+      case 2: dir_cost2<4, 5, 8>(bp, c0, c1); break;
+      default: dir_cost2<6, 7, 8>(bp, c0, c1); break;
     }
     s_cost[lane][2*warp] = c0;
     s_cost[lane][2*warp + 1] = c1;

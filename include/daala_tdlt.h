@@ -196,7 +196,11 @@ int od_tdlt_cfl_pred_batch(od_tdlt_ctx *ctx, od_coeff *l, const od_coeff *d_luma
             plane p, row stride nhsb*8 for every plane (state->bskip[p], skip_stride,
             src/state.c:450-463; 4:2:0 chroma uses the upper-left quarter);
      q[p]:  the plane quantizers (state->quantizer[p]) of this batch, HOST array.
-   4:4:4 or 4:2:0.  DEVICE pointers in out/in/flags/bskip, asynchronous on `stream`. */
+   4:4:4 or 4:2:0.  DEVICE pointers in out/in/flags/bskip (16-byte aligned planes),
+   asynchronous on `stream`, at most 65535 frames per call.  Two kernels: the direction
+   search of the luma blocks, then the filters; 64 bytes per superblock of context-owned
+   device scratch pass between them (grown on demand), so calls on one context must be
+   ordered by their stream like every other call here. */
 int od_tdlt_dering_batch(od_tdlt_ctx *ctx, od_coeff *const out[], const od_coeff *const in[],
  const unsigned char *flags, const unsigned char *const bskip[], const int q[], int nframes,
  void *stream);
