@@ -107,6 +107,21 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, int bytes, 
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
       :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// 1-D bulk copy shared -> global (16-byte aligned, size a multiple of 16) in the calling
+// thread's bulk group; the thread must wait for its group before the CTA's shared memory
+// may go away.  Shared memory written with ordinary stores needs fence_proxy_async_smem()
+// by the writers (and a barrier) before the copy engine reads it.
+__device__ __forceinline__ void bulk_s2g(void *dst, const void *src, int bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_wait_read() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
 // 3-D tiled load: coordinates (x, y, frame), innermost first.
 __device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, void *bar,
                                             int x, int y, int z) {

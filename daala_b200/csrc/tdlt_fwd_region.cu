@@ -171,7 +171,7 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
                      ((size_t)(TY >> lS)*sbw + (TX >> lS))*(size_t)(1 << 2*lS);
         region_store_tile_coding(At, ls0, bd.cotab, pd.dec, gtile, sbw << 2*lS, lane);
       }
-      else if (!(TDLT_ABLATE & 16)) {
+      else if (!(TDLT_ABLATE & 16) && !TDLT_BULK_STORE) {
         int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + TY + (lane >> 3))*pd.w + TX + 4*(lane & 7);
         const int *a = At + (lane >> 3)*kAP + 4*(lane & 7);
 #pragma unroll
@@ -180,6 +180,16 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
               *reinterpret_cast<const int4 *>(a + 4*it*kAP);
         }
       }
+    }
+  }
+  if (TDLT_BULK_STORE && !(TDLT_ABLATE & 16) && (haar || !(bd.flags & kFlagCodingOrder))) {
+    // the region's rows go out by the copy engine, one bulk copy of up to 512 bytes per row
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid < kRegH && Y0 + tid < pd.h) {
+      int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + tid)*pd.w + X0;
+      bulk_s2g(g, s.A + (tid + 2)*kAP + 4, 4*min(kRegW, pd.w - X0));
+      bulk_commit_wait_read();
     }
   }
   TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 6);

@@ -341,6 +341,7 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
     const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
     int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
     if (!(TDLT_ABLATE & 1)) region_lap_pass<true>(s.A, s.ub, s.msk, last_r ? kCellsFwd : kCellsInv, warp, lane);
+    if (TDLT_BULK_STORE_INV && !kPix) fence_proxy_async_smem();   // the copy engine reads A next
     __syncthreads();
     if (kPix) {
       // od_coeff_to_ref_buf fused into the store: out.p[] are planes of kPix-byte samples
@@ -348,7 +349,9 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
                           (((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2))*kPix;
       region_store_owned_pix<(kPix ? kPix : 1)>(s.A, gp, (size_t)pd.w*kPix, b0, b1, cs, ce, bd.pix_shift, warp, lane);
     }
-    else if (!(TDLT_ABLATE & 128)) region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
+    else if (TDLT_ABLATE & 128) { }
+    else if (TDLT_BULK_STORE_INV) region_store_owned_bulk(s.A, g, (size_t)pd.w, b0, b1, cs, ce, tid);
+    else region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
   }
   TDLT_MARK(t, 8);
 }

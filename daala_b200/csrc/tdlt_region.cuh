@@ -50,6 +50,12 @@ extern __device__ long long *g_tdlt_trace;
 #ifndef TDLT_MINB
 #define TDLT_MINB 5
 #endif
+#ifndef TDLT_BULK_STORE
+#define TDLT_BULK_STORE 1   // forward: the coefficient rows leave shared memory as bulk copies (measured -2.5 %)
+#endif
+#ifndef TDLT_BULK_STORE_INV
+#define TDLT_BULK_STORE_INV 0   // inverse: the same for the owned rectangle (measured +1 %: off)
+#endif
 #ifndef TDLT_ABLATE
 #define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores, 1024 no polling for the ring (what is not there after the transforms is left out), 2048 the left neighbour's columns are not fetched at all
 #endif
@@ -434,6 +440,23 @@ __device__ __forceinline__ void region_store_owned(const int *A, int *g, size_t 
     if (half) *reinterpret_cast<int2 *>(grow) = make_int2(v.x, v.y);
     if (left) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
   }
+}
+
+// The same by the copy engine: one thread per row issues a bulk copy of the row's 16-byte
+// aligned part (region columns 0 .. 123, or up to where the plane ends) and stores the 8-byte
+// pieces at either end itself.  The caller has fenced the lapping pass's writes
+// (fence_proxy_async_smem) before its barrier.
+__device__ __forceinline__ void region_store_owned_bulk(const int *A, int *g, size_t pitch, int b0,
+                                                        int b1, int cs, int ce, int tid) {
+  const int b = b0 + tid;
+  if (b >= b1) return;
+  const int nb = ce & ~3;                               // columns that go out in bulk (124, or all)
+  const int *arow = A + b*kAP + 4;                      // -> region column 0
+  int *grow = g + (size_t)b*pitch + 2;
+  bulk_s2g(grow, arow, 4*nb);
+  if (cs < 0) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
+  if (ce > nb) *reinterpret_cast<int2 *>(grow + nb) = *reinterpret_cast<const int2 *>(arow + nb);
+  bulk_commit_wait_read();
 }
 
 // The same with the samples narrowed to kPix-byte reference-buffer pixels on the way out
