@@ -453,9 +453,16 @@ __device__ __forceinline__ void region_store_owned_bulk(const int *A, int *g, si
   const int nb = ce & ~3;                               // columns that go out in bulk (124, or all)
   const int *arow = A + b*kAP + 4;                      // -> region column 0
   int *grow = g + (size_t)b*pitch + 2;
-  bulk_s2g(grow, arow, 4*nb);
-  if (cs < 0) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
-  if (ce > nb) *reinterpret_cast<int2 *>(grow + nb) = *reinterpret_cast<const int2 *>(arow + nb);
+  // (TDLT_BULK_STORE_INV 2: no end pieces, 3: 384 bytes only -- timing experiments, wrong results)
+  if (TDLT_BULK_STORE_INV == 4 && nb > 96) {            // whole 128-byte lines, then the rest
+    bulk_s2g(grow, arow, 384);
+    bulk_s2g(grow + 96, arow + 96, 4*(nb - 96));
+  }
+  else bulk_s2g(grow, arow, TDLT_BULK_STORE_INV == 3 ? 384 : 4*nb);
+  if (TDLT_BULK_STORE_INV == 1 || TDLT_BULK_STORE_INV == 4) {
+    if (cs < 0) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
+    if (ce > nb) *reinterpret_cast<int2 *>(grow + nb) = *reinterpret_cast<const int2 *>(arow + nb);
+  }
   bulk_commit_wait_read();
 }
 
