@@ -186,9 +186,24 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
     // the region's rows go out by the copy engine, one bulk copy of up to 512 bytes per row
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid < kRegH && Y0 + tid < pd.h) {
-      int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + tid)*pd.w + X0;
-      bulk_s2g(g, s.A + (tid + 2)*kAP + 4, 4*min(kRegW, pd.w - X0));
+    // (warp w: rows 8w .. 8w+7, issued by one elected lane from warp-uniform addresses -- a
+    // copy per lane compiles to a loop over the lanes, the copy engine's operands being
+    // uniform registers)
+    const int wu = __shfl_sync(0xffffffffu, warp, 0);
+    constexpr int kRows = kRegH/kRegWarps;
+    const int bytes = 4*min(kRegW, pd.w - X0);
+    const int n = min(kRegH, pd.h - Y0) - kRows*wu;     // rows of this warp that exist
+    if (elect_one()) {
+      unsigned long long ga = reinterpret_cast<unsigned long long>(
+          out.p[id.pli] + ((size_t)id.frame*pd.h + Y0 + kRows*wu)*pd.w + X0);
+      unsigned sa = smem_u32(s.A + (kRows*wu + 2)*kAP + 4);
+      const unsigned long long gstep = 4ull*pd.w;
+#pragma unroll
+      for (int i = 0; i < kRows; i++) {
+        if (i < n) bulk_s2g_addr(ga, sa, bytes);
+        ga += gstep;
+        sa += 4*kAP;
+      }
       bulk_commit_wait_read();
     }
   }

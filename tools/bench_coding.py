@@ -93,6 +93,13 @@ def main():
                                              out=np.full(want.shape, 1 << 30, np.int32)) != (1 << 30)
         assert np.array_equal(back[p][0].cpu().numpy()[covered], d[p][0].cpu().numpy()[covered])
     line["parity"] = "frame 0 equal to the oracle, round trip exact on the ordered coefficients"
+    if not args.no_cpu and ol.have_ref():
+        # od_raster_to_coding_order itself, block by block, against the GPU's planes (before the
+        # fused runs below reuse the buffers)
+        for p, dec in enumerate(bench.DECS):
+            want = ol.ref_coding_order_plane_c(d[p][0].cpu().numpy(), maps_np[0], dec, True)
+            assert np.array_equal(v[p][0].cpu().numpy(), want), "plane %d differs from the reference" % p
+        line["parity"] += "; frame 0 equal to the compiled reference"
     # ---- the permutation fused into the transform kernels (OD_TDLT_CODING_ORDER) -------------
     # forward: coefficients leave as vectors; inverse: they arrive as vectors.  Timed against
     # the same kernels writing / reading the raster plane (plan kernel included in the forward).
@@ -122,11 +129,6 @@ def main():
     if not args.no_cpu:
         a = [t[0].cpu().numpy() for t in d]
         use_ref = ol.have_ref()
-        if use_ref:      # od_raster_to_coding_order itself, block by block, against the GPU's planes
-            for p, dec in enumerate(bench.DECS):
-                want = ol.ref_coding_order_plane_c(a[p], maps_np[0], dec, True)
-                assert np.array_equal(v[p][0].cpu().numpy(), want), "plane %d differs from the reference" % p
-            line["parity"] += "; frame 0 equal to the compiled reference"
         t0 = time.perf_counter()
         reps = 0
         while time.perf_counter() - t0 < 5.0:
