@@ -337,8 +337,9 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
   {
     const int b0 = (id.ry == 0) ? 2 : 0;
     const int b1 = last_r ? min(kRegH, pd.h - Y0) + 2 : kRegH;
-    const int cs = (id.rx > 0) ? -2 : 0;
-    const int ce = last_c ? min(kRegW, pd.w - X0) : kRegW - 2;
+    // (TDLT_ABLATE 4096: whole sectors only -- columns 0 .. 127, wrong at the region seams)
+    const int cs = (id.rx > 0 && !(TDLT_ABLATE & 4096)) ? -2 : 0;
+    const int ce = (last_c || (TDLT_ABLATE & 4096)) ? min(kRegW, pd.w - X0) : kRegW - 2;
     int *g = out.p[id.pli] + ((ptrdiff_t)id.frame*pd.h + Y0 - 2)*(ptrdiff_t)pd.w + (X0 - 2);
     if (!(TDLT_ABLATE & 1)) region_lap_pass<true>(s.A, s.ub, s.msk, last_r ? kCellsFwd : kCellsInv, warp, lane);
     if (TDLT_BULK_STORE_INV && !kPix) fence_proxy_async_smem();   // the copy engine reads A next
@@ -350,6 +351,7 @@ __device__ __forceinline__ void tdlt_inv_region_body(const TmapSet &maps,
       region_store_owned_pix<(kPix ? kPix : 1)>(s.A, gp, (size_t)pd.w*kPix, b0, b1, cs, ce, bd.pix_shift, warp, lane);
     }
     else if (TDLT_ABLATE & 128) { }
+    else if (TDLT_BULK_STORE_INV == 5) region_store_owned_mixed(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
     else if (TDLT_BULK_STORE_INV) region_store_owned_bulk(s.A, g, (size_t)pd.w, b0, b1, cs, ce, tid);
     else region_store_owned(s.A, g, (size_t)pd.w, b0, b1, cs, ce, warp, lane);
   }

@@ -54,10 +54,10 @@ extern __device__ long long *g_tdlt_trace;
 #define TDLT_BULK_STORE 1   // forward: the coefficient rows leave shared memory as bulk copies (measured -2.5 %)
 #endif
 #ifndef TDLT_BULK_STORE_INV
-#define TDLT_BULK_STORE_INV 0   // inverse: the same for the owned rectangle (measured +1 %: off)
+#define TDLT_BULK_STORE_INV 0   // inverse: the same for the owned rectangle (measured +1 %: off; 2 .. 5 are the experiments of DESIGN section 4)
 #endif
 #ifndef TDLT_ABLATE
-#define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores, 1024 no polling for the ring (what is not there after the transforms is left out), 2048 the left neighbour's columns are not fetched at all
+#define TDLT_ABLATE 0    // 1: no lapping, 2: no transforms, 4: no DC pyramid, 8: no set-up, 16: no global I/O (forward); inverse: 32 no strip exchange, 64 ticket = blockIdx, 128 no output stores, 1024 no polling for the ring (what is not there after the transforms is left out), 2048 the left neighbour's columns are not fetched at all, 4096 the inverse stores columns 0 .. 127 (whole sectors, wrong at the seams)
 #endif
 
 constexpr int kRegW = 128, kRegH = 64;       // region size in samples
@@ -462,6 +462,41 @@ __device__ __forceinline__ void region_store_owned_bulk(const int *A, int *g, si
   if (TDLT_BULK_STORE_INV == 1 || TDLT_BULK_STORE_INV == 4) {
     if (cs < 0) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
     if (ce > nb) *reinterpret_cast<int2 *>(grow + nb) = *reinterpret_cast<const int2 *>(arow + nb);
+  }
+  bulk_commit_wait_read();
+}
+
+// Mixed form: the first 96 columns of every owned row (three whole 128-byte lines of the
+// plane) leave as a bulk copy issued by one elected lane per warp, the columns 96 .. ce-1 and
+// the two left of the region by ordinary stores, four rows per warp instruction (lane = row
+// of the four, 16-byte chunk of the eight).  The caller has fenced the lapping pass's writes.
+__device__ __forceinline__ void region_store_owned_mixed(const int *A, int *g, size_t pitch, int b0,
+                                                         int b1, int cs, int ce, int warp, int lane) {
+  constexpr int kBulkCols = 96, kRowsPerWarp = 9;       // 8 x 9 rows cover the 66 a region can own
+  const int wu = __shfl_sync(0xffffffffu, warp, 0);
+  const int nbulk = min(ce, kBulkCols);
+  if (elect_one()) {
+    const int bfirst = max(b0, kRowsPerWarp*wu);
+    unsigned long long ga = reinterpret_cast<unsigned long long>(g + (size_t)bfirst*pitch + 2);
+    unsigned sa = smem_u32(A + bfirst*kAP + 4);
+    const int n = min(b1, kRowsPerWarp*(wu + 1)) - bfirst;
+#pragma unroll
+    for (int i = 0; i < kRowsPerWarp; i++) {
+      if (i < n) bulk_s2g_addr(ga, sa, 4*nbulk);
+      ga += 4ull*pitch;
+      sa += 4*kAP;
+    }
+  }
+  // the rest of the rows
+  const int c = kBulkCols + 4*(lane & 7);
+  const bool full = c + 3 < ce, half = !full && c + 1 < ce, left = (lane & 7) == 0 && cs < 0;
+#pragma unroll 1
+  for (int b = b0 + 4*warp + (lane >> 3); b < b1; b += 4*kRegWarps) {
+    const int *arow = A + b*kAP + 4;
+    int *grow = g + (size_t)b*pitch + 2;
+    if (full) *reinterpret_cast<int4 *>(grow + c) = *reinterpret_cast<const int4 *>(arow + c);
+    if (half) *reinterpret_cast<int2 *>(grow + c) = *reinterpret_cast<const int2 *>(arow + c);
+    if (left) *reinterpret_cast<int2 *>(grow - 2) = *reinterpret_cast<const int2 *>(arow - 2);
   }
   bulk_commit_wait_read();
 }
