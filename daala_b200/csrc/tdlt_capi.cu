@@ -939,7 +939,13 @@ static int run_frames_queue(od_tdlt_ctx *ctx, const FramesJob &j) {
       else {
         const RegionPlane &pd = ctx->rb.pl[p];
         const size_t row = (size_t)pd.w*j.xstride;
-        for (int f = f0; f < f0 + n; f++) {
+        if ((size_t)j.ystride[p] == row && (size_t)j.frame_stride[p] == row*pd.h) {
+          // dense frames one after the other: the chunk's pixels in one copy
+          CK(ctx, cudaMemcpyAsync((char *)ctx->dev_pix[p] + (size_t)f0*row*pd.h,
+                                  (const char *)j.pix_in[p] + (size_t)f0*row*pd.h, row*pd.h*n,
+                                  cudaMemcpyHostToDevice, s_in));
+        }
+        else for (int f = f0; f < f0 + n; f++) {
           CK(ctx, cudaMemcpy2DAsync((char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row,
                                     (const char *)j.pix_in[p] + f*j.frame_stride[p], j.ystride[p],
                                     row, pd.h, cudaMemcpyHostToDevice, s_in));
@@ -1002,7 +1008,12 @@ static int run_frames_queue(od_tdlt_ctx *ctx, const FramesJob &j) {
       else {
         const RegionPlane &pd = ctx->rb.pl[p];
         const size_t row = (size_t)pd.w*j.xstride;
-        for (int f = f0; f < f0 + n; f++) {
+        if ((size_t)j.ystride[p] == row && (size_t)j.frame_stride[p] == row*pd.h) {
+          CK(ctx, cudaMemcpyAsync((char *)j.pix_out[p] + (size_t)f0*row*pd.h,
+                                  (const char *)ctx->dev_pix[p] + (size_t)f0*row*pd.h, row*pd.h*n,
+                                  cudaMemcpyDeviceToHost, s_out));
+        }
+        else for (int f = f0; f < f0 + n; f++) {
           CK(ctx, cudaMemcpy2DAsync((char *)j.pix_out[p] + f*j.frame_stride[p], j.ystride[p],
                                     (const char *)ctx->dev_pix[p] + (size_t)f*row*pd.h, row, row,
                                     pd.h, cudaMemcpyDeviceToHost, s_out));
