@@ -244,7 +244,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=0,
                     help="host threads of the e2e figure, one context and one batch each "
-                         "(0 = 4 on one GPU, 2 per rank under torchrun)")
+                         "(0 = 6 on one GPU, 2 per rank under torchrun)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary lines (fused pixel kernels, 16-bit / pageable e2e, neighbours)")
@@ -512,10 +512,11 @@ def main():
         # independent), each running whole steps on its own batch, started a fraction of a
         # step apart: the forward call is download-heavy (pixels up, od_coeff down), the
         # inverse call upload-heavy, so the two directions of the link are busy at the same
-        # time.  Measured on one GPU (profiles/e2e_threads_r2l.txt): 2 / 3 / 4 threads reach
-        # 0.79 / 0.83 / 0.85 of the link; under torchrun the ranks already share the host's
-        # link, two per rank reach 0.96 at N = 2.
-        nthr = args.e2e_threads if args.e2e_threads > 0 else (4 if world == 1 else 2)
+        # time.  Measured on one GPU (profiles/e2e_threads_r2w.txt): 1 / 2 / 4 / 6 / 8 threads
+        # reach 0.67 / 0.78 / 0.89 / 0.93-0.95 / 1.0 of the link (6 pin 48 GB of host memory);
+        # under torchrun the ranks already share the host's link, two per rank reach 0.96 at
+        # N = 2.
+        nthr = args.e2e_threads if args.e2e_threads > 0 else (6 if world == 1 else 2)
         L = ctx.L
         arr = daala_b200._ptr_array
         ctxs = [ctx] + [daala_b200.TdltContext(pic_w, pic_h, device=local_rank, max_frames=nframes)
