@@ -150,28 +150,37 @@ __device__ __forceinline__ void tdlt_fwd_region_body(const TmapSet &maps,
     TDLT_MARK(blockIdx.y*gridDim.x + blockIdx.x, 5);
   }
 
-  // ---- per tile (warp w <-> tile w): DC pyramid (or the Haar wavelet), then the tile
-  // goes out: 4 rows of 128 bytes per warp instruction ---------------------------
-  {
+  // ---- keyframe DC pyramid of the tiles: the warps 0..3 take two tiles each, 16 lanes per
+  // tile (half the instructions of one tile per warp); lossless mode: the Haar wavelet of
+  // its tile by every warp.  Then the region goes out.
+  const bool coding = !haar && (bd.flags & kFlagCodingOrder);
+  if (haar) {
+    const int tx = warp & 3, ty = warp >> 2;
+    if (X0 + 32*tx < pd.w && Y0 + 32*ty < pd.h) {
+      region_haar_tile<false>(s.A + (32*ty + 2)*kAP + 32*tx + 4, lane, 32 >> pd.dec);
+    }
+  }
+  else if ((bd.flags & 1) && warp < kRegTiles/2 && !(TDLT_ABLATE & 4)) {
+    const int tl = 2*warp + (lane >> 4), ttx = tl & 3, tty = tl >> 2;
+    const bool on = X0 + 32*ttx < pd.w && Y0 + 32*tty < pd.h;
+    region_dc_merge_tile(s.A + (32*tty + 2)*kAP + 32*ttx + 4, s.ls + ut(4*tty, 4*ttx), lane, on,
+                         pd.dec == 0);
+  }
+  if (coding || !TDLT_BULK_STORE) {
+    if (!haar) __syncthreads();           // the pyramid of a tile is another warp's work
     const int tx = warp & 3, ty = warp >> 2;
     const int TX = X0 + 32*tx, TY = Y0 + 32*ty;
     if (TX < pd.w && TY < pd.h) {
       int *At = s.A + (32*ty + 2)*kAP + 32*tx + 4;
-      const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
-      if (haar) {
-        region_haar_tile<false>(At, lane, 32 >> pd.dec);
-      }
-      else if ((bd.flags & 1) && !(TDLT_ABLATE & 4)) {
-        region_dc_merge_tile(At, ls0, lane, pd.dec == 0);
-      }
-      if (!haar && (bd.flags & kFlagCodingOrder)) {
+      if (coding) {
         // the tile leaves as the coding-order vectors of its blocks (block-linear plane)
+        const unsigned char *ls0 = s.ls + ut(4*ty, 4*tx);
         const int lS = 5 - pd.dec, sbw = pd.w >> lS;
         int *gtile = out.p[id.pli] + (size_t)id.frame*pd.w*pd.h +
                      ((size_t)(TY >> lS)*sbw + (TX >> lS))*(size_t)(1 << 2*lS);
         region_store_tile_coding(At, ls0, bd.cotab, pd.dec, gtile, sbw << 2*lS, lane);
       }
-      else if (!(TDLT_ABLATE & 16) && !TDLT_BULK_STORE) {
+      else if (!(TDLT_ABLATE & 16)) {
         int *g = out.p[id.pli] + ((size_t)id.frame*pd.h + TY + (lane >> 3))*pd.w + TX + 4*(lane & 7);
         const int *a = At + (lane >> 3)*kAP + 4*(lane & 7);
 #pragma unroll

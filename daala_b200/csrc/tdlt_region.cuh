@@ -799,17 +799,19 @@ __device__ __forceinline__ void a_row32(int *a, int *v) {     // a -> (row lane,
 // ---- keyframe DC pyramid on one tile (reference src/encode.c:1328-1341,
 // src/decode.c:733).  At -> the tile's origin in A, ls0 -> unit table entry of the
 // tile's first unit.
-// The forward direction (bottom-up merge) of a whole tile in ONE step: lane j < 16
+// The forward direction (bottom-up merge) of a whole tile in ONE step: lane j of a half warp
 // takes unit j of the tile -- the DCs of its 4x4 blocks if it is split -- and the levels
 // above travel by shuffle: the four lanes of a 16x16 quadrant exchange their unit DCs,
 // the lanes 0, 2, 8, 10 the quadrant DCs (luma only: in 4:2:0 chroma the tile is four
 // superblocks).  Every lane of a group computes the group's butterfly redundantly and
 // keeps its own output.  Called by the whole warp.
 __device__ __forceinline__ void region_dc_merge_tile(int *At, const unsigned char *ls0, int lane,
-                                                     bool luma) {
+                                                     bool act, bool luma) {
+  // lane = 0..31: the unit (lane & 15) of the tile of this half warp (At / ls0 / act may
+  // differ between the halves: two tiles per warp); the shuffles stay inside the half
+  const int hb = lane & 16;
   const int uy = (lane >> 2) & 3, ux = lane & 3;
   int *U = At + 8*uy*kAP + 8*ux;
-  const bool act = lane < 16;
   int vu = 0, L = 3, Lq = 3;
   if (act) {
     L = ls0[uy*kUS + ux];
@@ -831,9 +833,9 @@ __device__ __forceinline__ void region_dc_merge_tile(int *At, const unsigned cha
     }
   }
   if (luma) {
-    const int L0 = __shfl_sync(0xffffffffu, L, 0);
-    int q0 = __shfl_sync(0xffffffffu, vu, 0), q1 = __shfl_sync(0xffffffffu, vu, 2);
-    int q2 = __shfl_sync(0xffffffffu, vu, 8), q3 = __shfl_sync(0xffffffffu, vu, 10);
+    const int L0 = __shfl_sync(0xffffffffu, L, hb);
+    int q0 = __shfl_sync(0xffffffffu, vu, hb), q1 = __shfl_sync(0xffffffffu, vu, hb + 2);
+    int q2 = __shfl_sync(0xffffffffu, vu, hb + 8), q3 = __shfl_sync(0xffffffffu, vu, hb + 10);
     if (L0 < 3 && !(lane & 5)) {
       haar2x2(q0, q2, q1, q3);
       vu = (lane & 8) ? ((lane & 2) ? q3 : q2) : ((lane & 2) ? q1 : q0);
