@@ -84,35 +84,25 @@ tdlt_plan_kernel(const __grid_constant__ RegionBatch bd, const unsigned char *__
       unsigned char *ub = rec[k] + (kOffUb - kOffLs);
       unsigned char *tasks = rec[k] + (kOffTasks - kOffLs);
       int *cnt = reinterpret_cast<int *>(rec[k] + (kOffCnt - kOffLs));
-      int L = 0xFF, bits = 0, which = -1;
-      if (inside[k]) {
-        L = haar ? 3 : max(raw[k], dec) - dec;
-        if (!haar) {
-          const int X = 8*(ux0 + kRegUX*k);
-          const int nm = (4 << L) - 1;          // block size - 1
-          if (Y > 0) {
-            // an edge inside the unit's block is no edge; the mid-edge of a split block
-            // is filtered along the whole block iff the block's right side is inside
-            // the picture
-            bool e = top_sb || (!(Y & nm) && (X & -nbY) + nbY <= bd.pic_w);
-            if (e) bits |= kUbTop;
-          }
-          if (X > 0) {
-            const int nbX = 2*(X & -X);
-            bool e = !(X & (sb - 1)) || (!(X & nm) && (Y & -nbX) + nbX <= bd.pic_h);
-            if (e) bits |= kUbLeft;
-          }
-          if (L == 0) {
-            if (X + 8 <= bd.pic_w) bits |= kUbMidH;
-            if (midv_in) bits |= kUbMidV;
-          }
-        }
-        if (owned) {
-          if (L <= 1) which = L;
-          else if (L == 2 && !(UR & 1) && !(UC & 1)) which = 2;
-          else if (L == 3 && !(UR & 3) && !(UC & 3)) which = 3;
-        }
-      }
+      // Branch-free (bitwise and / or, selects): the lanes of a warp differ in every one of
+      // these conditions.
+      const bool in = inside[k];
+      const int Lin = haar ? 3 : max(raw[k], dec) - dec;
+      const int X = 8*(ux0 + kRegUX*k);
+      const int nm = (4 << Lin) - 1;          // block size - 1
+      const int nbX = 2*(X & -X);
+      // an edge inside the unit's block is no edge; the mid-edge of a split block is filtered
+      // along the whole block iff the block's right (bottom) side is inside the picture
+      const bool eT = (Y > 0) & (top_sb | (((Y & nm) == 0) & ((X & -nbY) + nbY <= bd.pic_w)));
+      const bool eL = (X > 0) & (((X & (sb - 1)) == 0) | (((X & nm) == 0) & ((Y & -nbX) + nbX <= bd.pic_h)));
+      const bool l0 = Lin == 0;
+      int bits = (eT ? kUbTop : 0) | (eL ? kUbLeft : 0) | ((l0 & (X + 8 <= bd.pic_w)) ? kUbMidH : 0) |
+                 ((l0 & midv_in) ? kUbMidV : 0);
+      bits = (in & !haar) ? bits : 0;
+      const int L = in ? Lin : 0xFF;
+      const bool first2 = ((UR | UC) & 1) == 0, first3 = ((UR | UC) & 3) == 0;
+      int which = Lin <= 1 ? Lin : ((Lin == 2) & first2) ? 2 : ((Lin == 3) & first3) ? 3 : -1;
+      which = (in & owned) ? which : -1;
       if (active) {
         ls[r*kUS + c] = (unsigned char)L;
         ub[r*kUS + c] = (unsigned char)bits;
