@@ -517,6 +517,16 @@ def main():
         # under torchrun the ranks already share the host's link, two per rank reach 0.96 at
         # N = 2.
         nthr = args.e2e_threads if args.e2e_threads > 0 else (6 if world == 1 else 2)
+        if args.e2e_threads <= 0:
+            # every thread holds its own host planes (od_coeff + 16-bit pixels of a batch):
+            # stay well inside the host's free memory, two threads at least
+            try:
+                import psutil
+                per_thread = 6 * samples_per_frame * nframes * world
+                while nthr > 2 and 2 * nthr * per_thread > psutil.virtual_memory().available:
+                    nthr -= 1
+            except ImportError:
+                pass
         L = ctx.L
         arr = daala_b200._ptr_array
         ctxs = [ctx] + [daala_b200.TdltContext(pic_w, pic_h, device=local_rank, max_frames=nframes)
