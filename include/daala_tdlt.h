@@ -5,6 +5,12 @@
  * stream crosses the boundary as a void*).  Each entry point cites the
  * reference interface it replaces (KyleSiefring/daala, file:line).
  *
+ * Results equal the reference's bit for bit for every input whose intermediate
+ * products stay inside 32 bits in the reference's own transforms (what its
+ * OD_DCT_OVERFLOW_CHECK asserts; 8- to 16-bit video is far inside).  Where the
+ * reference's int arithmetic overflows its answer is that of signed overflow in
+ * the compiled C and is not reproduced.
+ *
  * Three layers, coarsest first:
  *   1. device-resident batch calls   (od_tdlt_fwd_batch / od_tdlt_inv_batch)
  *      -- what bench.py times as `value`; pointers are DEVICE pointers.

@@ -1,0 +1,110 @@
+#!/usr/bin/env python3
+"""Randomised parity sweep (test infrastructure, like tests/): random picture sizes, map
+kinds, plane layouts, frame counts and flags through the whole-frame C-ABI calls, against the
+CPU checker (the compiled reference when it is built, else the restatement).  Bit-exact or
+it stops.  One summary line on stdout.
+
+  python tools/fuzz_parity.py [--seconds 120] [--seed 1]
+"""
+import argparse
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--seconds", type=float, default=120.0)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--coeff", type=int, default=8000,
+                    help="range of the arbitrary coefficients fed to the inverse (inside the domain in "
+                         "which the reference's own int32 products do not overflow: DESIGN.md section 5)")
+    ap.add_argument("--start", type=int, default=0, help="draw the first N cases without running them")
+    ap.add_argument("--dump", default="", help="on a mismatch, write the case to this .npz")
+    args = ap.parse_args()
+    import daala_b200
+    import oracle_libs as ol
+    from checker import Checker, make_maps
+    rng = np.random.default_rng(args.seed)
+    kinds = ["quad", "deep", "uniform0", "uniform1", "uniform2", "uniform3"]
+    layouts = [(0, 1, 1), (0, 1, 1), (0, 1, 1), (0,), (0, 0, 0)]
+    t0 = time.time()
+    cases = 0
+    samples = 0
+    t_run = None
+    while True:
+        if cases >= args.start:
+            if t_run is None:
+                t_run = time.time()
+            elif time.time() - t_run > args.seconds:
+                break
+        pic_w = int(rng.integers(8, 700))
+        pic_h = int(rng.integers(8, 420))
+        decs = layouts[int(rng.integers(len(layouts)))]
+        kind = kinds[int(rng.integers(len(kinds)))]
+        nframes = int(rng.integers(1, 4))
+        key = int(rng.integers(2))
+        haar = int(rng.integers(8) == 0)
+        if haar:
+            kind = "uniform3"       # lossless mode codes whole superblocks (src/encode.c:3090)
+        flags = (daala_b200.OD_TDLT_KEYFRAME if key else 0) | (daala_b200.OD_TDLT_HAAR if haar else 0)
+        desc = "%dx%d decs %s %s frames %d key %d haar %d" % (pic_w, pic_h, decs, kind, nframes, key, haar)
+        if cases < args.start:
+            # keep the random stream aligned: the same draws, no GPU or checker work
+            fw, fh = (pic_w + 63) & ~63, (pic_h + 63) & ~63
+            make_maps(kind, nframes, fw // 32, fh // 32, rng)
+            for lo_, hi_ in ((-2048, 2048), (-args.coeff, args.coeff)):
+                for dec in decs:
+                    rng.integers(lo_, hi_, size=(nframes, fh >> dec, fw >> dec))
+            cases += 1
+            continue
+        if cases == args.start and args.start:
+            print("first case run:", desc, flush=True)
+        chk = Checker(pic_w, pic_h)
+        with daala_b200.TdltContext(pic_w, pic_h, decs=decs, device=0, max_frames=nframes) as ctx:
+            bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+            c = [rng.integers(-2048, 2048, size=(nframes,) + s).astype(np.int32) for s in ctx.plane_shapes]
+            d = [np.zeros_like(a) for a in c]
+            ctx.fwd_frames(d, c, bsize, flags)
+            d_ref = chk.fwd_frames(c, bsize, decs, key, haar=haar)
+            for p in range(len(decs)):
+                assert np.array_equal(d[p], d_ref[p]), "forward plane %d: %s" % (p, desc)
+            c2 = [np.zeros_like(a) for a in c]
+            ctx.inv_frames(c2, d, bsize, flags)
+            for p in range(len(decs)):
+                assert np.array_equal(c2[p], c[p]), "round trip plane %d: %s" % (p, desc)
+            dq = [rng.integers(-args.coeff, args.coeff, size=a.shape).astype(np.int32) for a in c]
+            ctx.inv_frames(c2, dq, bsize, flags)
+            c_ref = chk.inv_frames(dq, bsize, decs, key, haar=haar)
+            for p in range(len(decs)):
+                if not np.array_equal(c2[p], c_ref[p]):
+                    bad = np.argwhere(c2[p] != c_ref[p])
+                    print("MISMATCH inverse plane %d: %s: case %d, %d samples, frames %s rows %s cols %s" % (
+                        p, desc, cases, len(bad), sorted(set(bad[:, 0].tolist())),
+                        sorted(set(bad[:, 1].tolist()))[:24], sorted(set(bad[:, 2].tolist()))[:24]))
+                    again = [np.zeros_like(a) for a in c]
+                    ctx.inv_frames(again, dq, bsize, flags)
+                    print("  the same call again: %s" % ("equal to the checker" if np.array_equal(again[p], c_ref[p])
+                                                        else "differs again"))
+                    if args.dump:
+                        np.savez_compressed(args.dump, pic=np.array([pic_w, pic_h]), decs=np.array(decs),
+                                            key=key, bsize=bsize, **{"dq%d" % i: a for i, a in enumerate(dq)},
+                                            **{"gpu%d" % i: a for i, a in enumerate(c2)},
+                                            **{"ref%d" % i: a for i, a in enumerate(c_ref)})
+                    raise SystemExit(1)
+            samples += sum(a.size for a in c)
+        chk.close()
+        cases += 1
+    print("fuzz_parity: %d random cases, %.1f Msamples, all bit-exact against %s (seed %d, %.0f s)"
+          % (cases, samples / 1e6, "the compiled reference" if ol.have_ref() else "the restatement",
+             args.seed, time.time() - t0))
+
+
+if __name__ == "__main__":
+    main()
