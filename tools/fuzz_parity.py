@@ -22,6 +22,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=120.0)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--what", default="tdlt", choices=["tdlt", "dering"],
+                    help="tdlt: forward / inverse; dering: the deringing filter over whole frames")
     ap.add_argument("--coeff", type=int, default=8000,
                     help="range of the arbitrary coefficients fed to the inverse (inside the domain in "
                          "which the reference's own int32 products do not overflow: DESIGN.md section 5)")
@@ -32,6 +34,8 @@ def main():
     import oracle_libs as ol
     from checker import Checker, make_maps
     rng = np.random.default_rng(args.seed)
+    if args.what == "dering":
+        return fuzz_dering(args, rng)
     kinds = ["quad", "deep", "uniform0", "uniform1", "uniform2", "uniform3"]
     layouts = [(0, 1, 1), (0, 1, 1), (0, 1, 1), (0,), (0, 0, 0)]
     t0 = time.time()
@@ -102,6 +106,46 @@ def main():
         chk.close()
         cases += 1
     print("fuzz_parity: %d random cases, %.1f Msamples, all bit-exact against %s (seed %d, %.0f s)"
+          % (cases, samples / 1e6, "the compiled reference" if ol.have_ref() else "the restatement",
+             args.seed, time.time() - t0))
+
+
+def fuzz_dering(args, rng):
+    """Random sizes, 4:2:0 or 4:4:4, quantizers and skip densities through od_tdlt_dering_frames
+    against the reference's od_dering (the loop of src/decode.c:1044-1122)."""
+    import daala_b200
+    import oracle_libs as ol
+    from checker import Checker
+    t0 = time.time()
+    cases = 0
+    samples = 0
+    while time.time() - t0 < args.seconds:
+        pic_w = int(rng.integers(8, 500))
+        pic_h = int(rng.integers(8, 300))
+        decs = (0, 1, 1) if rng.integers(4) else (0, 0, 0)
+        nframes = int(rng.integers(1, 4))
+        q = int(rng.integers(1, 600))
+        skip_prob = float(rng.random())
+        qs = (q, max(1, 3 * q // 4), max(1, q // 2))
+        desc = "%dx%d decs %s frames %d q %d skip %.2f" % (pic_w, pic_h, decs, nframes, q, skip_prob)
+        chk = Checker(pic_w, pic_h)
+        with daala_b200.TdltContext(pic_w, pic_h, decs=decs, device=0, max_frames=nframes) as ctx:
+            fr = [ol.dering_test_frame(rng, ctx.nhsb, ctx.nvsb, decs, skip_prob=skip_prob) for _ in range(nframes)]
+            planes = [np.stack([f[0][p] for f in fr]) for p in range(3)]
+            flags = np.stack([f[1] for f in fr])
+            bskip = [np.stack([f[2][p] for f in fr]) for p in range(3)]
+            out = [np.full_like(p, 77777) for p in planes]
+            ctx.dering_frames(out, planes, flags, bskip, qs)
+            want = chk.dering_frames(planes, decs, flags, bskip, qs)
+            for p in range(3):
+                if not np.array_equal(out[p], want[p]):
+                    bad = np.argwhere(out[p] != want[p])
+                    print("MISMATCH dering plane %d: %s: %d samples, first %s" % (p, desc, len(bad), bad[0]))
+                    raise SystemExit(1)
+            samples += sum(a.size for a in planes)
+        chk.close()
+        cases += 1
+    print("fuzz_parity dering: %d random cases, %.1f Msamples, all bit-exact against %s (seed %d, %.0f s)"
           % (cases, samples / 1e6, "the compiled reference" if ol.have_ref() else "the restatement",
              args.seed, time.time() - t0))
 
