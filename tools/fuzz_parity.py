@@ -22,7 +22,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=120.0)
     ap.add_argument("--seed", type=int, default=1)
-    ap.add_argument("--what", default="tdlt", choices=["tdlt", "dering"],
+    ap.add_argument("--what", default="tdlt", choices=["tdlt", "dering", "pix"],
                     help="tdlt: forward / inverse; dering: the deringing filter over whole frames")
     ap.add_argument("--coeff", type=int, default=8000,
                     help="range of the arbitrary coefficients fed to the inverse (inside the domain in "
@@ -36,6 +36,8 @@ def main():
     rng = np.random.default_rng(args.seed)
     if args.what == "dering":
         return fuzz_dering(args, rng)
+    if args.what == "pix":
+        return fuzz_pix(args, rng)
     kinds = ["quad", "deep", "uniform0", "uniform1", "uniform2", "uniform3"]
     layouts = [(0, 1, 1), (0, 1, 1), (0, 1, 1), (0,), (0, 0, 0)]
     t0 = time.time()
@@ -108,6 +110,75 @@ def main():
     print("fuzz_parity: %d random cases, %.1f Msamples, all bit-exact against %s (seed %d, %.0f s)"
           % (cases, samples / 1e6, "the compiled reference" if ol.have_ref() else "the restatement",
              args.seed, time.time() - t0))
+
+
+def fuzz_pix(args, rng):
+    """The pixel-facing whole-frame calls (conversion fused into the transform kernels): random
+    sizes, 8- and 16-bit reference buffers, dense or padded rows, quadtree maps; forward
+    against od_ref_buf_to_coeff + the checker's forward, inverse against the checker's inverse
+    + od_coeff_to_ref_buf, and nothing outside the picture window may change."""
+    import daala_b200
+    import oracle_libs as ol
+    from checker import Checker, make_maps
+    port = ol.port()
+    decs = (0, 1, 1)
+    t0 = time.time()
+    cases = 0
+    samples = 0
+    while time.time() - t0 < args.seconds:
+        pic_w = int(rng.integers(8, 700))
+        pic_h = int(rng.integers(8, 420))
+        xstride, mode, lossless = [(1, 1, 0), (2, 2, 0), (2, 3, 0), (1, 2, 0), (2, 1, 0)][int(rng.integers(5))]
+        nframes = int(rng.integers(1, 4))
+        pad = int(rng.integers(3)) * 16
+        kind = ["quad", "deep", "uniform1"][int(rng.integers(3))]
+        desc = "%dx%d xstride %d mode %d frames %d pad %d %s" % (pic_w, pic_h, xstride, mode, nframes, pad, kind)
+        chk = Checker(pic_w, pic_h)
+        with daala_b200.TdltContext(pic_w, pic_h, decs=decs, device=0, max_frames=nframes) as ctx:
+            bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+            pix, views = [], []
+            for (h, w) in ctx.plane_shapes:
+                if xstride == 1:
+                    buf = rng.integers(0, 256, size=(nframes, h + 2 * pad, w + 2 * pad)).astype(np.uint8)
+                else:
+                    buf = rng.integers(0, 4096, size=(nframes, h + 2 * pad, w + 2 * pad)).astype(np.int16)
+                pix.append(buf)
+                views.append(buf[:, pad:pad + h, pad:pad + w])
+            d = [np.zeros((nframes,) + sh, np.int32) for sh in ctx.plane_shapes]
+            ctx.fwd_frames_pix(d, views, bsize, 1, xstride=xstride, bitdepth_mode=mode, lossless=lossless)
+            c = []
+            for v in views:
+                cc = np.zeros(v.shape, np.int32)
+                for f in range(nframes):
+                    src = np.ascontiguousarray(v[f])
+                    port.oc_buf_to_coeff(mode, ol.ptr(cc[f]), v.shape[2], lossless, ol.ptr(src.view(np.uint8)),
+                                         xstride, src.strides[0], v.shape[2], v.shape[1])
+                c.append(cc)
+            d_ref = chk.fwd_frames(c, bsize, decs, 1)
+            for p in range(3):
+                assert np.array_equal(d[p], d_ref[p]), "forward plane %d: %s" % (p, desc)
+            outs = [np.full_like(b, 7) for b in pix]
+            oviews = [b[:, pad:pad + sh[0], pad:pad + sh[1]] for b, sh in zip(outs, ctx.plane_shapes)]
+            dq = [(a // 3) * 3 for a in d]
+            ctx.inv_frames_pix(oviews, dq, bsize, 1, xstride=xstride, bitdepth_mode=mode, lossless=lossless)
+            c_ref = chk.inv_frames(dq, bsize, decs, 1)
+            for p in range(3):
+                h, w = ctx.plane_shapes[p]
+                exp = np.zeros((nframes, h, w), pix[p].dtype)
+                for f in range(nframes):
+                    tmp = np.zeros((h, w * xstride), np.uint8)
+                    port.oc_coeff_to_buf(mode, ol.ptr(tmp), xstride, w * xstride, ol.ptr(c_ref[p][f]), w,
+                                         lossless, w, h)
+                    exp[f] = tmp.view(pix[p].dtype).reshape(h, w)
+                assert np.array_equal(oviews[p], exp), "inverse plane %d: %s" % (p, desc)
+                border = outs[p].copy()
+                border[:, pad:pad + h, pad:pad + w] = 7
+                assert (border == 7).all(), "outside the window, plane %d: %s" % (p, desc)
+            samples += sum(a.size for a in d)
+        chk.close()
+        cases += 1
+    print("fuzz_parity pix: %d random cases, %.1f Msamples, all bit-exact (seed %d, %.0f s)"
+          % (cases, samples / 1e6, args.seed, time.time() - t0))
 
 
 def fuzz_dering(args, rng):
