@@ -22,7 +22,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seconds", type=float, default=120.0)
     ap.add_argument("--seed", type=int, default=1)
-    ap.add_argument("--what", default="tdlt", choices=["tdlt", "dering", "pix"],
+    ap.add_argument("--what", default="tdlt", choices=["tdlt", "dering", "pix", "coding"],
                     help="tdlt: forward / inverse; dering: the deringing filter over whole frames")
     ap.add_argument("--coeff", type=int, default=8000,
                     help="range of the arbitrary coefficients fed to the inverse (inside the domain in "
@@ -38,6 +38,8 @@ def main():
         return fuzz_dering(args, rng)
     if args.what == "pix":
         return fuzz_pix(args, rng)
+    if args.what == "coding":
+        return fuzz_coding(args, rng)
     kinds = ["quad", "deep", "uniform0", "uniform1", "uniform2", "uniform3"]
     layouts = [(0, 1, 1), (0, 1, 1), (0, 1, 1), (0,), (0, 0, 0)]
     t0 = time.time()
@@ -178,6 +180,64 @@ def fuzz_pix(args, rng):
         chk.close()
         cases += 1
     print("fuzz_parity pix: %d random cases, %.1f Msamples, all bit-exact (seed %d, %.0f s)"
+          % (cases, samples / 1e6, args.seed, time.time() - t0))
+
+
+def fuzz_coding(args, rng):
+    """OD_TDLT_CODING_ORDER through the device-pointer batch calls: the forward kernel's
+    block-linear coding-order vectors against forward + od_raster_to_coding_order, the inverse
+    kernel's load of them against od_coding_order_to_raster (into a cleared block) + inverse."""
+    import torch
+    import daala_b200
+    import oracle_libs as ol
+    from checker import Checker, make_maps
+    dev = torch.device("cuda", 0)
+    tables = ol.scan_tables()
+    KEY, CO = daala_b200.OD_TDLT_KEYFRAME, daala_b200.OD_TDLT_CODING_ORDER
+    t0 = time.time()
+    cases = 0
+    samples = 0
+    ptrs = lambda ts: [t.data_ptr() for t in ts]  # noqa: E731
+    while time.time() - t0 < args.seconds:
+        pic_w = int(rng.integers(8, 600))
+        pic_h = int(rng.integers(8, 360))
+        decs = (0, 1, 1) if rng.integers(4) else (0, 0, 0)
+        kind = ["quad", "deep", "uniform0", "uniform1", "uniform2", "uniform3"][int(rng.integers(6))]
+        nframes = int(rng.integers(1, 4))
+        desc = "%dx%d decs %s %s frames %d" % (pic_w, pic_h, decs, kind, nframes)
+        chk = Checker(pic_w, pic_h)
+        with daala_b200.TdltContext(pic_w, pic_h, decs=decs, device=0, max_frames=0) as ctx:
+            ctx.set_scan_tables(tables, ol.SCAN_LEN)
+            bsize = make_maps(kind, nframes, ctx.nhsb, ctx.nvsb, rng)
+            maps = torch.from_numpy(bsize).to(dev)
+            st = torch.cuda.current_stream().cuda_stream
+            c_np = [rng.integers(-2048, 2048, size=(nframes,) + sh).astype(np.int32) for sh in ctx.plane_shapes]
+            c = [torch.from_numpy(a).to(dev) for a in c_np]
+            v = [torch.full_like(t, 424242) for t in c]
+            ctx.fwd_batch(ptrs(v), ptrs(c), maps.data_ptr(), nframes, KEY | CO, st)
+            torch.cuda.synchronize()
+            d_ref = chk.fwd_frames(c_np, bsize, decs, 1)
+            d0 = []
+            for p, dec in enumerate(decs):
+                zeroed = np.zeros_like(d_ref[p])
+                vp = v[p].cpu().numpy()
+                for f in range(nframes):
+                    want = ol.port_coding_order_plane(d_ref[p][f], bsize[f], dec, tables, True,
+                                                      out=np.full_like(d_ref[p][f], 424242))
+                    assert np.array_equal(vp[f], want), "fused store plane %d frame %d: %s" % (p, f, desc)
+                    zeroed[f] = ol.port_coding_order_plane(want, bsize[f], dec, tables, False,
+                                                           out=np.zeros_like(d_ref[p][f]))
+                d0.append(zeroed)
+            c_b = [torch.empty_like(t) for t in c]
+            ctx.inv_batch(ptrs(c_b), ptrs(v), maps.data_ptr(), nframes, KEY | CO, st)
+            torch.cuda.synchronize()
+            c_ref = chk.inv_frames(d0, bsize, decs, 1)
+            for p in range(3):
+                assert np.array_equal(c_b[p].cpu().numpy(), c_ref[p]), "fused load plane %d: %s" % (p, desc)
+            samples += sum(a.size for a in c_np)
+        chk.close()
+        cases += 1
+    print("fuzz_parity coding: %d random cases, %.1f Msamples, all bit-exact (seed %d, %.0f s)"
           % (cases, samples / 1e6, args.seed, time.time() - t0))
 
 
