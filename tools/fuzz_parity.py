@@ -27,6 +27,9 @@ def main():
     ap.add_argument("--coeff", type=int, default=8000,
                     help="range of the arbitrary coefficients fed to the inverse (inside the domain in "
                          "which the reference's own int32 products do not overflow: DESIGN.md section 5)")
+    ap.add_argument("--max-frames", type=int, default=3,
+                    help="tdlt: frames per case are drawn from 1 .. this (the inverse kernel picks one of "
+                         "three region orders by batch size: < 16, < 48, >= 48)")
     ap.add_argument("--start", type=int, default=0, help="draw the first N cases without running them")
     ap.add_argument("--dump", default="", help="on a mismatch, write the case to this .npz")
     args = ap.parse_args()
@@ -56,7 +59,7 @@ def main():
         pic_h = int(rng.integers(8, 420))
         decs = layouts[int(rng.integers(len(layouts)))]
         kind = kinds[int(rng.integers(len(kinds)))]
-        nframes = int(rng.integers(1, 4))
+        nframes = int(rng.integers(1, args.max_frames + 1))
         key = int(rng.integers(2))
         haar = int(rng.integers(8) == 0)
         if haar:
